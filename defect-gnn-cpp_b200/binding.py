@@ -1,0 +1,249 @@
+"""ctypes binding to libdgnn_b200.so -- the C ABI declared in include/dgnn_cabi.h.
+
+This is plumbing for tests / bench / smoke only (Python owns no part of the hot path): it passes plain pointers
+through the C ABI exactly like the C++ facade in host/ does.  There is NO CPU fallback: if the shared library or a
+CUDA device is missing every call raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libdgnn_b200.so")
+
+UNCAPPED = 2**64 - 1
+INPUT_DEVICE = 0x1
+SKIP_RBF = 0x2
+
+EXPORTS = [
+    "dgnn_abi_version", "dgnn_strerror", "dgnn_last_error", "dgnn_create", "dgnn_destroy", "dgnn_build",
+    "dgnn_copy_to_host", "dgnn_copy_edges_to_host", "dgnn_rbf_expand", "dgnn_rbf_expand_f64",
+    "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
+]
+
+
+class DgnnBatch(C.Structure):
+    _fields_ = [
+        ("n_structs", C.c_int64),
+        ("atom_offsets", C.c_void_p),
+        ("x", C.c_void_p),
+        ("y", C.c_void_p),
+        ("z", C.c_void_p),
+        ("lattice", C.c_void_p),
+        ("r_cutoff", C.c_double),
+        ("max_neighbors", C.c_uint64),
+        ("epsilon", C.c_double),
+        ("rbf_r_cutoff", C.c_double),
+        ("dr", C.c_double),
+        ("flags", C.c_uint32),
+    ]
+
+
+class DgnnGraphs(C.Structure):
+    _fields_ = [
+        ("n_structs", C.c_int64),
+        ("n_atoms", C.c_int64),
+        ("n_edges", C.c_int64),
+        ("K", C.c_int32),
+        ("max_degree", C.c_int32),
+        ("row_ptr", C.c_void_p),
+        ("dst", C.c_void_p),
+        ("image", C.c_void_p),
+        ("dist", C.c_void_p),
+        ("rbf", C.c_void_p),
+        ("struct_edge_offsets", C.c_void_p),
+        ("n_near_cutoff", C.c_int64),
+        ("n_tie_rows", C.c_int64),
+    ]
+
+
+class DgnnBuildInfo(C.Structure):
+    _fields_ = [
+        ("h2d_ms", C.c_float), ("bin_ms", C.c_float), ("count_ms", C.c_float), ("fill_ms", C.c_float),
+        ("rbf_ms", C.c_float), ("total_ms", C.c_float),
+        ("kernel_launches", C.c_int32), ("n_items", C.c_int32), ("cloud_points", C.c_int64),
+        ("staged_tile_cap", C.c_int32), ("row_cap", C.c_int32),
+    ]
+
+
+class DgnnError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"dgnn error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def load_library():
+    """Load libdgnn_b200.so; raises (never falls back) if it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FileNotFoundError(
+                f"{LIB_PATH} is missing: build it with __graft_entry__.build() (nvcc, sm_100a). "
+                "There is no CPU fallback.")
+        L = C.CDLL(LIB_PATH)
+        L.dgnn_abi_version.restype = C.c_int
+        L.dgnn_strerror.argtypes = [C.c_int]
+        L.dgnn_strerror.restype = C.c_char_p
+        L.dgnn_last_error.argtypes = [C.c_void_p]
+        L.dgnn_last_error.restype = C.c_char_p
+        L.dgnn_create.argtypes = [C.c_int, C.c_size_t, C.POINTER(C.c_void_p)]
+        L.dgnn_create.restype = C.c_int
+        L.dgnn_destroy.argtypes = [C.c_void_p]
+        L.dgnn_destroy.restype = None
+        L.dgnn_build.argtypes = [C.c_void_p, C.POINTER(DgnnBatch), C.POINTER(DgnnGraphs)]
+        L.dgnn_build.restype = C.c_int
+        L.dgnn_copy_to_host.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs)] + [C.c_void_p] * 6
+        L.dgnn_copy_to_host.restype = C.c_int
+        L.dgnn_copy_edges_to_host.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs), C.c_int64, C.c_int64] + [C.c_void_p] * 4
+        L.dgnn_copy_edges_to_host.restype = C.c_int
+        L.dgnn_rbf_expand.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_double, C.c_double, C.c_void_p,
+                                      C.POINTER(C.c_int32)]
+        L.dgnn_rbf_expand.restype = C.c_int
+        L.dgnn_rbf_expand_f64.argtypes = L.dgnn_rbf_expand.argtypes
+        L.dgnn_rbf_expand_f64.restype = C.c_int
+        L.dgnn_last_build_info.argtypes = [C.c_void_p, C.POINTER(DgnnBuildInfo)]
+        L.dgnn_last_build_info.restype = C.c_int
+        L.dgnn_stream.argtypes = [C.c_void_p]
+        L.dgnn_stream.restype = C.c_void_p
+        L.dgnn_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
+        L.dgnn_set_option.restype = C.c_int
+        _lib = L
+    return _lib
+
+
+@dataclass
+class HostGraphs:
+    """Host copy of a build result (numpy)."""
+    n_structs: int
+    n_atoms: int
+    n_edges: int
+    K: int
+    max_degree: int
+    row_ptr: np.ndarray
+    dst: np.ndarray
+    image: np.ndarray  # int8 [E,4]
+    dist: np.ndarray
+    rbf: np.ndarray | None
+    struct_edge_offsets: np.ndarray
+    n_near_cutoff: int
+    n_tie_rows: int
+
+
+def _ptr(a) -> int | None:
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    if hasattr(a, "data_ptr"):  # torch tensor (host pinned or device)
+        return a.data_ptr()
+    return int(a)
+
+
+class GraphBuilder:
+    """One dgnn_ctx (one CUDA device).  Mirrors the call sequence of the C++ facade."""
+
+    def __init__(self, device: int = 0, arena_bytes: int = 0):
+        self.lib = load_library()
+        h = C.c_void_p()
+        rc = self.lib.dgnn_create(int(device), int(arena_bytes), C.byref(h))
+        if rc != 0:
+            raise DgnnError(rc, self.lib.dgnn_strerror(rc).decode() + " (dgnn_create; a B200 is required, no CPU fallback)")
+        self.h = h
+        self.device = device
+        self.last = None
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.dgnn_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise DgnnError(rc, self.lib.dgnn_last_error(self.h).decode() or self.lib.dgnn_strerror(rc).decode())
+
+    def set_option(self, name: str, value: float):
+        self._check(self.lib.dgnn_set_option(self.h, name.encode(), float(value)))
+
+    @property
+    def stream(self) -> int:
+        return int(self.lib.dgnn_stream(self.h) or 0)
+
+    def build(self, atom_offsets, x, y, z, lattices, r_cutoff=10.0, max_neighbors=20, epsilon=1e-10,
+              rbf_r_cutoff=10.0, dr=0.1, device_inputs=False, skip_rbf=False) -> DgnnGraphs:
+        """dgnn_build.  Inputs: numpy arrays / pinned torch tensors (host) or device tensors (device_inputs=True)."""
+        if isinstance(atom_offsets, np.ndarray):
+            atom_offsets = np.ascontiguousarray(atom_offsets, dtype=np.int64)
+            x, y, z = (np.ascontiguousarray(a, dtype=np.float64) for a in (x, y, z))
+            lattices = np.ascontiguousarray(lattices, dtype=np.float64)
+            n_structs = atom_offsets.shape[0] - 1
+        else:
+            n_structs = int(atom_offsets.shape[0]) - 1
+        self._keep = (atom_offsets, x, y, z, lattices)  # keep inputs alive during the call
+        b = DgnnBatch(n_structs, _ptr(atom_offsets), _ptr(x), _ptr(y), _ptr(z), _ptr(lattices), float(r_cutoff),
+                      C.c_uint64(int(max_neighbors)), float(epsilon), float(rbf_r_cutoff),
+                      float(dr if dr is not None else 0.0),
+                      (INPUT_DEVICE if device_inputs else 0) | (SKIP_RBF if (skip_rbf or dr is None) else 0))
+        g = DgnnGraphs()
+        self._check(self.lib.dgnn_build(self.h, C.byref(b), C.byref(g)))
+        self.last = g
+        return g
+
+    def info(self) -> DgnnBuildInfo:
+        i = DgnnBuildInfo()
+        self._check(self.lib.dgnn_last_build_info(self.h, C.byref(i)))
+        return i
+
+    def to_host(self, g: DgnnGraphs | None = None, with_rbf: bool = True) -> HostGraphs:
+        g = g or self.last
+        e = int(g.n_edges)
+        row_ptr = np.empty(g.n_atoms + 1, dtype=np.int64)
+        seo = np.empty(g.n_structs + 1, dtype=np.int64)
+        dst = np.empty(e, dtype=np.int32)
+        image = np.empty(e, dtype=np.int32)
+        dist = np.empty(e, dtype=np.float64)
+        rbf = np.empty((e, g.K), dtype=np.float32) if (with_rbf and g.K > 0 and g.rbf) else None
+        self._check(self.lib.dgnn_copy_to_host(self.h, C.byref(g), _ptr(row_ptr), _ptr(dst), _ptr(image), _ptr(dist),
+                                               _ptr(rbf), _ptr(seo)))
+        return HostGraphs(int(g.n_structs), int(g.n_atoms), e, int(g.K), int(g.max_degree), row_ptr, dst,
+                          image.view(np.int8).reshape(e, 4), dist, rbf, seo, int(g.n_near_cutoff),
+                          int(g.n_tie_rows))
+
+    def edges_to_host(self, e0: int, e1: int, g: DgnnGraphs | None = None, with_rbf: bool = True):
+        g = g or self.last
+        n = e1 - e0
+        dst = np.empty(n, dtype=np.int32)
+        image = np.empty(n, dtype=np.int32)
+        dist = np.empty(n, dtype=np.float64)
+        rbf = np.empty((n, g.K), dtype=np.float32) if (with_rbf and g.K > 0 and g.rbf) else None
+        self._check(self.lib.dgnn_copy_edges_to_host(self.h, C.byref(g), e0, e1, _ptr(dst), _ptr(image), _ptr(dist),
+                                                     _ptr(rbf)))
+        return dst, image.view(np.int8).reshape(n, 4), dist, rbf
+
+    def rbf_expand(self, dist, r_cutoff: float, dr: float, out=None, f64_colmajor: bool = False):
+        """graph::gaussian_rbf for many distances (edge_features.cpp:7-24).  dist/out: numpy or device tensors."""
+        n = int(dist.shape[0])
+        k = C.c_int32()
+        if isinstance(dist, np.ndarray):
+            dist = np.ascontiguousarray(dist, dtype=np.float64)
+        kk = int(np.floor(r_cutoff / dr))
+        if out is None:
+            out = np.empty((kk, n), dtype=np.float64) if f64_colmajor else np.empty((n, kk), dtype=np.float32)
+        fn = self.lib.dgnn_rbf_expand_f64 if f64_colmajor else self.lib.dgnn_rbf_expand
+        self._check(fn(self.h, _ptr(dist), n, float(r_cutoff), float(dr), _ptr(out), C.byref(k)))
+        assert k.value == kk
+        if f64_colmajor and isinstance(out, np.ndarray):
+            return out.T  # column-major E x K viewed as E x K
+        return out

@@ -1,0 +1,585 @@
+// dgnn_api.cu -- C ABI of libdgnn_b200.so (include/dgnn_cabi.h): context, device arena, build orchestration.
+// No CPU fallback: every entry point needs a CUDA device; failures are reported as status codes + message.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+
+#include "../../include/dgnn_cabi.h"
+#include "dgnn_internal.h"
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+};
+
+struct BuildEvents {
+    cudaEvent_t e[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+}  // namespace
+
+struct dgnn_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    int sm_count = 148;
+    int smem_optin = 0;
+    std::string err;
+    // inputs staged from host
+    DevBuf in_off, in_x, in_y, in_z, in_lat;
+    // planning / binning
+    DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
+    DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
+    // results
+    DevBuf deg, row_ptr, seo, dst, image, dist, rbf;
+    // stand-alone rbf staging
+    DevBuf tmp_in, tmp_out;
+    DevBuf stats;
+    DgStats* h_stats = nullptr;  // pinned
+    BuildEvents ev;
+    dgnn_build_info info{};
+    // options
+    double cell_frac = 0.5;
+    int tile_target = 2048;
+    int src_target = 512;
+    int tile_limit = 4096;
+    int traverse_grid_mult = 16;
+};
+
+namespace {
+
+int fail(dgnn_ctx* c, int code, const char* fmt, ...) {
+    if (c) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof(buf), fmt, ap);
+        va_end(ap);
+        c->err = buf;
+    }
+    return code;
+}
+
+#define CU(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t _e = (call);                                                                       \
+        if (_e != cudaSuccess)                                                                         \
+            return fail(ctx, _e == cudaErrorMemoryAllocation ? DGNN_ERR_OOM : DGNN_ERR_CUDA,           \
+                        "%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__, __LINE__);   \
+    } while (0)
+
+int ensure(dgnn_ctx* ctx, DevBuf& b, size_t bytes) {
+    if (bytes <= b.cap) return DGNN_OK;
+    if (b.p) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaFree(b.p));
+        b.p = nullptr;
+        b.cap = 0;
+    }
+    size_t want = bytes < (size_t(64) << 20) ? bytes + bytes / 2 + 256 : bytes + bytes / 16;
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        want = bytes;
+        e = cudaMalloc(&p, want);
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, DGNN_ERR_OOM, "device allocation of %zu bytes failed: %s", bytes, cudaGetErrorString(e));
+    }
+    b.p = p;
+    b.cap = want;
+    return DGNN_OK;
+}
+
+#define ENSURE(buf, bytes)                          \
+    do {                                            \
+        int _r = ensure(ctx, (buf), (bytes));       \
+        if (_r != DGNN_OK) return _r;               \
+    } while (0)
+
+void release(DevBuf& b) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.cap = 0;
+}
+
+int status_to_code(int st) {
+    switch (st) {
+        case DG_ST_SINGULAR: return DGNN_ERR_SINGULAR;
+        case DG_ST_IMAGE_RANGE: return DGNN_ERR_IMAGE_RANGE;
+        case DG_ST_GEOMETRY: return DGNN_ERR_GEOMETRY;
+        case DG_ST_UNWRAPPED: return DGNN_ERR_UNWRAPPED;
+        default: return DGNN_ERR_UNSUPPORTED;
+    }
+}
+
+bool is_device_ptr(const void* p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged;
+}
+
+int fetch_stats(dgnn_ctx* ctx) {
+    CU(cudaMemcpyAsync(ctx->h_stats, ctx->stats.p, sizeof(DgStats), cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return DGNN_OK;
+}
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+}  // namespace
+
+extern "C" {
+
+int dgnn_abi_version(void) { return DGNN_ABI_VERSION; }
+
+const char* dgnn_strerror(int code) {
+    switch (code) {
+        case DGNN_OK: return "ok";
+        case DGNN_ERR_INVALID_ARG: return "invalid argument";
+        case DGNN_ERR_CUDA: return "CUDA runtime error";
+        case DGNN_ERR_OOM: return "device out of memory";
+        case DGNN_ERR_SINGULAR: return "singular or non-finite lattice";
+        case DGNN_ERR_IMAGE_RANGE: return "reference image range exceeds 127";
+        case DGNN_ERR_GEOMETRY: return "cell too thin for the supported stencil reach";
+        case DGNN_ERR_UNWRAPPED: return "atoms too far outside the unit cell";
+        case DGNN_ERR_DEGREE: return "row degree exceeds the supported maximum";
+        case DGNN_ERR_TOO_LARGE: return "batch too large: split it";
+        case DGNN_ERR_UNSUPPORTED: return "unsupported";
+        default: return "unknown error";
+    }
+}
+
+const char* dgnn_last_error(const dgnn_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out) {
+    if (!out) return DGNN_ERR_INVALID_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0) {
+        cudaGetLastError();
+        return DGNN_ERR_CUDA;  // no CPU fallback by design
+    }
+    if (device < 0 || device >= ndev) return DGNN_ERR_INVALID_ARG;
+    dgnn_ctx* ctx = new (std::nothrow) dgnn_ctx();
+    if (!ctx) return DGNN_ERR_OOM;
+    ctx->device = device;
+    auto bail = [&](int code) {
+        dgnn_destroy(ctx);
+        return code;
+    };
+    if (cudaSetDevice(device) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (prop.major < 10) return bail(DGNN_ERR_UNSUPPORTED);  // sm_100a cubin only
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    for (auto& e : ctx->ev.e)
+        if (cudaEventCreate(&e) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (cudaMallocHost(&ctx->h_stats, sizeof(DgStats)) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (ensure(ctx, ctx->stats, sizeof(DgStats)) != DGNN_OK) return bail(DGNN_ERR_OOM);
+    if (arena_bytes > 0) {
+        // split the hint the way a K = 40 build uses it: 160 B features + 16 B edge arrays per edge
+        const size_t edges = arena_bytes / 176;
+        if (ensure(ctx, ctx->rbf, edges * 160) != DGNN_OK || ensure(ctx, ctx->dist, edges * 8) != DGNN_OK ||
+            ensure(ctx, ctx->dst, edges * 4) != DGNN_OK || ensure(ctx, ctx->image, edges * 4) != DGNN_OK)
+            return bail(DGNN_ERR_OOM);
+    }
+    *out = ctx;
+    return DGNN_OK;
+}
+
+void dgnn_destroy(dgnn_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->geoms, &ctx->astruct,
+                      &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
+                      &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
+                      &ctx->deg, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->tmp_in, &ctx->tmp_out, &ctx->stats};
+    for (DevBuf* b : bufs) release(*b);
+    if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
+    for (auto& e : ctx->ev.e)
+        if (e) cudaEventDestroy(e);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+void* dgnn_stream(dgnn_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
+    if (!ctx || !name) return DGNN_ERR_INVALID_ARG;
+    if (!strcmp(name, "cell_frac")) {
+        if (!(value >= 0.05 && value <= 4.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "cell_frac out of range");
+        ctx->cell_frac = value;
+    } else if (!strcmp(name, "tile_target")) {
+        if (!(value >= 64 && value <= 8192)) return fail(ctx, DGNN_ERR_INVALID_ARG, "tile_target out of range");
+        ctx->tile_target = (int)value;
+    } else if (!strcmp(name, "tile_limit")) {
+        if (!(value >= 0 && value <= 8192)) return fail(ctx, DGNN_ERR_INVALID_ARG, "tile_limit out of range");
+        ctx->tile_limit = (int)value;  // 0 forces the unstaged (global-memory) traversal everywhere
+    } else if (!strcmp(name, "src_target")) {
+        if (!(value >= 1 && value <= 1024)) return fail(ctx, DGNN_ERR_INVALID_ARG, "src_target out of range");
+        ctx->src_target = (int)value;
+    } else if (!strcmp(name, "traverse_grid_mult")) {
+        if (!(value >= 1 && value <= 64)) return fail(ctx, DGNN_ERR_INVALID_ARG, "traverse_grid_mult out of range");
+        ctx->traverse_grid_mult = (int)value;
+    } else {
+        return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s'", name);
+    }
+    return DGNN_OK;
+}
+
+int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out) {
+    if (!ctx || !out) return DGNN_ERR_INVALID_ARG;
+    *out = ctx->info;
+    return DGNN_OK;
+}
+
+int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    if (!b || !out) return fail(ctx, DGNN_ERR_INVALID_ARG, "null batch / output");
+    memset(out, 0, sizeof(*out));
+    ctx->err.clear();
+    const long long S = b->n_structs;
+    if (S < 0) return fail(ctx, DGNN_ERR_INVALID_ARG, "n_structs < 0");
+    if (!(b->r_cutoff > 0.0) || !std::isfinite(b->r_cutoff))
+        return fail(ctx, DGNN_ERR_INVALID_ARG, "r_cutoff must be positive and finite");
+    if (!b->atom_offsets) return fail(ctx, DGNN_ERR_INVALID_ARG, "atom_offsets is null");
+    if (S >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "too many structures");
+    const bool want_rbf = !(b->flags & DGNN_SKIP_RBF) && b->dr > 0.0;
+    int K = 0;
+    if (want_rbf) {
+        if (!(b->rbf_r_cutoff > 0.0) || !std::isfinite(b->rbf_r_cutoff))
+            return fail(ctx, DGNN_ERR_INVALID_ARG, "rbf_r_cutoff must be positive and finite");
+        const double kf = std::floor(b->rbf_r_cutoff / b->dr);  // edge_features.cpp:10
+        if (!(kf >= 1.0 && kf <= 65536.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "RBF bin count out of range");
+        K = (int)kf;
+    }
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    dg_num_kernel_launches_reset();
+    dg_rbf_launch_count_reset();
+    memset(&ctx->info, 0, sizeof(ctx->info));
+
+    // ---- inputs ----------------------------------------------------------------------------------------------
+    const bool dev_in = (b->flags & DGNN_INPUT_DEVICE) != 0;
+    long long N = 0;
+    CU(cudaEventRecord(ctx->ev.e[0], st));
+    const long long* d_off;
+    const double *d_x, *d_y, *d_z, *d_lat;
+    if (dev_in) {
+        CU(cudaMemcpyAsync(&N, b->atom_offsets + S, sizeof(long long), cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        d_off = (const long long*)b->atom_offsets;
+        d_x = b->x; d_y = b->y; d_z = b->z; d_lat = b->lattice;
+    } else {
+        if (b->atom_offsets[0] != 0) return fail(ctx, DGNN_ERR_INVALID_ARG, "atom_offsets[0] must be 0");
+        for (long long s = 0; s < S; ++s)
+            if (b->atom_offsets[s + 1] < b->atom_offsets[s])
+                return fail(ctx, DGNN_ERR_INVALID_ARG, "atom_offsets not monotone at structure %lld", s);
+        N = b->atom_offsets[S];
+    }
+    if (N < 0 || N >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "atom count %lld out of range", N);
+    if (N > 0 && (!b->x || !b->y || !b->z)) return fail(ctx, DGNN_ERR_INVALID_ARG, "coordinate pointer is null");
+    if (S > 0 && !b->lattice) return fail(ctx, DGNN_ERR_INVALID_ARG, "lattice pointer is null");
+    if (!dev_in) {
+        ENSURE(ctx->in_off, (size_t)(S + 1) * 8);
+        ENSURE(ctx->in_x, (size_t)N * 8 + 8);
+        ENSURE(ctx->in_y, (size_t)N * 8 + 8);
+        ENSURE(ctx->in_z, (size_t)N * 8 + 8);
+        ENSURE(ctx->in_lat, (size_t)S * 72 + 8);
+        CU(cudaMemcpyAsync(ctx->in_off.p, b->atom_offsets, (size_t)(S + 1) * 8, cudaMemcpyHostToDevice, st));
+        if (N > 0) {
+            CU(cudaMemcpyAsync(ctx->in_x.p, b->x, (size_t)N * 8, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(ctx->in_y.p, b->y, (size_t)N * 8, cudaMemcpyHostToDevice, st));
+            CU(cudaMemcpyAsync(ctx->in_z.p, b->z, (size_t)N * 8, cudaMemcpyHostToDevice, st));
+        }
+        if (S > 0) CU(cudaMemcpyAsync(ctx->in_lat.p, b->lattice, (size_t)S * 72, cudaMemcpyHostToDevice, st));
+        d_off = (const long long*)ctx->in_off.p;
+        d_x = (const double*)ctx->in_x.p; d_y = (const double*)ctx->in_y.p; d_z = (const double*)ctx->in_z.p;
+        d_lat = (const double*)ctx->in_lat.p;
+    }
+    CU(cudaEventRecord(ctx->ev.e[1], st));
+
+    // ---- K0: geometry + planning -------------------------------------------------------------------------------
+    ENSURE(ctx->geoms, (size_t)(S + 1) * sizeof(DgGeom));
+    ENSURE(ctx->astruct, (size_t)(N + 1) * 4);
+    ENSURE(ctx->acell, (size_t)(N + 1) * 12);
+    ENSURE(ctx->ncells32, (size_t)(S + 1) * 4);
+    ENSURE(ctx->nitems32, (size_t)(S + 1) * 4);
+    ENSURE(ctx->cell_base, (size_t)(S + 2) * 8);
+    ENSURE(ctx->item_base, (size_t)(S + 2) * 8);
+    ENSURE(ctx->row_ptr, (size_t)(N + 2) * 8);
+    ENSURE(ctx->deg, (size_t)(N + 1) * 4);
+    ENSURE(ctx->seo, (size_t)(S + 2) * 8);
+    CU(cudaMemsetAsync(ctx->stats.p, 0, sizeof(DgStats), st));
+    DgGeom* geoms = (DgGeom*)ctx->geoms.p;
+    DgStats* d_stats = (DgStats*)ctx->stats.p;
+    {
+        const long long mx = (N > S ? N : S) + 1;
+        ENSURE(ctx->scratch, (size_t)(mx / 2048 + 4) * 8);
+    }
+    dg_launch_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->cell_frac, geoms);
+    dg_launch_atom_cells(st, N, S, d_off, d_x, d_y, d_z, geoms, (int*)ctx->astruct.p, (int*)ctx->acell.p);
+    dg_launch_plan(st, S, geoms, ctx->tile_target, ctx->src_target, (int*)ctx->ncells32.p, (int*)ctx->nitems32.p,
+                   d_stats);
+    dg_scan_i32_i64(st, (const int*)ctx->ncells32.p, (long long*)ctx->cell_base.p, S, (long long*)ctx->scratch.p);
+    dg_scan_i32_i64(st, (const int*)ctx->nitems32.p, (long long*)ctx->item_base.p, S, (long long*)ctx->scratch.p);
+    dg_launch_plan_finish(st, S, geoms, (const long long*)ctx->cell_base.p, (const long long*)ctx->item_base.p,
+                          d_stats);
+    CU(cudaGetLastError());
+    {
+        int r = fetch_stats(ctx);  // sync 1: totals for the cell arrays
+        if (r != DGNN_OK) return r;
+    }
+    if (ctx->h_stats->err_status != 0)
+        return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
+                    dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
+    const long long n_cells = ctx->h_stats->n_cells;
+    const long long n_items = ctx->h_stats->n_items;
+    if (n_cells >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld grid cells: split the batch", n_cells);
+
+    // ---- K1: cell-list binning of the pruned image cloud -------------------------------------------------------
+    ENSURE(ctx->cellcount, (size_t)(n_cells + 1) * 4);
+    ENSURE(ctx->cellstart, (size_t)(n_cells + 2) * 8);
+    {
+        const size_t need = (size_t)(n_cells / 2048 + 4) * 8;
+        ENSURE(ctx->scratch, need);
+    }
+    CU(cudaMemsetAsync(ctx->cellcount.p, 0, (size_t)(n_cells + 1) * 4, st));
+    dg_launch_cloud_count(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p, (int*)ctx->cellcount.p);
+    dg_scan_i32_i64(st, (const int*)ctx->cellcount.p, (long long*)ctx->cellstart.p, n_cells,
+                    (long long*)ctx->scratch.p);
+    dg_launch_item_stats(st, n_items, S, geoms, (const long long*)ctx->item_base.p,
+                         (const long long*)ctx->cellstart.p, n_cells, d_stats);
+    CU(cudaGetLastError());
+    {
+        int r = fetch_stats(ctx);  // sync 2: cloud size, tile sizes
+        if (r != DGNN_OK) return r;
+    }
+    const long long P = ctx->h_stats->cloud_points;
+    if (P >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld image-cloud points: split the batch", P);
+    ENSURE(ctx->cx, (size_t)(P + 1) * 8);
+    ENSURE(ctx->cy, (size_t)(P + 1) * 8);
+    ENSURE(ctx->cz, (size_t)(P + 1) * 8);
+    ENSURE(ctx->cj, (size_t)(P + 1) * 4);
+    ENSURE(ctx->cn, (size_t)(P + 1) * 4);
+    dg_launch_cloud_scatter(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p, d_x, d_y, d_z,
+                            (const long long*)ctx->cellstart.p, (int*)ctx->cellcount.p, (double*)ctx->cx.p,
+                            (double*)ctx->cy.p, (double*)ctx->cz.p, (int*)ctx->cj.p, (uint32_t*)ctx->cn.p);
+    CU(cudaEventRecord(ctx->ev.e[2], st));
+
+    // ---- K2: count pass ----------------------------------------------------------------------------------------
+    DgTraverseArgs A;
+    memset(&A, 0, sizeof(A));
+    A.geoms = geoms;
+    A.item_base = (const long long*)ctx->item_base.p;
+    A.n_items = n_items;
+    A.n_structs = S;
+    A.cellstart = (const long long*)ctx->cellstart.p;
+    A.cx = (const double*)ctx->cx.p; A.cy = (const double*)ctx->cy.p; A.cz = (const double*)ctx->cz.p;
+    A.cj = (const int*)ctx->cj.p; A.cn = (const uint32_t*)ctx->cn.p;
+    A.r2 = b->r_cutoff * b->r_cutoff;  // neighbor_list.cpp:40
+    A.r_cutoff = b->r_cutoff;
+    A.rcm = DG_RCM(b->r_cutoff);
+    A.epsilon = b->epsilon;
+    A.inv_rc = (float)(1.0 / b->r_cutoff);
+    {
+        const double lo = b->r_cutoff - 2e-6 > 0 ? b->r_cutoff - 2e-6 : 0.0, hi = b->r_cutoff + 2e-6;
+        const double lo2 = lo * lo, hi2 = hi * hi;
+        long long lb, hb;
+        memcpy(&lb, &lo2, 8);
+        memcpy(&hb, &hi2, 8);
+        A.near_lo_hi = (int)(lb >> 32);
+        A.near_hi_hi = (int)(hb >> 32);
+    }
+    A.max_neighbors = b->max_neighbors > 0x7fffffffULL ? 0x7fffffff : (int)b->max_neighbors;
+    A.deg_capped = (int*)ctx->deg.p;
+    A.stats = d_stats;
+    // shared-memory plan: tile sized to the largest actual tile (bounded), rest goes the unstaged way
+    int tile_cap = round_up(ctx->h_stats->max_tile_pts > 32 ? ctx->h_stats->max_tile_pts : 32, 32);
+    if (tile_cap > ctx->tile_limit) tile_cap = ctx->tile_limit;
+    if (tile_cap < 32) tile_cap = 32;  // tile_limit 0: everything unstaged, keep a token tile
+    int tcs_cap = round_up(ctx->h_stats->max_tile_tcs > 4 ? ctx->h_stats->max_tile_tcs : 4, 4);
+    if (tcs_cap > 4096) tcs_cap = 4096;
+    A.tile_cap = ctx->tile_limit == 0 ? 0 : tile_cap;
+    A.tcs_cap = tcs_cap;
+    A.src_cap = 1024;
+    A.row_cap = 0;
+    A.n_buckets = 32;
+    A.n_warps = 8;
+    const int grid = (int)((long long)ctx->sm_count * ctx->traverse_grid_mult < n_items
+                               ? (long long)ctx->sm_count * ctx->traverse_grid_mult
+                               : (n_items > 0 ? n_items : 1));
+    if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)
+        return fail(ctx, DGNN_ERR_UNSUPPORTED, "count-pass shared memory plan does not fit");
+    CU(dg_launch_traverse(st, A, false, grid));
+    dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+    dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
+    CU(cudaGetLastError());
+    CU(cudaEventRecord(ctx->ev.e[3], st));
+    {
+        int r = fetch_stats(ctx);  // sync 3: E and the largest row
+        if (r != DGNN_OK) return r;
+    }
+    const long long E = ctx->h_stats->n_edges;
+    const int max_deg = ctx->h_stats->max_deg;
+    if (max_deg > DGNN_MAX_DEGREE)
+        return fail(ctx, DGNN_ERR_DEGREE, "row degree %d exceeds %d: lower r_cutoff", max_deg, DGNN_MAX_DEGREE);
+
+    // ---- K2: fill pass (rows -> sorted CSR) --------------------------------------------------------------------
+    ENSURE(ctx->dst, (size_t)(E + 1) * 4);
+    ENSURE(ctx->image, (size_t)(E + 1) * 4);
+    ENSURE(ctx->dist, (size_t)(E + 1) * 8);
+    A.row_ptr = (const long long*)ctx->row_ptr.p;
+    A.dst = (int*)ctx->dst.p;
+    A.image = (uint32_t*)ctx->image.p;
+    A.dist = (double*)ctx->dist.p;
+    A.row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
+    A.n_buckets = A.row_cap <= 256 ? 128 : (A.row_cap <= 1024 ? 256 : 512);
+    A.n_warps = 8;
+    while (A.n_warps > 1 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) A.n_warps >>= 1;
+    while (A.tile_cap > 0 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) {
+        A.tile_cap = A.tile_cap > 512 ? A.tile_cap / 2 : 0;  // shrink the tile: more items go unstaged
+        if (A.tile_cap == 0) A.tcs_cap = 4;
+    }
+    if ((int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin)
+        return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
+    CU(dg_launch_traverse(st, A, true, grid));
+    CU(cudaEventRecord(ctx->ev.e[4], st));
+
+    // ---- K3: fused Gaussian RBF expansion ----------------------------------------------------------------------
+    if (want_rbf && E > 0) {
+        ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
+        dg_launch_rbf_f32(st, (const double*)ctx->dist.p, E, K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p,
+                          ctx->sm_count);
+    }
+    CU(cudaEventRecord(ctx->ev.e[5], st));
+    CU(cudaGetLastError());
+    {
+        int r = fetch_stats(ctx);  // sync 4: completion + tie statistics
+        if (r != DGNN_OK) return r;
+    }
+    if (ctx->h_stats->overflow) return fail(ctx, DGNN_ERR_DEGREE, "internal: row buffer overflow");
+
+    out->n_structs = S;
+    out->n_atoms = N;
+    out->n_edges = E;
+    out->K = want_rbf ? K : 0;
+    out->max_degree = max_deg;
+    out->row_ptr = (const int64_t*)ctx->row_ptr.p;
+    out->dst = (const int32_t*)ctx->dst.p;
+    out->image = (const int32_t*)ctx->image.p;
+    out->dist = (const double*)ctx->dist.p;
+    out->rbf = (want_rbf && E > 0) ? (const float*)ctx->rbf.p : nullptr;
+    out->struct_edge_offsets = (const int64_t*)ctx->seo.p;
+    out->n_near_cutoff = (int64_t)ctx->h_stats->n_near;
+    out->n_tie_rows = ctx->h_stats->n_tie_rows;
+
+    dgnn_build_info& I = ctx->info;
+    cudaEventElapsedTime(&I.h2d_ms, ctx->ev.e[0], ctx->ev.e[1]);
+    cudaEventElapsedTime(&I.bin_ms, ctx->ev.e[1], ctx->ev.e[2]);
+    cudaEventElapsedTime(&I.count_ms, ctx->ev.e[2], ctx->ev.e[3]);
+    cudaEventElapsedTime(&I.fill_ms, ctx->ev.e[3], ctx->ev.e[4]);
+    cudaEventElapsedTime(&I.rbf_ms, ctx->ev.e[4], ctx->ev.e[5]);
+    cudaEventElapsedTime(&I.total_ms, ctx->ev.e[0], ctx->ev.e[5]);
+    I.kernel_launches = dg_num_kernel_launches_reset() + dg_rbf_launch_count_reset();
+    I.n_items = (int32_t)n_items;
+    I.cloud_points = P;
+    I.staged_tile_cap = A.tile_cap;
+    I.row_cap = A.row_cap;
+    return DGNN_OK;
+}
+
+int dgnn_copy_edges_to_host(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t e0, int64_t e1, int32_t* dst,
+                            int32_t* image, double* dist, float* rbf) {
+    if (!ctx || !g) return DGNN_ERR_INVALID_ARG;
+    if (e0 < 0 || e1 < e0 || e1 > g->n_edges) return fail(ctx, DGNN_ERR_INVALID_ARG, "edge range out of bounds");
+    CU(cudaSetDevice(ctx->device));
+    const size_t n = (size_t)(e1 - e0);
+    if (n == 0) return DGNN_OK;
+    cudaStream_t st = ctx->stream;
+    if (dst) CU(cudaMemcpyAsync(dst, g->dst + e0, n * 4, cudaMemcpyDeviceToHost, st));
+    if (image) CU(cudaMemcpyAsync(image, g->image + e0, n * 4, cudaMemcpyDeviceToHost, st));
+    if (dist) CU(cudaMemcpyAsync(dist, g->dist + e0, n * 8, cudaMemcpyDeviceToHost, st));
+    if (rbf) {
+        if (!g->rbf) return fail(ctx, DGNN_ERR_INVALID_ARG, "no RBF features in this build");
+        CU(cudaMemcpyAsync(rbf, g->rbf + (size_t)e0 * g->K, n * (size_t)g->K * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaStreamSynchronize(st));
+    return DGNN_OK;
+}
+
+int dgnn_copy_to_host(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t* row_ptr, int32_t* dst, int32_t* image,
+                      double* dist, float* rbf, int64_t* struct_edge_offsets) {
+    if (!ctx || !g) return DGNN_ERR_INVALID_ARG;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (row_ptr) CU(cudaMemcpyAsync(row_ptr, g->row_ptr, (size_t)(g->n_atoms + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (struct_edge_offsets)
+        CU(cudaMemcpyAsync(struct_edge_offsets, g->struct_edge_offsets, (size_t)(g->n_structs + 1) * 8,
+                           cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return dgnn_copy_edges_to_host(ctx, g, 0, g->n_edges, dst, image, dist, rbf);
+}
+
+static int rbf_common(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, void* out,
+                      int32_t* K_out, bool f64) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    if (n < 0 || (n > 0 && (!dist || !out))) return fail(ctx, DGNN_ERR_INVALID_ARG, "null pointer / negative n");
+    if (!(r_cutoff > 0.0) || !(dr > 0.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "r_cutoff and dr must be positive");
+    const double kf = std::floor(r_cutoff / dr);
+    if (!(kf >= 1.0 && kf <= 65536.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "RBF bin count out of range");
+    const int K = (int)kf;
+    if (K_out) *K_out = K;
+    if (n == 0) return DGNN_OK;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    const double* d_in = dist;
+    void* d_out = out;
+    const size_t out_bytes = (size_t)n * K * (f64 ? 8 : 4);
+    const bool in_dev = is_device_ptr(dist), out_dev = is_device_ptr(out);
+    if (!in_dev) {
+        ENSURE(ctx->tmp_in, (size_t)n * 8);
+        CU(cudaMemcpyAsync(ctx->tmp_in.p, dist, (size_t)n * 8, cudaMemcpyHostToDevice, st));
+        d_in = (const double*)ctx->tmp_in.p;
+    }
+    if (!out_dev) {
+        ENSURE(ctx->tmp_out, out_bytes + 16);
+        d_out = ctx->tmp_out.p;
+    }
+    if (f64)
+        dg_launch_rbf_f64_colmajor(st, d_in, n, K, r_cutoff, dr, (double*)d_out);
+    else
+        dg_launch_rbf_f32(st, d_in, n, K, r_cutoff, dr, (float*)d_out, ctx->sm_count);
+    CU(cudaGetLastError());
+    if (!out_dev) CU(cudaMemcpyAsync(out, d_out, out_bytes, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return DGNN_OK;
+}
+
+int dgnn_rbf_expand(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, float* out,
+                    int32_t* K_out) {
+    return rbf_common(ctx, dist, n, r_cutoff, dr, out, K_out, false);
+}
+
+int dgnn_rbf_expand_f64(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, double* out,
+                        int32_t* K_out) {
+    return rbf_common(ctx, dist, n, r_cutoff, dr, out, K_out, true);
+}
+
+}  // extern "C"

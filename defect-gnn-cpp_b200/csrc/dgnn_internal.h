@@ -1,0 +1,91 @@
+// dgnn_internal.h -- shared declarations between the kernel translation units and the C-ABI host layer.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "geom.h"
+
+// Device-resident statistics block, copied to the host at the (few) sync points of a build.
+struct DgStats {
+    unsigned long long n_near;   // candidate pairs with |d - r_c| <= 1e-6
+    long long n_cells;           // total halo cells of the batch
+    long long n_items;           // total work items
+    long long cloud_points;      // pruned image cloud size
+    long long n_edges;
+    int max_tile_pts;            // largest staged-tile point count over items
+    int max_tile_tcs;            // largest tile cell-start table (rows * (tdc + 1))
+    int max_deg;                 // largest uncapped row
+    int n_tie_rows;
+    int err_status;              // first non-zero DgGeom::status seen
+    int err_struct;              // and the structure it was seen on
+    int overflow;                // a row did not fit the row buffer (must not happen)
+    int pad;
+};
+
+struct DgTraverseArgs {
+    // inputs
+    const DgGeom* geoms;
+    const long long* item_base;  // [S+1]
+    long long n_items;
+    long long n_structs;
+    const long long* cellstart;  // [n_cells+1] offsets into the cloud
+    const double* cx;            // cloud: image positions (reference arithmetic), cell-sorted
+    const double* cy;
+    const double* cz;
+    const int* cj;               // cloud: local atom index
+    const uint32_t* cn;          // cloud: packed image
+    double r2;                   // r_c * r_c (fp64, computed once like neighbor_list.cpp:40)
+    double r_cutoff;
+    double rcm;                  // r_c * (1 + margin) for candidate generation
+    double epsilon;
+    float inv_rc;
+    int near_lo_hi, near_hi_hi;  // high words of (r_c -+ 2e-6)^2
+    int max_neighbors;           // clamped to INT_MAX
+    // capacities (shared memory carve-up)
+    int tile_cap, tcs_cap, src_cap, row_cap, n_buckets, n_warps;
+    // outputs
+    int* deg_capped;             // [N] (count pass)
+    const long long* row_ptr;    // [N+1] (fill pass)
+    int* dst;
+    uint32_t* image;
+    double* dist;
+    DgStats* stats;
+};
+
+#define DG_ROWS_CAP 1024  // tile rows (td_a * td_b) <= 32 * 32
+#define DG_STN_CAP 961    // stencil rows (2R_a+1)(2R_b+1) <= 31 * 31
+
+// ---- launch wrappers (dgnn_kernels.cu) ----
+void dg_launch_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
+                    double r_cutoff, double cell_frac, DgGeom* geoms);
+void dg_launch_atom_cells(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
+                          const double* x, const double* y, const double* z, DgGeom* geoms, int* astruct,
+                          int* acell);
+void dg_launch_plan(cudaStream_t st, long long S, DgGeom* geoms, int tile_target, int src_target, int* ncells32,
+                    int* nitems32, DgStats* stats);
+void dg_launch_plan_finish(cudaStream_t st, long long S, DgGeom* geoms, const long long* cell_base,
+                           const long long* item_base, DgStats* stats);
+void dg_launch_cloud_count(cudaStream_t st, long long N, const DgGeom* geoms, const int* astruct,
+                           const int* acell, int* cellcount);
+void dg_launch_item_stats(cudaStream_t st, long long n_items, long long S, const DgGeom* geoms,
+                          const long long* item_base, const long long* cellstart, long long n_cells,
+                          DgStats* stats);
+void dg_launch_cloud_scatter(cudaStream_t st, long long N, const DgGeom* geoms, const int* astruct,
+                             const int* acell, const double* x, const double* y, const double* z,
+                             const long long* cellstart, int* cellcount, double* cx, double* cy, double* cz,
+                             int* cj, uint32_t* cn);
+size_t dg_traverse_smem_bytes(const DgTraverseArgs& a, bool fill);
+cudaError_t dg_launch_traverse(cudaStream_t st, const DgTraverseArgs& a, bool fill, int grid);
+void dg_launch_finish_rows(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
+                           const long long* row_ptr, long long* struct_edge_offsets, DgStats* stats);
+// exclusive scan int32 -> int64, out has n+1 entries (out[n] = total); scratch >= n/2048 + 2 entries
+void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch);
+int dg_num_kernel_launches_reset();  // returns launches since last reset
+
+// ---- dgnn_rbf.cu ----
+void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff, double dr,
+                       float* out, int sm_count);
+void dg_launch_rbf_f64_colmajor(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff,
+                                double dr, double* out);
+int dg_rbf_launch_count_reset();

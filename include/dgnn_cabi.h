@@ -1,0 +1,145 @@
+/*
+ * dgnn_cabi.h -- C ABI of the B200-native crystal-graph builder (libdgnn_b200.so).
+ *
+ * This is the drop-in boundary for the reference's graph layer.  The reference has no FFI for this path; its
+ * boundary is the C++ class API in include/graph/ (SURVEY.md section 8b).  Each entry point below names the
+ * reference interface it replaces (paths relative to the reference repository):
+ *
+ *   dgnn_build            NeighborList::NeighborList / build_with_pbc      src/graph/neighbor_list.cpp:14-66
+ *                         + compute_num_images / create_image_cloud        src/graph/neighbor_list.cpp:68-94
+ *                         + CrystalGraph ctor, edge part                   src/graph/crystal_graph.cpp:23-40
+ *                         (batched over many structures: new surface, the reference is one structure per call)
+ *   dgnn_rbf_expand       graph::gaussian_rbf                              src/graph/edge_features.cpp:7-24
+ *   dgnn_rbf_expand_f64   CrystalGraph::edge_attr() storage (col-major)    src/graph/crystal_graph.cpp:30,37
+ *   dgnn_copy_to_host     NeighborList::neighbors(i) / edge_index()        src/graph/neighbor_list.cpp:23-25,
+ *                                                                          src/graph/crystal_graph.cpp:49-55
+ *
+ * The C++ facade that keeps the reference's class API (defect_gnn::graph::NeighborList, gaussian_rbf,
+ * CrystalGraph) on top of this ABI lives in defect-gnn-cpp_b200/host/.  No torch / C++ types cross this
+ * boundary: plain pointers, sizes and int status codes; errors never propagate as exceptions.
+ *
+ * Threading: a dgnn_ctx belongs to one CUDA device and one host thread at a time.  Results returned by
+ * dgnn_build are device buffers owned by the ctx and stay valid until the next dgnn_build / dgnn_destroy on it.
+ * There is no CPU fallback: every call fails with DGNN_ERR_CUDA if no sm_100 device is usable.
+ */
+#ifndef DGNN_CABI_H
+#define DGNN_CABI_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGNN_ABI_VERSION 1
+
+/* status codes (0 = ok, < 0 = error) */
+enum {
+    DGNN_OK = 0,
+    DGNN_ERR_INVALID_ARG = -1,   /* null pointer, negative size, r_cutoff <= 0, non-monotone offsets ... */
+    DGNN_ERR_CUDA = -2,          /* CUDA runtime error (message in dgnn_last_error) */
+    DGNN_ERR_OOM = -3,           /* device allocation failed */
+    DGNN_ERR_SINGULAR = -4,      /* a lattice matrix is singular / non-finite */
+    DGNN_ERR_IMAGE_RANGE = -5,   /* reference image range n = ceil(r_c / l_min) + 1 exceeds 127 */
+    DGNN_ERR_GEOMETRY = -6,      /* cell so thin that the stencil reach exceeds the supported 15 cells */
+    DGNN_ERR_UNWRAPPED = -7,     /* atoms lie absurdly far outside the unit cell (halo grid too large) */
+    DGNN_ERR_DEGREE = -8,        /* a row has more neighbours than the sorter supports (see DGNN_MAX_DEGREE) */
+    DGNN_ERR_TOO_LARGE = -9,     /* batch exceeds 2^31-1 atoms / image-cloud points / cells: split it */
+    DGNN_ERR_UNSUPPORTED = -10
+};
+
+#define DGNN_MAX_DEGREE 8192
+#define DGNN_UNCAPPED UINT64_MAX /* max_neighbors = SIZE_MAX: topology caller, betti_features.cpp:107 */
+
+/* dgnn_batch.flags */
+#define DGNN_INPUT_DEVICE 0x1u /* atom_offsets/x/y/z/lattice are device pointers on the ctx's device */
+#define DGNN_SKIP_RBF 0x2u     /* build the neighbour list only (the viewer path never asks for features) */
+
+typedef struct dgnn_ctx dgnn_ctx; /* opaque, one per CUDA device */
+
+/* arena_bytes: initial size hint for the edge arena (0 = grow on demand). */
+int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out);
+void dgnn_destroy(dgnn_ctx* ctx);
+const char* dgnn_last_error(const dgnn_ctx* ctx);
+const char* dgnn_strerror(int code);
+int dgnn_abi_version(void);
+
+/* A batch of structures in SoA form (the repack of crystal::Structure, include/crystal/structure.hpp:12-38). */
+typedef struct {
+    int64_t n_structs;
+    const int64_t* atom_offsets; /* [n_structs+1], atom_offsets[0] = 0 */
+    const double* x;             /* [n_atoms] Cartesian Angstrom = Structure::atoms()[i].position, SoA */
+    const double* y;
+    const double* z;
+    const double* lattice;       /* [n_structs*9] row-major, rows = a, b, c (vasp_parser.cpp:32-38) */
+    double r_cutoff;             /* NeighborList r_cutoff   (neighbor_list.hpp:20, default 10.0) */
+    uint64_t max_neighbors;      /* NeighborList max_neighbors (default 20; DGNN_UNCAPPED = no cap) */
+    double epsilon;              /* NeighborList epsilon    (default 1e-10) */
+    double rbf_r_cutoff;         /* CrystalGraph r_cutoff   (crystal_graph.hpp:18, default 10) */
+    double dr;                   /* CrystalGraph dr (default 0.1); K = floor(rbf_r_cutoff / dr); dr <= 0: no RBF */
+    uint32_t flags;
+} dgnn_batch;
+
+/* Result: device pointers owned by ctx.  CSR by source atom (global atom index across the batch); rows are
+ * sorted by the canonical key (distance, dst, n_a, n_b, n_c) and truncated to max_neighbors
+ * (neighbor_list.cpp:56-62; the reference's tie order is unspecified).
+ * Edge order == CrystalGraph edge order (crystal_graph.cpp:32-40): source ascending, then row order. */
+typedef struct {
+    int64_t n_structs;
+    int64_t n_atoms;
+    int64_t n_edges;
+    int32_t K;                     /* RBF bins (0 if skipped) */
+    int32_t max_degree;            /* largest uncapped row in the batch */
+    const int64_t* row_ptr;        /* [n_atoms+1] */
+    const int32_t* dst;            /* [E] Neighbor::idx, local to its structure (edge_index(1,e)) */
+    const int32_t* image;          /* [E] periodic image of the neighbour: int8 n_a | n_b<<8 | n_c<<16 */
+    const double* dist;            /* [E] Neighbor::distance (fp64, bit-exact with the reference arithmetic) */
+    const float* rbf;              /* [E*K] row-major fp32 edge_attr (consumer layout, utilities.py:69-71) */
+    const int64_t* struct_edge_offsets; /* [n_structs+1] first edge of every structure */
+    int64_t n_near_cutoff;         /* candidate pairs with |d - r_c| <= 1e-6 A (either side), parity report */
+    int64_t n_tie_rows;            /* rows truncated through a distance tie (capped mode; R8) */
+} dgnn_graphs;
+
+int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* batch, dgnn_graphs* out);
+
+/* Copy results of the last build to host buffers (any pointer may be NULL to skip it).  Sizes as in dgnn_graphs. */
+int dgnn_copy_to_host(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t* row_ptr, int32_t* dst, int32_t* image,
+                      double* dist, float* rbf, int64_t* struct_edge_offsets);
+
+/* Copy the edges [e0, e1) of the last build (for chunked / per-structure host materialisation). */
+int dgnn_copy_edges_to_host(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t e0, int64_t e1, int32_t* dst,
+                            int32_t* image, double* dist, float* rbf);
+
+/* Stand-alone fused Gaussian RBF expansion (edge_features.cpp:7-24) of n distances.
+ * dist / out may be host or device pointers independently (device pointers must live on the ctx's device).
+ * out: n * K floats row-major; returns K through *K_out. */
+int dgnn_rbf_expand(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, float* out,
+                    int32_t* K_out);
+/* fp64 variant writing the reference's own storage: column-major E x K doubles (crystal_graph.cpp:30,37). */
+int dgnn_rbf_expand_f64(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, double* out,
+                        int32_t* K_out);
+
+/* Device timings of the phases of the last dgnn_build (CUDA events on the ctx stream), milliseconds:
+ * bin = geometry + cell-list binning (K1), dist = count + scan + fill/sort (K2), rbf = K3, h2d = input upload,
+ * total = first to last event. */
+typedef struct {
+    float h2d_ms, bin_ms, count_ms, fill_ms, rbf_ms, total_ms;
+    int32_t kernel_launches; /* kernels launched by the last build */
+    int32_t n_items;         /* work items (structure x source-cell block) */
+    int64_t cloud_points;    /* pruned periodic image cloud size */
+    int32_t staged_tile_cap; /* shared-memory tile capacity used (points) */
+    int32_t row_cap;         /* shared-memory row buffer capacity used */
+} dgnn_build_info;
+int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
+
+/* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
+void* dgnn_stream(dgnn_ctx* ctx);
+
+/* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5). */
+int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DGNN_CABI_H */

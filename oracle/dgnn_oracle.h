@@ -1,0 +1,94 @@
+/*
+ * dgnn_oracle.h -- CPU ORACLE for the crystal-graph construction path.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This is a plain C++17 restatement (no Eigen, no nanoflann: neither exists on this
+ * image) of the reference algorithm in
+ *     /root/reference/src/graph/neighbor_list.cpp:27-94     (periodic radius-neighbour search)
+ *     /root/reference/src/graph/edge_features.cpp:7-24      (Gaussian RBF)
+ *     /root/reference/src/graph/crystal_graph.cpp:23-40     (edge_index / edge_attr assembly)
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may load it.  The
+ * product library (libdgnn_b200.so) never links, loads or calls anything in oracle/.
+ *
+ * PARITY STATUS: "parity unpinned".  The reference ships no tests, golden vectors or known-answer fixtures for
+ * this path and cannot be compiled here (Eigen 3.4.0 / nanoflann v1.5.5 are un-vendored
+ * downloads, Makefile:157-186).  The oracle is therefore pinned against (i) analytic known answers (simple-cubic
+ * shell multiplicities, closed-form Gaussians) and (ii) three independent algorithms inside this file that must
+ * agree with each other: exhaustive scan of the reference image cloud, a KD-tree restating nanoflann's
+ * build/search, and a cell list.
+ */
+#ifndef DGNN_ORACLE_H
+#define DGNN_ORACLE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum { ORC_ALGO_BRUTE = 0, ORC_ALGO_KDTREE = 1, ORC_ALGO_CELLLIST = 2 };
+
+/* CSR-by-source neighbour list of one structure; rows sorted by the canonical key
+ * (distance, dst, n_a, n_b, n_c) and truncated to max_neighbors (neighbor_list.cpp:56-62). */
+typedef struct {
+    int64_t n_atoms;
+    int64_t n_edges;
+    int64_t* row_ptr; /* [n_atoms+1] */
+    int32_t* dst;     /* [E]   Neighbor::idx */
+    int8_t* image;    /* [E*4] (n_a,n_b,n_c,0) of the periodic image the neighbour sits in */
+    double* dist;     /* [E]   Neighbor::distance = sqrt(d2) */
+    double* disp;     /* [E*3] Neighbor::displacement = image_pos - query_pos (neighbor_list.cpp:51) */
+    int64_t n_near_cutoff; /* candidate pairs with |d - r_c| <= 1e-6 (inside or outside), reported separately */
+    int64_t n_tie_rows;    /* rows whose k-th and (k+1)-th neighbour have equal distance (capped mode only) */
+    int32_t num_images;    /* compute_num_images (neighbor_list.cpp:68-72) */
+} orc_graph;
+
+/* neighbor_list.cpp:68-72 */
+int orc_num_images(const double lattice[9], double r_cutoff);
+
+/* One structure.  x,y,z: Cartesian positions exactly as Structure::atoms()[i].position; lattice rows = a,b,c. */
+int orc_neighbor_list(int64_t n_atoms, const double* x, const double* y, const double* z, const double lattice[9],
+                      double r_cutoff, uint64_t max_neighbors, double epsilon, int algo, orc_graph* out);
+void orc_free_graph(orc_graph* g);
+
+/* edge_features.cpp:7-24.  Returns K = floor(r_cutoff/dr); writes K doubles if out != NULL. */
+int orc_gaussian_rbf(double distance, double r_cutoff, double dr, double* out);
+
+/* crystal_graph.cpp:28-40 edge part: edge_attr as the reference stores it (column-major fp64, E x K). */
+int orc_edge_attr_colmajor(int64_t n_edges, const double* dist, double r_cutoff, double dr, double* out);
+/* same values, row-major (consumer layout, utilities.py:69-71) */
+int orc_edge_attr_rowmajor(int64_t n_edges, const double* dist, double r_cutoff, double dr, double* out);
+
+/* structure.cpp:17  position = lattice^T * frac, evaluated as L0k*f0 + (L1k*f1 + L2k*f2). */
+void orc_frac_to_cart(int64_t n, const double* frac /*n*3*/, const double lattice[9], double* x, double* y,
+                      double* z);
+
+/* Whole-batch CPU baseline: for every structure do NeighborList (algo) + CrystalGraph edge part (RBF fp64) the
+ * way the reference would, with `threads` std::threads (<=0: all cores) over structures.  Nothing is retained; returns totals. */
+typedef struct {
+    int64_t n_edges;
+    double checksum;  /* sum of all distances + sum of all features, to keep the optimiser honest */
+    double seconds;   /* wall-clock of the parallel region */
+    int32_t threads;  /* threads actually used */
+} orc_batch_result;
+
+int orc_build_batch(int64_t n_structs, const int64_t* atom_offsets, const double* x, const double* y,
+                    const double* z, const double* lattices, double r_cutoff, uint64_t max_neighbors,
+                    double epsilon, double rbf_r_cutoff, double dr, int algo, int threads,
+                    orc_batch_result* out);
+
+/* Per-structure edge counts for a batch (used by the sharding / offsets tests). */
+int orc_batch_edge_counts(int64_t n_structs, const int64_t* atom_offsets, const double* x, const double* y,
+                          const double* z, const double* lattices, double r_cutoff, uint64_t max_neighbors,
+                          double epsilon, int algo, int threads, int64_t* counts);
+
+/* Brute-force neighbours of selected source atoms only (for spot checks on the 1M-atom config).  For source
+ * sources[q] writes its degree to deg[q]; if dst/image/dist non-NULL they receive rows of `row_cap` slots. */
+int orc_rows_brute(int64_t n_atoms, const double* x, const double* y, const double* z, const double lattice[9],
+                   double r_cutoff, double epsilon, int64_t n_sources, const int64_t* sources, int64_t row_cap,
+                   int64_t* deg, int32_t* dst, int8_t* image, double* dist);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,224 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C ABI (libdgnn_b200.so).
+
+Bar (BASELINE.json north_star): edge sets (src, dst, image) and distances BIT-EXACT vs the oracle after the canonical
+row sort; near-cutoff pairs reported separately and equal; RBF features within 1e-5 relative (fp32 vs fp64 oracle).
+"""
+import hashlib
+import json
+import os
+
+import numpy as np
+import pytest
+
+from conftest import assert_graph_equal
+
+pytestmark = pytest.mark.gpu
+
+RBF_RTOL = 1e-5  # north_star tolerance for the fp32 features
+
+
+def build_and_fetch(gb, b, rc, cap, rbf_rc=None, dr=None, eps=1e-10, device_inputs=False):
+    g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=rc, max_neighbors=cap, epsilon=eps,
+                 rbf_r_cutoff=rbf_rc if rbf_rc else rc, dr=dr, skip_rbf=dr is None, device_inputs=device_inputs)
+    return gb.to_host(g)
+
+
+def check_batch(gb, oracle, b, rc, cap, dr=None, eps=1e-10, algo=None, rbf_rc=None):
+    cap_o = oracle.UNCAPPED if cap is None else cap
+    h = build_and_fetch(gb, b, rc, cap_o, rbf_rc, dr, eps)
+    e0 = 0
+    near = ties = 0
+    maxdeg = 0
+    for s in range(b.n_structs):
+        x, y, z, L = b.structure(s)
+        o = oracle.neighbor_list(x, y, z, L, rc, cap_o, eps, oracle.ALGO_CELLLIST if algo is None else algo)
+        a0, a1 = int(b.atom_offsets[s]), int(b.atom_offsets[s + 1])
+        assert h.struct_edge_offsets[s] == e0
+        e1 = assert_graph_equal(h, e0, a0, a1, o, what=f"structure {s}")
+        if dr is not None and o.n_edges:
+            ref = oracle.edge_attr(o.dist, rbf_rc if rbf_rc else rc, dr)
+            rel = np.max(np.abs(h.rbf[e0:e1].astype(np.float64) - ref) / ref)
+            assert rel <= RBF_RTOL, f"structure {s}: RBF rel err {rel:.3e}"
+        near += o.n_near_cutoff
+        ties += o.n_tie_rows
+        e0 = e1
+    assert e0 == h.n_edges == h.struct_edge_offsets[-1]
+    assert h.n_near_cutoff == near
+    assert h.n_tie_rows == ties
+    return h
+
+
+def test_c2_perovskite_batch_uncapped_with_rbf(gpu_builder, oracle, syn):
+    b = syn.c2_batch(24)
+    h = check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2)
+    assert h.K == 40 and h.n_edges > 24 * 25_000
+    info = gpu_builder.info()
+    assert info.kernel_launches >= 10 and info.staged_tile_cap > 0
+
+
+def test_c2_capped_and_viewer_params(gpu_builder, oracle, syn):
+    b = syn.c2_batch(8, seed0=5000)
+    h = check_batch(gpu_builder, oracle, b, 10.0, 20, dr=0.1)       # reference defaults, K = 100
+    assert h.K == 100 and h.n_edges == 20 * b.n_atoms
+    check_batch(gpu_builder, oracle, b, 5.0, 12)                     # viewer: buildGraph(5.0, 12), no RBF
+
+
+def test_c1_shipped_poscars_all_param_sets(gpu_builder, oracle, syn, c1_structures, golden_dir):
+    exp = json.load(open(os.path.join(golden_dir, "c1_expected.json")))
+    names = sorted(c1_structures)
+    b = syn.concat([c1_structures[n][:4] for n in names])
+    for pname, rc, cap, dr in (("reference_default", 10.0, 20, 0.1), ("viewer_default", 5.0, 12, None),
+                               ("benchmark_uncapped", 8.0, None, 0.2), ("topology_uncapped", 10.0, None, 0.1)):
+        h = check_batch(gpu_builder, oracle, b, rc, cap, dr=dr)
+        # and against the committed golden digests (independent of the oracle binary on this box)
+        for s, nm in enumerate(names):
+            a0, a1 = int(b.atom_offsets[s]), int(b.atom_offsets[s + 1])
+            e0, e1 = int(h.struct_edge_offsets[s]), int(h.struct_edge_offsets[s + 1])
+            assert e1 - e0 == exp[nm][pname]["n_edges"]
+            hh = hashlib.sha256()
+            hh.update((h.row_ptr[a0:a1 + 1] - h.row_ptr[a0]).astype(np.int64).tobytes())
+            hh.update(h.dst[e0:e1].tobytes())
+            hh.update(np.ascontiguousarray(h.image[e0:e1]).tobytes())
+            hh.update(h.dist[e0:e1].tobytes())
+            assert hh.hexdigest() == exp[nm][pname]["edge_sha256"], (nm, pname)
+
+
+def test_c3_triclinic_short_vectors(gpu_builder, oracle, syn):
+    b = syn.c3_batch(300)
+    h = check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2)
+    # multi-image and self-image edges are present (same (src,dst) through several images; dst == src)
+    src = np.repeat(np.arange(b.n_atoms), np.diff(h.row_ptr))
+    local_src = src - np.repeat(b.atom_offsets[:-1], np.diff(h.struct_edge_offsets))
+    assert np.any(local_src == h.dst)
+
+
+def test_adversarial_cells_reference_image_range(gpu_builder, oracle, syn):
+    b = syn.adversarial_cells()
+    check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+    check_batch(gpu_builder, oracle, b, 3.0, 5, algo=oracle.ALGO_BRUTE)
+
+
+def test_known_answers_and_edge_cases(gpu_builder, oracle, syn, pkg):
+    gb = gpu_builder
+    sc = syn.simple_cubic(1.0, 1)
+    h = check_batch(gb, oracle, sc, 3.05, None, algo=oracle.ALGO_BRUTE)
+    d2 = np.round(h.dist ** 2).astype(int)
+    assert {k: int((d2 == k).sum()) for k in (1, 2, 3, 4, 5, 6, 8, 9)} == {1: 6, 2: 12, 3: 8, 4: 6, 5: 24, 6: 24, 8: 12, 9: 30}
+    # neighbours at exactly r_c: strict '<' decided by rounding, identical to the oracle
+    sc3 = syn.simple_cubic(2.0, 3)
+    check_batch(gb, oracle, sc3, 4.0, None, algo=oracle.ALGO_BRUTE)
+    check_batch(gb, oracle, sc3, 2.0, None, algo=oracle.ALGO_BRUTE)
+    # epsilon semantics (R6)
+    check_batch(gb, oracle, sc3, 2.5, None, eps=0.0, algo=oracle.ALGO_BRUTE)
+    check_batch(gb, oracle, sc3, 6.5, None, eps=6.1, algo=oracle.ALGO_BRUTE)
+    # empty batch, empty structures, ragged sizes
+    empty = syn.concat([])
+    g = gb.build(empty.atom_offsets, empty.x, empty.y, empty.z, empty.lattices, 8.0, 20, dr=0.2, rbf_r_cutoff=8.0)
+    assert g.n_edges == 0 and g.n_structs == 0
+    one = syn.perovskite_supercell(2, 2, 2, seed=3)[:4]
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    tiny = syn.triclinic_cell(7)[:4]
+    ragged = syn.concat([none, one, none, tiny, syn.perovskite_supercell(4, 4, 4, seed=4)[:4], none])
+    h = check_batch(gb, oracle, ragged, 8.0, None, dr=0.2)
+    assert h.struct_edge_offsets[0] == h.struct_edge_offsets[1] == 0
+    # max_neighbors = 0 and 1
+    check_batch(gb, oracle, ragged, 8.0, 1)
+    h0 = build_and_fetch(gb, ragged, 8.0, 0)
+    assert h0.n_edges == 0
+
+
+def test_error_codes(gpu_builder, syn, pkg):
+    gb = gpu_builder
+    x, y, z, L = syn.perovskite_supercell(2, 2, 2, seed=3)[:4]
+    b = syn.concat([(x, y, z, L)])
+    with pytest.raises(pkg.DgnnError) as ei:
+        gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=-1.0)
+    assert ei.value.code == -1
+    bad = syn.concat([(x, y, z, np.array([[1.0, 0, 0], [2.0, 0, 0], [0, 0, 1.0]]))])
+    with pytest.raises(pkg.DgnnError) as ei:
+        gb.build(bad.atom_offsets, bad.x, bad.y, bad.z, bad.lattices, r_cutoff=8.0)
+    assert ei.value.code == -4  # singular lattice
+    thin = syn.concat([(x, y, z, np.diag([0.05, 8.0, 8.0]))])
+    with pytest.raises(pkg.DgnnError) as ei:
+        gb.build(thin.atom_offsets, thin.x, thin.y, thin.z, thin.lattices, r_cutoff=8.0)
+    assert ei.value.code in (-5, -6)
+    # the context stays usable after an error
+    g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=5.0, max_neighbors=12, skip_rbf=True)
+    assert g.n_edges == 12 * len(x)
+
+
+def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
+    """Medium supercell: (i) default plan (several work items), (ii) tiny tiles, (iii) forced unstaged traversal --
+    all three must give the same bit-exact result."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    x, y, z, L, _ = syn.perovskite_supercell(9, 8, 7, seed=11)
+    b = syn.concat([(x, y, z, L)])
+    o = oracle.neighbor_list(x, y, z, L, 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
+    for opts in ({}, {"tile_target": 512, "src_target": 48}, {"tile_limit": 0}, {"cell_frac": 0.3}, {"cell_frac": 1.0}):
+        gb = pkg.GraphBuilder(0)
+        for k, v in opts.items():
+            gb.set_option(k, v)
+        g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, 8.0, oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
+        h = gb.to_host(g)
+        assert_graph_equal(h, 0, 0, len(x), o, what=str(opts))
+        info = gb.info()
+        if opts.get("tile_limit") == 0:
+            assert info.staged_tile_cap == 0
+        if "tile_target" in opts:
+            assert info.n_items > 20
+        gb.close()
+
+
+def test_device_resident_inputs_and_rbf_standalone(gpu_builder, oracle, syn):
+    import torch
+    gb = gpu_builder
+    b = syn.c2_batch(5, seed0=777)
+    dev = torch.device("cuda:0")
+    t = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+    torch.cuda.synchronize()
+    g = gb.build(*t, r_cutoff=8.0, max_neighbors=oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2, device_inputs=True)
+    h_dev = gb.to_host(g)
+    h_host = build_and_fetch(gb, b, 8.0, oracle.UNCAPPED, 8.0, 0.2)
+    for f in ("row_ptr", "dst", "image", "dist", "rbf"):
+        assert np.array_equal(getattr(h_dev, f), getattr(h_host, f)), f
+    # stand-alone gaussian_rbf replacement, host and device pointers, fp32 row-major and fp64 column-major
+    d = np.concatenate([[0.0, 4.0, 8.0 - 1e-9], np.random.default_rng(0).uniform(0.0, 8.0, 5000)])
+    for rc, dr in ((8.0, 0.2), (10.0, 0.1), (8.0, 0.3)):   # K = 40, 100, 26 (scalar-store path)
+        ref = oracle.edge_attr(d, rc, dr)
+        out = gb.rbf_expand(d, rc, dr)
+        assert out.shape == ref.shape
+        assert np.max(np.abs(out - ref) / ref) <= RBF_RTOL
+        out64 = gb.rbf_expand(d, rc, dr, f64_colmajor=True)
+        assert np.max(np.abs(out64 - ref) / ref) <= 1e-12
+    dd = torch.from_numpy(d).to(dev)
+    od = torch.empty((d.shape[0], 40), dtype=torch.float32, device=dev)
+    gb.rbf_expand(dd, 8.0, 0.2, out=od)
+    assert np.max(np.abs(od.cpu().numpy() - oracle.edge_attr(d, 8.0, 0.2)) / oracle.edge_attr(d, 8.0, 0.2)) <= RBF_RTOL
+
+
+def test_determinism_and_symmetry_property(gpu_builder, oracle, syn):
+    """Size-independent properties on a larger batch: two builds are byte-identical; every edge (i -> j, n) has its
+    mirror (j -> i, -n) with the bit-identical distance; rows are sorted."""
+    b = syn.c2_batch(200, seed0=9000)
+    h1 = build_and_fetch(gpu_builder, b, 8.0, oracle.UNCAPPED, 8.0, 0.2)
+    h2 = build_and_fetch(gpu_builder, b, 8.0, oracle.UNCAPPED, 8.0, 0.2)
+    for f in ("row_ptr", "dst", "image", "dist", "rbf"):
+        assert np.array_equal(getattr(h1, f), getattr(h2, f)), f
+    counts = oracle.batch_edge_counts(b.atom_offsets, b.x, b.y, b.z, b.lattices, 8.0)
+    assert np.array_equal(np.diff(h1.struct_edge_offsets), counts)
+    src = np.repeat(np.arange(b.n_atoms, dtype=np.int64), np.diff(h1.row_ptr))
+    sid = np.repeat(np.arange(b.n_structs), np.diff(h1.struct_edge_offsets))
+    dstg = h1.dst.astype(np.int64) + b.atom_offsets[sid]
+    n = h1.image[:, :3].astype(np.int64)
+    key_f = ((src * b.n_atoms + dstg) * 8 + (n[:, 0] + 3)) * 64 + (n[:, 1] + 3) * 8 + (n[:, 2] + 3)
+    key_b = ((dstg * b.n_atoms + src) * 8 + (3 - n[:, 0])) * 64 + (3 - n[:, 1]) * 8 + (3 - n[:, 2])
+    of, ob = np.argsort(key_f), np.argsort(key_b)
+    assert np.array_equal(key_f[of], key_b[ob])
+    # the mirrored pair is computed from (pos_j + off(-n)) - pos_i: equal up to rounding, not necessarily bitwise
+    assert np.allclose(h1.dist[of], h1.dist[ob], rtol=0, atol=1e-12)
+    seg_start = np.zeros(h1.n_edges, dtype=bool)
+    seg_start[h1.row_ptr[:-1][np.diff(h1.row_ptr) > 0]] = True
+    dd = np.diff(h1.dist)
+    assert np.all((dd >= 0) | seg_start[1:])
