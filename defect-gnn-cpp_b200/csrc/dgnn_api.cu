@@ -34,6 +34,7 @@ struct dgnn_ctx {
     // inputs staged from host
     DevBuf in_off, in_x, in_y, in_z, in_lat;
     // planning / binning
+    DevBuf small, fa, fb, fc;
     DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
     DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
     // results
@@ -50,6 +51,7 @@ struct dgnn_ctx {
     int src_target = 512;
     int tile_limit = 4096;
     int traverse_grid_mult = 16;
+    int direct_max_atoms = 2048;
 };
 
 namespace {
@@ -205,7 +207,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->geoms, &ctx->astruct,
+    DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
                       &ctx->deg, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
@@ -237,6 +239,9 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "traverse_grid_mult")) {
         if (!(value >= 1 && value <= 64)) return fail(ctx, DGNN_ERR_INVALID_ARG, "traverse_grid_mult out of range");
         ctx->traverse_grid_mult = (int)value;
+    } else if (!strcmp(name, "direct_max_atoms")) {
+        if (!(value >= 0 && value <= 65535)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_max_atoms out of range");
+        ctx->direct_max_atoms = (int)value;  // 0 sends every structure to the cell-list path
     } else {
         return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s'", name);
     }
@@ -273,6 +278,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     cudaStream_t st = ctx->stream;
     dg_num_kernel_launches_reset();
     dg_rbf_launch_count_reset();
+    dg_direct_launch_count_reset();
     memset(&ctx->info, 0, sizeof(ctx->info));
 
     // ---- inputs ----------------------------------------------------------------------------------------------
@@ -315,151 +321,223 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     CU(cudaEventRecord(ctx->ev.e[1], st));
 
-    // ---- K0: geometry + planning -------------------------------------------------------------------------------
-    ENSURE(ctx->geoms, (size_t)(S + 1) * sizeof(DgGeom));
+    // ---- geometry, classification, per-atom fractional coordinates ------------------------------------------
+    ENSURE(ctx->small, (size_t)(S + 1) * sizeof(DgSmall));
     ENSURE(ctx->astruct, (size_t)(N + 1) * 4);
-    ENSURE(ctx->acell, (size_t)(N + 1) * 12);
-    ENSURE(ctx->ncells32, (size_t)(S + 1) * 4);
-    ENSURE(ctx->nitems32, (size_t)(S + 1) * 4);
-    ENSURE(ctx->cell_base, (size_t)(S + 2) * 8);
-    ENSURE(ctx->item_base, (size_t)(S + 2) * 8);
+    ENSURE(ctx->fa, (size_t)(N + 1) * 8);
+    ENSURE(ctx->fb, (size_t)(N + 1) * 8);
+    ENSURE(ctx->fc, (size_t)(N + 1) * 8);
     ENSURE(ctx->row_ptr, (size_t)(N + 2) * 8);
     ENSURE(ctx->deg, (size_t)(N + 1) * 4);
     ENSURE(ctx->seo, (size_t)(S + 2) * 8);
-    CU(cudaMemsetAsync(ctx->stats.p, 0, sizeof(DgStats), st));
-    DgGeom* geoms = (DgGeom*)ctx->geoms.p;
-    DgStats* d_stats = (DgStats*)ctx->stats.p;
     {
         const long long mx = (N > S ? N : S) + 1;
         ENSURE(ctx->scratch, (size_t)(mx / 2048 + 4) * 8);
     }
-    dg_launch_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->cell_frac, geoms);
-    dg_launch_atom_cells(st, N, S, d_off, d_x, d_y, d_z, geoms, (int*)ctx->astruct.p, (int*)ctx->acell.p);
-    dg_launch_plan(st, S, geoms, ctx->tile_target, ctx->src_target, (int*)ctx->ncells32.p, (int*)ctx->nitems32.p,
-                   d_stats);
-    dg_scan_i32_i64(st, (const int*)ctx->ncells32.p, (long long*)ctx->cell_base.p, S, (long long*)ctx->scratch.p);
-    dg_scan_i32_i64(st, (const int*)ctx->nitems32.p, (long long*)ctx->item_base.p, S, (long long*)ctx->scratch.p);
-    dg_launch_plan_finish(st, S, geoms, (const long long*)ctx->cell_base.p, (const long long*)ctx->item_base.p,
-                          d_stats);
-    CU(cudaGetLastError());
-    {
-        int r = fetch_stats(ctx);  // sync 1: totals for the cell arrays
-        if (r != DGNN_OK) return r;
-    }
-    if (ctx->h_stats->err_status != 0)
-        return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
-                    dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
-    const long long n_cells = ctx->h_stats->n_cells;
-    const long long n_items = ctx->h_stats->n_items;
-    if (n_cells >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld grid cells: split the batch", n_cells);
-
-    // ---- K1: cell-list binning of the pruned image cloud -------------------------------------------------------
-    ENSURE(ctx->cellcount, (size_t)(n_cells + 1) * 4);
-    ENSURE(ctx->cellstart, (size_t)(n_cells + 2) * 8);
-    {
-        const size_t need = (size_t)(n_cells / 2048 + 4) * 8;
-        ENSURE(ctx->scratch, need);
-    }
-    CU(cudaMemsetAsync(ctx->cellcount.p, 0, (size_t)(n_cells + 1) * 4, st));
-    dg_launch_cloud_count(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p, (int*)ctx->cellcount.p);
-    dg_scan_i32_i64(st, (const int*)ctx->cellcount.p, (long long*)ctx->cellstart.p, n_cells,
-                    (long long*)ctx->scratch.p);
-    dg_launch_item_stats(st, n_items, S, geoms, (const long long*)ctx->item_base.p,
-                         (const long long*)ctx->cellstart.p, n_cells, d_stats);
-    CU(cudaGetLastError());
-    {
-        int r = fetch_stats(ctx);  // sync 2: cloud size, tile sizes
-        if (r != DGNN_OK) return r;
-    }
-    const long long P = ctx->h_stats->cloud_points;
-    if (P >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld image-cloud points: split the batch", P);
-    ENSURE(ctx->cx, (size_t)(P + 1) * 8);
-    ENSURE(ctx->cy, (size_t)(P + 1) * 8);
-    ENSURE(ctx->cz, (size_t)(P + 1) * 8);
-    ENSURE(ctx->cj, (size_t)(P + 1) * 4);
-    ENSURE(ctx->cn, (size_t)(P + 1) * 4);
-    dg_launch_cloud_scatter(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p, d_x, d_y, d_z,
-                            (const long long*)ctx->cellstart.p, (int*)ctx->cellcount.p, (double*)ctx->cx.p,
-                            (double*)ctx->cy.p, (double*)ctx->cz.p, (int*)ctx->cj.p, (uint32_t*)ctx->cn.p);
+    CU(cudaMemsetAsync(ctx->stats.p, 0, sizeof(DgStats), st));
+    DgStats* d_stats = (DgStats*)ctx->stats.p;
+    DgSmall* small = (DgSmall*)ctx->small.p;
+    dg_launch_small_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->direct_max_atoms, small, d_stats);
+    dg_launch_direct_prep(st, N, S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p, (double*)ctx->fa.p,
+                          (double*)ctx->fb.p, (double*)ctx->fc.p);
     CU(cudaEventRecord(ctx->ev.e[2], st));
 
-    // ---- K2: count pass ----------------------------------------------------------------------------------------
-    DgTraverseArgs A;
-    memset(&A, 0, sizeof(A));
-    A.geoms = geoms;
-    A.item_base = (const long long*)ctx->item_base.p;
-    A.n_items = n_items;
-    A.n_structs = S;
-    A.cellstart = (const long long*)ctx->cellstart.p;
-    A.cx = (const double*)ctx->cx.p; A.cy = (const double*)ctx->cy.p; A.cz = (const double*)ctx->cz.p;
-    A.cj = (const int*)ctx->cj.p; A.cn = (const uint32_t*)ctx->cn.p;
-    A.r2 = b->r_cutoff * b->r_cutoff;  // neighbor_list.cpp:40
-    A.r_cutoff = b->r_cutoff;
-    A.rcm = DG_RCM(b->r_cutoff);
-    A.epsilon = b->epsilon;
-    A.inv_rc = (float)(1.0 / b->r_cutoff);
+    // ---- common traversal parameters -------------------------------------------------------------------------
+    const double r2 = b->r_cutoff * b->r_cutoff;  // neighbor_list.cpp:40
+    int near_lo_hi, near_hi_hi;
     {
         const double lo = b->r_cutoff - 2e-6 > 0 ? b->r_cutoff - 2e-6 : 0.0, hi = b->r_cutoff + 2e-6;
         const double lo2 = lo * lo, hi2 = hi * hi;
         long long lb, hb;
         memcpy(&lb, &lo2, 8);
         memcpy(&hb, &hi2, 8);
-        A.near_lo_hi = (int)(lb >> 32);
-        A.near_hi_hi = (int)(hb >> 32);
+        near_lo_hi = (int)(lb >> 32);
+        near_hi_hi = (int)(hb >> 32);
     }
-    A.max_neighbors = b->max_neighbors > 0x7fffffffULL ? 0x7fffffff : (int)b->max_neighbors;
-    A.deg_capped = (int*)ctx->deg.p;
-    A.stats = d_stats;
-    // shared-memory plan: tile sized to the largest actual tile (bounded), rest goes the unstaged way
-    int tile_cap = round_up(ctx->h_stats->max_tile_pts > 32 ? ctx->h_stats->max_tile_pts : 32, 32);
-    if (tile_cap > ctx->tile_limit) tile_cap = ctx->tile_limit;
-    if (tile_cap < 32) tile_cap = 32;  // tile_limit 0: everything unstaged, keep a token tile
-    int tcs_cap = round_up(ctx->h_stats->max_tile_tcs > 4 ? ctx->h_stats->max_tile_tcs : 4, 4);
-    if (tcs_cap > 4096) tcs_cap = 4096;
-    A.tile_cap = ctx->tile_limit == 0 ? 0 : tile_cap;
-    A.tcs_cap = tcs_cap;
-    A.src_cap = 1024;
-    A.row_cap = 0;
-    A.n_buckets = 32;
-    A.n_warps = 8;
-    const int grid = (int)((long long)ctx->sm_count * ctx->traverse_grid_mult < n_items
-                               ? (long long)ctx->sm_count * ctx->traverse_grid_mult
-                               : (n_items > 0 ? n_items : 1));
-    if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)
-        return fail(ctx, DGNN_ERR_UNSUPPORTED, "count-pass shared memory plan does not fit");
-    CU(dg_launch_traverse(st, A, false, grid));
+    const int max_nb = b->max_neighbors > 0x7fffffffULL ? 0x7fffffff : (int)b->max_neighbors;
+
+    // ---- direct path: count pass -----------------------------------------------------------------------------
+    DgDirectArgs D;
+    memset(&D, 0, sizeof(D));
+    D.small = small;
+    D.astruct = (const int*)ctx->astruct.p;
+    D.n_atoms = N;
+    D.x = d_x; D.y = d_y; D.z = d_z;
+    D.fa = (const double*)ctx->fa.p; D.fb = (const double*)ctx->fb.p; D.fc = (const double*)ctx->fc.p;
+    D.r2 = r2;
+    D.r_cutoff = b->r_cutoff;
+    D.epsilon = b->epsilon;
+    D.inv_rc = (float)(1.0 / b->r_cutoff);
+    D.near_lo_hi = near_lo_hi;
+    D.near_hi_hi = near_hi_hi;
+    D.max_neighbors = max_nb;
+    D.n_warps = 8;
+    D.n_buckets = 32;
+    D.deg_capped = (int*)ctx->deg.p;
+    D.stats = d_stats;
+    CU(dg_launch_direct(st, D, false, ctx->sm_count));
     dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
     CU(cudaGetLastError());
-    CU(cudaEventRecord(ctx->ev.e[3], st));
     {
-        int r = fetch_stats(ctx);  // sync 3: E and the largest row
+        int r = fetch_stats(ctx);  // sync 1: errors, cell-path structures, E and the largest row (direct-only case)
         if (r != DGNN_OK) return r;
     }
+    if (ctx->h_stats->err_status != 0)
+        return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
+                    dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
+    const int n_cell_structs = ctx->h_stats->n_cell_structs;
+
+    // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
+    DgTraverseArgs A;
+    memset(&A, 0, sizeof(A));
+    long long n_items = 0, P = 0;
+    int grid = 1;
+    if (n_cell_structs > 0) {
+        ENSURE(ctx->geoms, (size_t)(S + 1) * sizeof(DgGeom));
+        ENSURE(ctx->acell, (size_t)(N + 1) * 12);
+        ENSURE(ctx->ncells32, (size_t)(S + 1) * 4);
+        ENSURE(ctx->nitems32, (size_t)(S + 1) * 4);
+        ENSURE(ctx->cell_base, (size_t)(S + 2) * 8);
+        ENSURE(ctx->item_base, (size_t)(S + 2) * 8);
+        DgGeom* geoms = (DgGeom*)ctx->geoms.p;
+        dg_launch_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->cell_frac, small, geoms);
+        dg_launch_atom_cells(st, N, S, d_off, d_x, d_y, d_z, geoms, (int*)ctx->astruct.p, (int*)ctx->acell.p);
+        dg_launch_plan(st, S, geoms, ctx->tile_target, ctx->src_target, (int*)ctx->ncells32.p,
+                       (int*)ctx->nitems32.p, d_stats);
+        dg_scan_i32_i64(st, (const int*)ctx->ncells32.p, (long long*)ctx->cell_base.p, S,
+                        (long long*)ctx->scratch.p);
+        dg_scan_i32_i64(st, (const int*)ctx->nitems32.p, (long long*)ctx->item_base.p, S,
+                        (long long*)ctx->scratch.p);
+        dg_launch_plan_finish(st, S, geoms, (const long long*)ctx->cell_base.p, (const long long*)ctx->item_base.p,
+                              d_stats);
+        CU(cudaGetLastError());
+        {
+            int r = fetch_stats(ctx);  // sync: totals for the cell arrays
+            if (r != DGNN_OK) return r;
+        }
+        if (ctx->h_stats->err_status != 0)
+            return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
+                        dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
+        const long long n_cells = ctx->h_stats->n_cells;
+        n_items = ctx->h_stats->n_items;
+        if (n_cells >= 0x7fffffffLL)
+            return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld grid cells: split the batch", n_cells);
+
+        // K1: cell-list binning of the pruned image cloud
+        ENSURE(ctx->cellcount, (size_t)(n_cells + 1) * 4);
+        ENSURE(ctx->cellstart, (size_t)(n_cells + 2) * 8);
+        {
+            const size_t need = (size_t)(n_cells / 2048 + 4) * 8;
+            ENSURE(ctx->scratch, need);
+        }
+        CU(cudaMemsetAsync(ctx->cellcount.p, 0, (size_t)(n_cells + 1) * 4, st));
+        dg_launch_cloud_count(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p,
+                              (int*)ctx->cellcount.p);
+        dg_scan_i32_i64(st, (const int*)ctx->cellcount.p, (long long*)ctx->cellstart.p, n_cells,
+                        (long long*)ctx->scratch.p);
+        dg_launch_item_stats(st, n_items, S, geoms, (const long long*)ctx->item_base.p,
+                             (const long long*)ctx->cellstart.p, n_cells, d_stats);
+        CU(cudaGetLastError());
+        {
+            int r = fetch_stats(ctx);  // sync: cloud size, tile sizes
+            if (r != DGNN_OK) return r;
+        }
+        P = ctx->h_stats->cloud_points;
+        if (P >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "%lld image-cloud points: split the batch", P);
+        ENSURE(ctx->cx, (size_t)(P + 1) * 8);
+        ENSURE(ctx->cy, (size_t)(P + 1) * 8);
+        ENSURE(ctx->cz, (size_t)(P + 1) * 8);
+        ENSURE(ctx->cj, (size_t)(P + 1) * 4);
+        ENSURE(ctx->cn, (size_t)(P + 1) * 4);
+        dg_launch_cloud_scatter(st, N, geoms, (const int*)ctx->astruct.p, (const int*)ctx->acell.p, d_x, d_y, d_z,
+                                (const long long*)ctx->cellstart.p, (int*)ctx->cellcount.p, (double*)ctx->cx.p,
+                                (double*)ctx->cy.p, (double*)ctx->cz.p, (int*)ctx->cj.p, (uint32_t*)ctx->cn.p);
+
+        // K2: count pass
+        A.geoms = geoms;
+        A.item_base = (const long long*)ctx->item_base.p;
+        A.n_items = n_items;
+        A.n_structs = S;
+        A.cellstart = (const long long*)ctx->cellstart.p;
+        A.cx = (const double*)ctx->cx.p; A.cy = (const double*)ctx->cy.p; A.cz = (const double*)ctx->cz.p;
+        A.cj = (const int*)ctx->cj.p; A.cn = (const uint32_t*)ctx->cn.p;
+        A.r2 = r2;
+        A.r_cutoff = b->r_cutoff;
+        A.rcm = DG_RCM(b->r_cutoff);
+        A.epsilon = b->epsilon;
+        A.inv_rc = (float)(1.0 / b->r_cutoff);
+        A.near_lo_hi = near_lo_hi;
+        A.near_hi_hi = near_hi_hi;
+        A.max_neighbors = max_nb;
+        A.deg_capped = (int*)ctx->deg.p;
+        A.stats = d_stats;
+        // shared-memory plan: tile sized to the largest actual tile (bounded), rest goes the unstaged way
+        int tile_cap = round_up(ctx->h_stats->max_tile_pts > 32 ? ctx->h_stats->max_tile_pts : 32, 32);
+        if (tile_cap > ctx->tile_limit) tile_cap = ctx->tile_limit;
+        if (tile_cap < 32) tile_cap = 32;  // tile_limit 0: everything unstaged, keep a token tile
+        int tcs_cap = round_up(ctx->h_stats->max_tile_tcs > 4 ? ctx->h_stats->max_tile_tcs : 4, 4);
+        if (tcs_cap > 4096) tcs_cap = 4096;
+        A.tile_cap = ctx->tile_limit == 0 ? 0 : tile_cap;
+        A.tcs_cap = tcs_cap;
+        A.src_cap = 1024;
+        A.row_cap = 0;
+        A.n_buckets = 32;
+        A.n_warps = 8;
+        grid = (int)((long long)ctx->sm_count * ctx->traverse_grid_mult < n_items
+                         ? (long long)ctx->sm_count * ctx->traverse_grid_mult
+                         : (n_items > 0 ? n_items : 1));
+        if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)
+            return fail(ctx, DGNN_ERR_UNSUPPORTED, "count-pass shared memory plan does not fit");
+        CU(dg_launch_traverse(st, A, false, grid));
+        dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+        dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
+        CU(cudaGetLastError());
+        {
+            int r = fetch_stats(ctx);  // sync: E and the largest row
+            if (r != DGNN_OK) return r;
+        }
+    }
+    CU(cudaEventRecord(ctx->ev.e[3], st));
     const long long E = ctx->h_stats->n_edges;
     const int max_deg = ctx->h_stats->max_deg;
     if (max_deg > DGNN_MAX_DEGREE)
         return fail(ctx, DGNN_ERR_DEGREE, "row degree %d exceeds %d: lower r_cutoff", max_deg, DGNN_MAX_DEGREE);
 
-    // ---- K2: fill pass (rows -> sorted CSR) --------------------------------------------------------------------
+    // ---- fill pass (rows -> sorted CSR) ----------------------------------------------------------------------
     ENSURE(ctx->dst, (size_t)(E + 1) * 4);
     ENSURE(ctx->image, (size_t)(E + 1) * 4);
     ENSURE(ctx->dist, (size_t)(E + 1) * 8);
-    A.row_ptr = (const long long*)ctx->row_ptr.p;
-    A.dst = (int*)ctx->dst.p;
-    A.image = (uint32_t*)ctx->image.p;
-    A.dist = (double*)ctx->dist.p;
-    A.row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
-    A.n_buckets = A.row_cap <= 256 ? 128 : (A.row_cap <= 1024 ? 256 : 512);
-    A.n_warps = 8;
-    while (A.n_warps > 1 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) A.n_warps >>= 1;
-    while (A.tile_cap > 0 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) {
-        A.tile_cap = A.tile_cap > 512 ? A.tile_cap / 2 : 0;  // shrink the tile: more items go unstaged
-        if (A.tile_cap == 0) A.tcs_cap = 4;
-    }
-    if ((int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin)
+    const int row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
+    const int n_buckets = row_cap <= 256 ? 128 : (row_cap <= 1024 ? 256 : 512);
+    D.row_ptr = (const long long*)ctx->row_ptr.p;
+    D.dst = (int*)ctx->dst.p;
+    D.image = (uint32_t*)ctx->image.p;
+    D.dist = (double*)ctx->dist.p;
+    D.row_cap = row_cap;
+    D.n_buckets = n_buckets;
+    D.n_warps = 8;
+    while (D.n_warps > 1 && (int)dg_direct_smem_bytes(D, true) > ctx->smem_optin) D.n_warps >>= 1;
+    if ((int)dg_direct_smem_bytes(D, true) > ctx->smem_optin)
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
-    CU(dg_launch_traverse(st, A, true, grid));
+    if (E > 0) CU(dg_launch_direct(st, D, true, ctx->sm_count));
+    if (n_cell_structs > 0 && E > 0) {
+        A.row_ptr = (const long long*)ctx->row_ptr.p;
+        A.dst = (int*)ctx->dst.p;
+        A.image = (uint32_t*)ctx->image.p;
+        A.dist = (double*)ctx->dist.p;
+        A.row_cap = row_cap;
+        A.n_buckets = n_buckets;
+        A.n_warps = 8;
+        while (A.n_warps > 1 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) A.n_warps >>= 1;
+        while (A.tile_cap > 0 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) {
+            A.tile_cap = A.tile_cap > 512 ? A.tile_cap / 2 : 0;  // shrink the tile: more items go unstaged
+            if (A.tile_cap == 0) A.tcs_cap = 4;
+        }
+        if ((int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin)
+            return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
+        CU(dg_launch_traverse(st, A, true, grid));
+    }
     CU(cudaEventRecord(ctx->ev.e[4], st));
 
     // ---- K3: fused Gaussian RBF expansion ----------------------------------------------------------------------
@@ -471,7 +549,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     CU(cudaEventRecord(ctx->ev.e[5], st));
     CU(cudaGetLastError());
     {
-        int r = fetch_stats(ctx);  // sync 4: completion + tie statistics
+        int r = fetch_stats(ctx);  // final sync: completion + tie statistics
         if (r != DGNN_OK) return r;
     }
     if (ctx->h_stats->overflow) return fail(ctx, DGNN_ERR_DEGREE, "internal: row buffer overflow");
@@ -497,11 +575,13 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     cudaEventElapsedTime(&I.fill_ms, ctx->ev.e[3], ctx->ev.e[4]);
     cudaEventElapsedTime(&I.rbf_ms, ctx->ev.e[4], ctx->ev.e[5]);
     cudaEventElapsedTime(&I.total_ms, ctx->ev.e[0], ctx->ev.e[5]);
-    I.kernel_launches = dg_num_kernel_launches_reset() + dg_rbf_launch_count_reset();
+    I.kernel_launches = dg_num_kernel_launches_reset() + dg_rbf_launch_count_reset() + dg_direct_launch_count_reset();
     I.n_items = (int32_t)n_items;
     I.cloud_points = P;
     I.staged_tile_cap = A.tile_cap;
-    I.row_cap = A.row_cap;
+    I.row_cap = row_cap;
+    I.n_cell_structs = n_cell_structs;
+    I.direct_warps = D.n_warps;
     return DGNN_OK;
 }
 

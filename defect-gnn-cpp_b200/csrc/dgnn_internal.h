@@ -20,7 +20,7 @@ struct DgStats {
     int err_status;              // first non-zero DgGeom::status seen
     int err_struct;              // and the structure it was seen on
     int overflow;                // a row did not fit the row buffer (must not happen)
-    int pad;
+    int n_cell_structs;          // non-empty structures routed to the cell-list path
 };
 
 struct DgTraverseArgs {
@@ -57,8 +57,9 @@ struct DgTraverseArgs {
 #define DG_STN_CAP 961    // stencil rows (2R_a+1)(2R_b+1) <= 31 * 31
 
 // ---- launch wrappers (dgnn_kernels.cu) ----
+// small: classification of the direct path (may be null); structures it owns get status DG_ST_SKIP here
 void dg_launch_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
-                    double r_cutoff, double cell_frac, DgGeom* geoms);
+                    double r_cutoff, double cell_frac, const DgSmall* small, DgGeom* geoms);
 void dg_launch_atom_cells(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
                           const double* x, const double* y, const double* z, DgGeom* geoms, int* astruct,
                           int* acell);
@@ -82,6 +83,40 @@ void dg_launch_finish_rows(cudaStream_t st, long long N, long long S, const long
 // exclusive scan int32 -> int64, out has n+1 entries (out[n] = total); scratch >= n/2048 + 2 entries
 void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch);
 int dg_num_kernel_launches_reset();  // returns launches since last reset
+
+// ---- dgnn_direct.cu: direct (small-structure) path ----
+struct DgDirectArgs {
+    const DgSmall* small;        // [S]
+    const int* astruct;          // [N] owning structure of every atom
+    long long n_atoms;
+    const double* x;             // Cartesian positions (reference arithmetic operands)
+    const double* y;
+    const double* z;
+    const double* fa;            // fractional coordinates (candidate windows only)
+    const double* fb;
+    const double* fc;
+    double r2;                   // r_c * r_c (fp64, computed once like neighbor_list.cpp:40)
+    double r_cutoff;
+    double epsilon;
+    float inv_rc;
+    int near_lo_hi, near_hi_hi;  // high words of (r_c -+ 2e-6)^2
+    int max_neighbors;           // clamped to INT_MAX
+    int row_cap, n_buckets, n_warps;
+    int* deg_capped;             // [N] (count pass)
+    const long long* row_ptr;    // [N+1] (fill pass)
+    int* dst;
+    uint32_t* image;
+    double* dist;
+    DgStats* stats;
+};
+void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
+                          double r_cutoff, int direct_max_atoms, DgSmall* small, DgStats* stats);
+void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
+                           const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
+                           double* fa, double* fb, double* fc);
+size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
+cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count);
+int dg_direct_launch_count_reset();
 
 // ---- dgnn_rbf.cu ----
 void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff, double dr,

@@ -13,6 +13,7 @@
 #include <stdint.h>
 
 #include "dgnn_internal.h"
+#include "row_sort.cuh"
 
 static int g_launches = 0;
 int dg_num_kernel_launches_reset() {
@@ -22,7 +23,9 @@ int dg_num_kernel_launches_reset() {
 }
 #define DG_COUNT_LAUNCH() (++g_launches)
 
+#ifndef FULL_MASK
 #define FULL_MASK 0xffffffffu
+#endif
 
 // =====================================================================================================================
 // Exclusive scan int32 -> int64 (three small kernels; inputs are a few million elements at most)
@@ -139,7 +142,8 @@ void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n
 // K0: per-structure geometry, per-atom cell coordinates, planning
 // =====================================================================================================================
 __global__ void k_geom(long long S, const long long* __restrict__ atom_offsets, const double* __restrict__ lattice,
-                       double r_cutoff, double cell_frac, DgGeom* __restrict__ geoms) {
+                       double r_cutoff, double cell_frac, const DgSmall* __restrict__ small,
+                       DgGeom* __restrict__ geoms) {
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= S) return;
     DgGeom G;
@@ -148,6 +152,7 @@ __global__ void k_geom(long long S, const long long* __restrict__ atom_offsets, 
     for (int i = 0; i < 9; ++i) L[i] = lattice[9 * s + i];
     const long long a0 = atom_offsets[s], a1 = atom_offsets[s + 1];
     dg_geom_init(&G, L, (int)(a1 - a0), r_cutoff, cell_frac);
+    if (small && small[s].mode != DG_MODE_CELL) G.status = DG_ST_SKIP;
     G.atom_base = a0;
     G.cell_base = 0;
     G.item_base = 0;
@@ -155,9 +160,9 @@ __global__ void k_geom(long long S, const long long* __restrict__ atom_offsets, 
 }
 
 void dg_launch_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
-                    double r_cutoff, double cell_frac, DgGeom* geoms) {
+                    double r_cutoff, double cell_frac, const DgSmall* small, DgGeom* geoms) {
     if (S <= 0) return;
-    k_geom<<<(unsigned)((S + 127) / 128), 128, 0, st>>>(S, atom_offsets, lattice, r_cutoff, cell_frac, geoms);
+    k_geom<<<(unsigned)((S + 127) / 128), 128, 0, st>>>(S, atom_offsets, lattice, r_cutoff, cell_frac, small, geoms);
     DG_COUNT_LAUNCH();
 }
 
@@ -226,7 +231,7 @@ __global__ void k_plan(long long S, DgGeom* __restrict__ geoms, int tile_target,
     DgGeom* G = geoms + s;
     dg_geom_plan(G, tile_target, src_target);
     if (G->status != DG_ST_OK) {
-        if (atomicCAS(&stats->err_status, 0, G->status) == 0) stats->err_struct = (int)s;
+        if (G->status != DG_ST_SKIP && atomicCAS(&stats->err_status, 0, G->status) == 0) stats->err_struct = (int)s;
         G->ncells = 0;
         G->nitems = 0;
     }
@@ -425,20 +430,13 @@ struct Smem {
     int* rowbase;
     uint32_t* src;
     signed char* stn;
-    // per-warp (fill)
-    double* rd;
-    uint32_t* rt;
-    uint32_t* bs;
-    unsigned short* ord;
-    unsigned short* fin;
-    int* cnt;
+    RowBuf rb;  // per-warp (fill)
 };
 
 __host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
 
 __host__ __device__ inline size_t warp_smem_bytes(int row_cap, int n_buckets) {
-    return align16((size_t)row_cap * 8) + align16((size_t)row_cap * 4) * 2 + align16((size_t)row_cap * 2) * 2 +
-           align16((size_t)(n_buckets + 1) * 4);
+    return dg_rowbuf_bytes(row_cap, n_buckets);
 }
 
 __host__ __device__ inline size_t shared_part_bytes(int tile_cap, int tcs_cap, int src_cap) {
@@ -464,16 +462,8 @@ __device__ __forceinline__ Smem carve(unsigned char* base, const DgTraverseArgs&
     s.rowbase = (int*)p; p += align16((size_t)(DG_ROWS_CAP + 1) * 4);
     s.src = (uint32_t*)p; p += align16((size_t)A.src_cap * 4);
     s.stn = (signed char*)p; p += align16((size_t)DG_STN_CAP * 2);
-    s.rd = nullptr; s.rt = nullptr; s.bs = nullptr; s.ord = nullptr; s.fin = nullptr; s.cnt = nullptr;
-    if (fill) {
-        p += (size_t)warp * warp_smem_bytes(A.row_cap, A.n_buckets);
-        s.rd = (double*)p; p += align16((size_t)A.row_cap * 8);
-        s.rt = (uint32_t*)p; p += align16((size_t)A.row_cap * 4);
-        s.bs = (uint32_t*)p; p += align16((size_t)A.row_cap * 4);
-        s.ord = (unsigned short*)p; p += align16((size_t)A.row_cap * 2);
-        s.fin = (unsigned short*)p; p += align16((size_t)A.row_cap * 2);
-        s.cnt = (int*)p;
-    }
+    s.rb = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (fill) s.rb = dg_rowbuf_carve(p + (size_t)warp * warp_smem_bytes(A.row_cap, A.n_buckets), A.row_cap);
     return s;
 }
 
@@ -543,8 +533,9 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
                 if (hit) {
                     const int pos = m + __popc(mask & lt_mask);
                     if (pos < A.row_cap) {
-                        sm.rd[pos] = d2;
-                        sm.rt[pos] = (uint32_t)pc;
+                        sm.rb.rd[pos] = d2;
+                        sm.rb.rj[pos] = pv.j[pc];
+                        sm.rb.rn[pos] = pv.n[pc];
                     }
                 }
             }
@@ -561,86 +552,7 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
         if (lane == 0) atomicExch(&A.stats->overflow, 1);
         return;
     }
-    // ---- row sort: sqrt, monotone bucket of the distance, histogram, exclusive scan, in-bucket rank ----
-    const int NBk = A.n_buckets;
-    for (int b = lane; b <= NBk; b += 32) sm.cnt[b] = 0;
-    __syncwarp();
-    const float scale = (float)NBk;
-    for (int e = lane; e < m; e += 32) {
-        const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
-        sm.rd[e] = d;
-        const float t = (float)d * A.inv_rc;
-        int b = (int)(t * t * t * scale);
-        b = b < 0 ? 0 : (b >= NBk ? NBk - 1 : b);
-        const int slot = atomicAdd(&sm.cnt[b], 1);
-        sm.bs[e] = (uint32_t)b | ((uint32_t)slot << 16);
-    }
-    __syncwarp();
-    {   // exclusive scan of cnt[0..NBk) in place, cnt[NBk] = m.  NBk is a multiple of 32.
-        const int per = NBk >> 5;
-        int local[16];
-        int sum = 0;
-        for (int i = 0; i < per; ++i) {
-            local[i] = sm.cnt[lane * per + i];
-            sum += local[i];
-        }
-        int inc = sum;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const int t = __shfl_up_sync(FULL_MASK, inc, o);
-            if (lane >= o) inc += t;
-        }
-        int run = inc - sum;
-        for (int i = 0; i < per; ++i) {
-            sm.cnt[lane * per + i] = run;
-            run += local[i];
-        }
-        if (lane == 31) sm.cnt[NBk] = run;
-    }
-    __syncwarp();
-    for (int e = lane; e < m; e += 32) {
-        const uint32_t v = sm.bs[e];
-        sm.ord[sm.cnt[v & 0xffffu] + (v >> 16)] = (unsigned short)e;
-    }
-    __syncwarp();
-    for (int e = lane; e < m; e += 32) {
-        const int b = sm.bs[e] & 0xffffu;
-        const int q0 = sm.cnt[b], q1 = sm.cnt[b + 1];
-        const double de = sm.rd[e];
-        int rank = q0;
-        if (q1 - q0 > 1) {
-            const uint32_t pe = sm.rt[e];
-            const unsigned long long ke =
-                ((unsigned long long)(uint32_t)pv.j[pe] << 32) | dg_image_sort_key(pv.n[pe]);
-            for (int q = q0; q < q1; ++q) {
-                const int f = sm.ord[q];
-                if (f == e) continue;
-                const double df = sm.rd[f];
-                if (df < de) {
-                    ++rank;
-                } else if (df == de) {
-                    const uint32_t pf = sm.rt[f];
-                    const unsigned long long kf =
-                        ((unsigned long long)(uint32_t)pv.j[pf] << 32) | dg_image_sort_key(pv.n[pf]);
-                    if (kf < ke) ++rank;
-                }
-            }
-        }
-        sm.fin[rank] = (unsigned short)e;
-    }
-    __syncwarp();
-    const long long o = A.row_ptr[iglob];
-    for (int r = lane; r < keep; r += 32) {
-        const int e = sm.fin[r];
-        const uint32_t p = sm.rt[e];
-        A.dst[o + r] = pv.j[p];
-        A.image[o + r] = pv.n[p];
-        A.dist[o + r] = sm.rd[e];
-    }
-    if (m > keep && keep > 0 && lane == 0) {
-        if (sm.rd[sm.fin[keep - 1]] == sm.rd[sm.fin[keep]]) atomicAdd(&A.stats->n_tie_rows, 1);
-    }
-    __syncwarp();
+    dg_row_sort_emit(sm.rb, m, keep, A.n_buckets, A.inv_rc, A.row_ptr[iglob], A.dst, A.image, A.dist, A.stats, lane);
 }
 
 template <bool FILL>

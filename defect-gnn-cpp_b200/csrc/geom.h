@@ -40,6 +40,7 @@
 
 enum {
     DG_ST_OK = 0,
+    DG_ST_SKIP = 1,  // structure handled by the direct path: the cell-list pipeline ignores it
     DG_ST_SINGULAR = 4,
     DG_ST_IMAGE_RANGE = 5,
     DG_ST_GEOMETRY = 6,
@@ -286,4 +287,108 @@ DG_HD uint32_t dg_pack_image(int na, int nb, int nc) {
 DG_HD uint32_t dg_image_sort_key(uint32_t packed) {
     const uint32_t b = packed ^ 0x00808080u;  // bias each int8 by +128
     return ((b & 0xffu) << 16) | (b & 0xff00u) | ((b >> 16) & 0xffu);
+}
+
+// =====================================================================================================================
+// Direct (small-structure) path: no cell list.  For a source atom i and a candidate atom j only the periodic images
+// n whose fractional offset can bring j within r_c of i are tested:  the projection of the displacement on the unit
+// normal of lattice plane k is |f_j[k] + n_k - f_i[k]| * h_k (h_k = perpendicular height of the cell along axis k), and
+// it never exceeds the distance, so  |f_j[k] + n_k - f_i[k]| < r_c / h_k  for every true neighbour.  The window is
+// evaluated with the candidate radius DG_RCM(r_c) (margin >> rounding of the fractional coordinates) and then clipped
+// to the reference cube |n_k| <= nimg (rule R3).  Acceptance itself always uses the reference arithmetic.
+// =====================================================================================================================
+enum { DG_MODE_CELL = 0, DG_MODE_ATOMPAR = 1, DG_MODE_IMGPAR = 2 };
+
+struct DgSmall {
+    double L[9];      // lattice rows a, b, c
+    double Linv[9];   // frac_k = x*Linv[0+k] + y*Linv[3+k] + z*Linv[6+k]
+    double w[3];      // DG_RCM(r_c) / h_k: half-width of the image window in fractional units
+    long long atom_base;
+    int natoms;
+    int nimg;         // reference image range n (neighbor_list.cpp:68-72)
+    int status;       // DG_ST_*
+    int mode;         // DG_MODE_*
+};
+
+// direct_max_atoms: structures with more atoms go to the cell-list path.
+DG_HD void dg_small_init(DgSmall* G, const double* L, long long atom_base, int natoms, double r_cutoff,
+                         int direct_max_atoms) {
+    for (int i = 0; i < 9; ++i) G->L[i] = L[i];
+    for (int i = 0; i < 9; ++i) G->Linv[i] = 0.0;
+    G->w[0] = G->w[1] = G->w[2] = 0.0;
+    G->atom_base = atom_base;
+    G->natoms = natoms;
+    G->status = DG_ST_OK;
+    G->mode = DG_MODE_ATOMPAR;
+    G->nimg = dg_num_images(L, r_cutoff);
+    if (G->nimg < 0) {
+        G->status = DG_ST_SINGULAR;
+        return;
+    }
+    if (G->nimg > 127) {
+        G->status = DG_ST_IMAGE_RANGE;
+        return;
+    }
+    const double c00 = L[4] * L[8] - L[5] * L[7];
+    const double c01 = L[5] * L[6] - L[3] * L[8];
+    const double c02 = L[3] * L[7] - L[4] * L[6];
+    const double det = L[0] * c00 + L[1] * c01 + L[2] * c02;
+    if (det == 0.0 || !isfinite(det)) {
+        G->status = DG_ST_SINGULAR;
+        return;
+    }
+    const double id = 1.0 / det;
+    G->Linv[0] = c00 * id;
+    G->Linv[1] = (L[2] * L[7] - L[1] * L[8]) * id;
+    G->Linv[2] = (L[1] * L[5] - L[2] * L[4]) * id;
+    G->Linv[3] = c01 * id;
+    G->Linv[4] = (L[0] * L[8] - L[2] * L[6]) * id;
+    G->Linv[5] = (L[2] * L[3] - L[0] * L[5]) * id;
+    G->Linv[6] = c02 * id;
+    G->Linv[7] = (L[1] * L[6] - L[0] * L[7]) * id;
+    G->Linv[8] = (L[0] * L[4] - L[1] * L[3]) * id;
+    const double rcm = DG_RCM(r_cutoff);
+    double test = 1.0;  // estimated images per candidate pair
+    for (int k = 0; k < 3; ++k) {
+        const double cn = sqrt(G->Linv[k] * G->Linv[k] + G->Linv[3 + k] * G->Linv[3 + k] +
+                               G->Linv[6 + k] * G->Linv[6 + k]);  // = 1 / h_k
+        if (!(cn > 0.0) || !isfinite(cn)) {
+            G->status = DG_ST_SINGULAR;
+            return;
+        }
+        G->w[k] = rcm * cn;
+        double t = 2.0 * G->w[k];
+        const double tmax = (double)(2 * G->nimg + 1);
+        if (t < 1.0) t = 1.0;
+        if (t > tmax) t = tmax;
+        test *= t;
+    }
+    if (natoms > direct_max_atoms) {
+        G->mode = DG_MODE_CELL;
+        return;
+    }
+    // lane efficiency of the two direct traversals: lanes over atoms (slot loop over images, ~60 % balance) versus
+    // lanes over the images of one pair
+    const double n = (double)(natoms > 0 ? natoms : 1);
+    const double eff_atom = n / (ceil(n / 32.0) * 32.0) * (test > 1.5 ? 0.6 : 1.0);
+    const double eff_img = test / (ceil(test / 32.0) * 32.0);
+    G->mode = eff_img > eff_atom ? DG_MODE_IMGPAR : DG_MODE_ATOMPAR;
+}
+
+DG_HD double dg_frac_coord(const double* Linv, int k, double x, double y, double z) {
+    return x * Linv[k] + y * Linv[3 + k] + z * Linv[6 + k];
+}
+
+// Images n of candidate j along one axis: integers in [t - w, t + w] with t = f_i - f_j, clipped to [-nimg, nimg].
+// Returns the count (0 if none), *lo = first n.
+DG_HD int dg_axis_window(double t, double w, int nimg, int* lo) {
+    double a = ceil(t - w), b = floor(t + w);
+    const double lim = (double)nimg;
+    if (!(a >= -lim)) a = -lim;  // also catches NaN
+    if (!(b <= lim)) b = lim;
+    if (a > lim + 1.0) a = lim + 1.0;  // keep the int conversions defined for absurd inputs
+    if (b < -lim - 1.0) b = -lim - 1.0;
+    *lo = (int)a;
+    const int c = (int)b - (int)a + 1;
+    return c > 0 ? c : 0;
 }

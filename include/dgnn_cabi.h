@@ -130,13 +130,16 @@ typedef struct {
     int64_t cloud_points;    /* pruned periodic image cloud size */
     int32_t staged_tile_cap; /* shared-memory tile capacity used (points) */
     int32_t row_cap;         /* shared-memory row buffer capacity used */
+    int32_t n_cell_structs;  /* structures routed to the cell-list path (the rest took the direct path) */
+    int32_t direct_warps;    /* warps per CTA of the direct fill pass */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
 void* dgnn_stream(dgnn_ctx* ctx);
 
-/* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5). */
+/* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5);
+ * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048). */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus

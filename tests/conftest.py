@@ -64,6 +64,9 @@ def harness_lib():
                                         C.c_int, C.c_int, C.c_int64, i64p, C.POINTER(C.c_int32),
                                         C.POINTER(C.c_uint32), dp, i64p, i64p, i64p]
     H.harness_neighbor_list.restype = C.c_int
+    H.harness_direct_neighbor_list.argtypes = [C.c_int64, dp, dp, dp, dp, C.c_double, C.c_uint64, C.c_double, C.c_int64,
+                                               i64p, C.POINTER(C.c_int32), C.POINTER(C.c_uint32), dp, i64p, i64p, i64p]
+    H.harness_direct_neighbor_list.restype = C.c_int
     return H
 
 
@@ -73,6 +76,18 @@ def gpu_builder(pkg):
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     gb = pkg.GraphBuilder(0)
+    yield gb
+    gb.close()
+
+
+@pytest.fixture(scope="session")
+def gpu_builder_cell(pkg):
+    """Same library, every structure forced through the cell-list path (direct_max_atoms = 0)."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("direct_max_atoms", 0)
     yield gb
     gb.close()
 

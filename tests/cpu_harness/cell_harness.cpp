@@ -189,4 +189,75 @@ int harness_neighbor_list(int64_t n, const double* x, const double* y, const dou
     return 0;
 }
 
+
+// CPU emulation of the direct (small-structure) traversal of dgnn_direct.cu: per source atom, per candidate atom, the
+// fractional-coordinate image window (dg_small_init / dg_axis_window from geom.h), reference arithmetic for the accept
+// test.  mode_out receives the traversal the classification picks; info[0] = candidates tested.
+int harness_direct_neighbor_list(int64_t n, const double* x, const double* y, const double* z, const double* lattice,
+                                 double r_cutoff, uint64_t max_neighbors, double epsilon, int64_t edge_cap,
+                                 int64_t* row_ptr, int32_t* dst, uint32_t* image, double* dist, int64_t* n_edges_out,
+                                 int64_t* n_near_out, int64_t* info /* [4]: candidates mode nimg - */) {
+    DgSmall G;
+    dg_small_init(&G, lattice, 0, (int)n, r_cutoff, 1 << 30);
+    if (G.status != DG_ST_OK) return G.status;
+    std::vector<double> fa((size_t)n), fb((size_t)n), fc((size_t)n);
+    for (int64_t a = 0; a < n; ++a) {
+        fa[a] = dg_frac_coord(G.Linv, 0, x[a], y[a], z[a]);
+        fb[a] = dg_frac_coord(G.Linv, 1, x[a], y[a], z[a]);
+        fc[a] = dg_frac_coord(G.Linv, 2, x[a], y[a], z[a]);
+    }
+    const double r2 = r_cutoff * r_cutoff;
+    int64_t e = 0, near = 0, ncand = 0;
+    bool fits = true;
+    std::vector<Edge> row;
+    for (int64_t i = 0; i < n; ++i) {
+        row.clear();
+        for (int64_t j = 0; j < n; ++j) {
+            int lo0, lo1, lo2;
+            const int c0 = dg_axis_window(fa[i] - fa[j], G.w[0], G.nimg, &lo0);
+            const int c1 = dg_axis_window(fb[i] - fb[j], G.w[1], G.nimg, &lo1);
+            const int c2 = dg_axis_window(fc[i] - fc[j], G.w[2], G.nimg, &lo2);
+            for (int ia = 0; ia < c0; ++ia)
+                for (int ib = 0; ib < c1; ++ib)
+                    for (int ic = 0; ic < c2; ++ic) {
+                        const int na = lo0 + ia, nb = lo1 + ib, nc = lo2 + ic;
+                        ++ncand;
+                        const double px = x[j] + dg_image_offset(G.L, 0, na, nb, nc);
+                        const double py = y[j] + dg_image_offset(G.L, 1, na, nb, nc);
+                        const double pz = z[j] + dg_image_offset(G.L, 2, na, nb, nc);
+                        const double dx = x[i] - px, dy = y[i] - py, dz = z[i] - pz;
+                        const double d2 = ((dx * dx) + (dy * dy)) + (dz * dz);
+                        if (std::fabs(std::sqrt(d2) - r_cutoff) <= 1e-6) ++near;
+                        if (!(d2 < r2)) continue;
+                        const double d = std::sqrt(d2);
+                        if (j == i && d < epsilon) continue;
+                        row.push_back(Edge{d, (int)j, dg_pack_image(na, nb, nc)});
+                    }
+        }
+        std::sort(row.begin(), row.end(), edge_less);
+        if (row.size() > max_neighbors) row.resize((size_t)max_neighbors);
+        row_ptr[i] = e;
+        for (const Edge& ed : row) {
+            if (e < edge_cap) {
+                dst[e] = ed.dst;
+                image[e] = ed.n;
+                dist[e] = ed.dist;
+            } else {
+                fits = false;
+            }
+            ++e;
+        }
+    }
+    row_ptr[n] = e;
+    *n_edges_out = e;
+    *n_near_out = near;
+    if (info) {
+        info[0] = ncand;
+        info[1] = G.mode;
+        info[2] = G.nimg;
+        info[3] = 0;
+    }
+    return fits ? 0 : -1;
+}
+
 }  // extern "C"

@@ -53,7 +53,34 @@ def test_c2_perovskite_batch_uncapped_with_rbf(gpu_builder, oracle, syn):
     h = check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2)
     assert h.K == 40 and h.n_edges > 24 * 25_000
     info = gpu_builder.info()
-    assert info.kernel_launches >= 10 and info.staged_tile_cap > 0
+    assert info.n_cell_structs == 0 and info.kernel_launches >= 7     # supercells take the direct path
+
+
+def test_c2_perovskite_batch_cell_list_path(gpu_builder_cell, oracle, syn):
+    b = syn.c2_batch(12, seed0=4321)
+    h = check_batch(gpu_builder_cell, oracle, b, 8.0, None, dr=0.2)
+    info = gpu_builder_cell.info()
+    assert info.n_cell_structs == 12 and info.staged_tile_cap > 0 and info.kernel_launches >= 10
+    check_batch(gpu_builder_cell, oracle, b, 10.0, 20, dr=0.1)
+
+
+def test_mixed_direct_and_cell_list_batch(pkg, oracle, syn):
+    """One batch, both paths: structures above direct_max_atoms go through the cell list, the rest direct; the CSR
+    is one array ordered by atom."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    parts = [syn.perovskite_supercell(4, 4, 4, seed=4)[:4], syn.triclinic_cell(7)[:4], none,
+             syn.perovskite_supercell(4, 4, 2, seed=9)[:4], syn.perovskite_supercell(5, 4, 3, seed=10)[:4],
+             syn.triclinic_cell(8)[:4]]
+    b = syn.concat(parts)
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("direct_max_atoms", 200)
+    check_batch(gb, oracle, b, 8.0, None, dr=0.2)
+    assert gb.info().n_cell_structs == 2
+    check_batch(gb, oracle, b, 6.0, 12, dr=0.2)
+    gb.close()
 
 
 def test_c2_capped_and_viewer_params(gpu_builder, oracle, syn):
@@ -83,8 +110,9 @@ def test_c1_shipped_poscars_all_param_sets(gpu_builder, oracle, syn, c1_structur
             assert hh.hexdigest() == exp[nm][pname]["edge_sha256"], (nm, pname)
 
 
-def test_c3_triclinic_short_vectors(gpu_builder, oracle, syn):
+def test_c3_triclinic_short_vectors(gpu_builder, gpu_builder_cell, oracle, syn):
     b = syn.c3_batch(300)
+    check_batch(gpu_builder_cell, oracle, syn.c3_batch(60, seed0=99), 8.0, None, dr=0.2)
     h = check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2)
     # multi-image and self-image edges are present (same (src,dst) through several images; dst == src)
     src = np.repeat(np.arange(b.n_atoms), np.diff(h.row_ptr))
@@ -92,14 +120,16 @@ def test_c3_triclinic_short_vectors(gpu_builder, oracle, syn):
     assert np.any(local_src == h.dst)
 
 
-def test_adversarial_cells_reference_image_range(gpu_builder, oracle, syn):
+def test_adversarial_cells_reference_image_range(gpu_builder, gpu_builder_cell, oracle, syn):
     b = syn.adversarial_cells()
-    check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
-    check_batch(gpu_builder, oracle, b, 3.0, 5, algo=oracle.ALGO_BRUTE)
+    for gb in (gpu_builder, gpu_builder_cell):
+        check_batch(gb, oracle, b, 8.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+        check_batch(gb, oracle, b, 3.0, 5, algo=oracle.ALGO_BRUTE)
 
 
-def test_known_answers_and_edge_cases(gpu_builder, oracle, syn, pkg):
-    gb = gpu_builder
+@pytest.mark.parametrize("path", ["direct", "cell"])
+def test_known_answers_and_edge_cases(gpu_builder, gpu_builder_cell, oracle, syn, pkg, path):
+    gb = gpu_builder if path == "direct" else gpu_builder_cell
     sc = syn.simple_cubic(1.0, 1)
     h = check_batch(gb, oracle, sc, 3.05, None, algo=oracle.ALGO_BRUTE)
     d2 = np.round(h.dist ** 2).astype(int)
@@ -156,8 +186,11 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
     x, y, z, L, _ = syn.perovskite_supercell(9, 8, 7, seed=11)
     b = syn.concat([(x, y, z, L)])
     o = oracle.neighbor_list(x, y, z, L, 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
-    for opts in ({}, {"tile_target": 512, "src_target": 48}, {"tile_limit": 0}, {"cell_frac": 0.3}, {"cell_frac": 1.0}):
+    for opts in ({}, {"tile_target": 512, "src_target": 48}, {"tile_limit": 0}, {"cell_frac": 0.3}, {"cell_frac": 1.0},
+                 {"direct_max_atoms": 4096}):
         gb = pkg.GraphBuilder(0)
+        if "direct_max_atoms" not in opts:
+            gb.set_option("direct_max_atoms", 0)
         for k, v in opts.items():
             gb.set_option(k, v)
         g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, 8.0, oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
@@ -168,6 +201,7 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
             assert info.staged_tile_cap == 0
         if "tile_target" in opts:
             assert info.n_items > 20
+        assert info.n_cell_structs == (0 if "direct_max_atoms" in opts else 1)
         gb.close()
 
 
