@@ -52,6 +52,9 @@ struct dgnn_ctx {
     int tile_limit = 4096;
     int traverse_grid_mult = 16;
     int direct_max_atoms = 2048;
+    int direct_min_blocks = 2;
+    int sort_buckets = 0;
+    int fuse_rbf = 1;
 };
 
 namespace {
@@ -239,6 +242,16 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "traverse_grid_mult")) {
         if (!(value >= 1 && value <= 64)) return fail(ctx, DGNN_ERR_INVALID_ARG, "traverse_grid_mult out of range");
         ctx->traverse_grid_mult = (int)value;
+    } else if (!strcmp(name, "direct_min_blocks")) {
+        if (!(value >= 2 && value <= 3)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_min_blocks must be 2 or 3");
+        ctx->direct_min_blocks = (int)value;  // register budget of the direct kernels: 128 (2) or 80 (3) per thread
+    } else if (!strcmp(name, "sort_buckets")) {
+        const int v = (int)value;
+        if (!(v == 0 || (v >= 32 && v <= 2048 && (v & (v - 1)) == 0)))
+            return fail(ctx, DGNN_ERR_INVALID_ARG, "sort_buckets must be 0 (auto) or a power of two in [32, 2048]");
+        ctx->sort_buckets = v;
+    } else if (!strcmp(name, "fuse_rbf")) {
+        ctx->fuse_rbf = value != 0.0;  // 0: separate K3 launch after the fill pass (phase-separated timing)
     } else if (!strcmp(name, "direct_max_atoms")) {
         if (!(value >= 0 && value <= 65535)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_max_atoms out of range");
         ctx->direct_max_atoms = (int)value;  // 0 sends every structure to the cell-list path
@@ -339,7 +352,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     DgSmall* small = (DgSmall*)ctx->small.p;
     dg_launch_small_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->direct_max_atoms, small, d_stats);
     dg_launch_direct_prep(st, N, S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p, (double*)ctx->fa.p,
-                          (double*)ctx->fb.p, (double*)ctx->fc.p);
+                          (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
     CU(cudaEventRecord(ctx->ev.e[2], st));
 
     // ---- common traversal parameters -------------------------------------------------------------------------
@@ -375,7 +388,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.n_buckets = 32;
     D.deg_capped = (int*)ctx->deg.p;
     D.stats = d_stats;
-    CU(dg_launch_direct(st, D, false, ctx->sm_count));
+    CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
     dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
     CU(cudaGetLastError());
@@ -509,7 +522,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     ENSURE(ctx->image, (size_t)(E + 1) * 4);
     ENSURE(ctx->dist, (size_t)(E + 1) * 8);
     const int row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
-    const int n_buckets = row_cap <= 256 ? 128 : (row_cap <= 1024 ? 256 : 512);
+    const int n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 1024 ? 512 : 1024);
     D.row_ptr = (const long long*)ctx->row_ptr.p;
     D.dst = (int*)ctx->dst.p;
     D.image = (uint32_t*)ctx->image.p;
@@ -517,10 +530,16 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.row_cap = row_cap;
     D.n_buckets = n_buckets;
     D.n_warps = 8;
+    // fused RBF epilogue: rows stream their K features right after the sort (needs K % 4 == 0 for the float4 stores)
+    const int keep_max = max_deg < max_nb ? max_deg : max_nb;
+    const bool fuse_rbf = want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
+                          (long long)keep_max * (K / 4) < (1LL << 22);
+    if (want_rbf && E > 0) ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
+    if (fuse_rbf) D.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
     while (D.n_warps > 1 && (int)dg_direct_smem_bytes(D, true) > ctx->smem_optin) D.n_warps >>= 1;
     if ((int)dg_direct_smem_bytes(D, true) > ctx->smem_optin)
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
-    if (E > 0) CU(dg_launch_direct(st, D, true, ctx->sm_count));
+    if (E > 0) CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
     if (n_cell_structs > 0 && E > 0) {
         A.row_ptr = (const long long*)ctx->row_ptr.p;
         A.dst = (int*)ctx->dst.p;
@@ -529,6 +548,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         A.row_cap = row_cap;
         A.n_buckets = n_buckets;
         A.n_warps = 8;
+        A.rbf = D.rbf;
         while (A.n_warps > 1 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) A.n_warps >>= 1;
         while (A.tile_cap > 0 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) {
             A.tile_cap = A.tile_cap > 512 ? A.tile_cap / 2 : 0;  // shrink the tile: more items go unstaged
@@ -541,8 +561,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     CU(cudaEventRecord(ctx->ev.e[4], st));
 
     // ---- K3: fused Gaussian RBF expansion ----------------------------------------------------------------------
-    if (want_rbf && E > 0) {
-        ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
+    if (want_rbf && E > 0 && !fuse_rbf) {
         dg_launch_rbf_f32(st, (const double*)ctx->dist.p, E, K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p,
                           ctx->sm_count);
     }
@@ -582,6 +601,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.row_cap = row_cap;
     I.n_cell_structs = n_cell_structs;
     I.direct_warps = D.n_warps;
+    I.rbf_fused = fuse_rbf ? 1 : 0;
     return DGNN_OK;
 }
 

@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(256) k_direct_prep(long long N, long long S,
                                                      const double* __restrict__ z,
                                                      const DgSmall* __restrict__ small, int* __restrict__ astruct,
                                                      double* __restrict__ fa, double* __restrict__ fb,
-                                                     double* __restrict__ fc) {
+                                                     double* __restrict__ fc, DgStats* __restrict__ stats) {
     const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= N) return;
     long long lo = 0, hi = S;  // last s with atom_offsets[s] <= a
@@ -75,38 +75,59 @@ __global__ void __launch_bounds__(256) k_direct_prep(long long N, long long S,
     astruct[a] = (int)lo;
     const DgSmall* G = small + lo;
     const double px = x[a], py = y[a], pz = z[a];
-    fa[a] = dg_frac_coord(G->Linv, 0, px, py, pz);
-    fb[a] = dg_frac_coord(G->Linv, 1, px, py, pz);
-    fc[a] = dg_frac_coord(G->Linv, 2, px, py, pz);
+    const double f0 = dg_frac_coord(G->Linv, 0, px, py, pz);
+    const double f1 = dg_frac_coord(G->Linv, 1, px, py, pz);
+    const double f2 = dg_frac_coord(G->Linv, 2, px, py, pz);
+    fa[a] = f0;
+    fb[a] = f1;
+    fc[a] = f2;
+    // the traversal's integer windows need bounded fractional coordinates (also rejects NaN / Inf positions)
+    if (G->status == DG_ST_OK && G->mode != DG_MODE_CELL &&
+        !(fabs(f0) <= 1.0e6 && fabs(f1) <= 1.0e6 && fabs(f2) <= 1.0e6)) {
+        if (atomicCAS(&stats->err_status, 0, DG_ST_UNWRAPPED) == 0) stats->err_struct = (int)lo;
+    }
 }
 
 void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
                            const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
-                           double* fa, double* fb, double* fc) {
+                           double* fa, double* fb, double* fc, DgStats* stats) {
     if (N <= 0) return;
     k_direct_prep<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, S, atom_offsets, x, y, z, small, astruct, fa, fb,
-                                                                fc);
+                                                                fc, stats);
     ++g_direct_launches;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // traversal
 // ---------------------------------------------------------------------------------------------------------------------
+#define DG_ROW_CHUNK 64  // consecutive source atoms owned by one CTA at a time (keeps the structure's lines in L1)
+
+// floor / ceil of |x| < 2^31 as int32 through the 2^52 + 2^51 trick: one FP64-pipe add instead of FRND + F2I on the
+// quarter-rate conversion unit.  The prep kernel rejects fractional coordinates beyond +-1e6, so |x| is bounded.
+#define DG_MAGIC 6755399441055744.0
+__device__ __forceinline__ int dg_floor_i(double x) { return __double2loint(__dadd_rd(x, DG_MAGIC)); }
+__device__ __forceinline__ int dg_ceil_i(double x) { return __double2loint(__dadd_ru(x, DG_MAGIC)); }
+
+// images n of a candidate along one axis: integers in [t - w, t + w] clipped to [-nimg, nimg]  (= dg_axis_window)
+__device__ __forceinline__ int axis_window_fast(double t, double w, int nimg, int* lo) {
+    int a = dg_ceil_i(t - w), b = dg_floor_i(t + w);
+    a = a < -nimg ? -nimg : a;
+    b = b > nimg ? nimg : b;
+    *lo = a;
+    const int c = b - a + 1;
+    return c > 0 ? c : 0;
+}
+
 struct Src {
     double x, y, z;
-    double L[9];
     int iloc;
 };
 
-// One candidate (atom jloc at (xj,yj,zj), image (na,nb,nc)) per lane; compacts hits into the row buffer.
+// One candidate image point (px,py,pz) of atom jloc per lane; compacts hits into the row buffer.
 template <bool FILL>
-__device__ __forceinline__ void test_candidate(const DgDirectArgs& A, const Src& S, const RowBuf& rb, bool active,
-                                               int jloc, double xj, double yj, double zj, int na, int nb, int nc,
-                                               unsigned lt_mask, int& m, unsigned& near) {
-    // reference cloud point: position + offset, offset = (n_a*row0 + n_b*row1) + n_c*row2  (neighbor_list.cpp:82-87)
-    const double px = DG_ADD(xj, dg_image_offset(S.L, 0, na, nb, nc));
-    const double py = DG_ADD(yj, dg_image_offset(S.L, 1, na, nb, nc));
-    const double pz = DG_ADD(zj, dg_image_offset(S.L, 2, na, nb, nc));
+__device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb, bool active, int jloc,
+                                           double px, double py, double pz, int na, int nb, int nc,
+                                           unsigned lt_mask, int& m, unsigned& near) {
     const double dx = DG_SUB(S.x, px);
     const double dy = DG_SUB(S.y, py);
     const double dz = DG_SUB(S.z, pz);
@@ -136,8 +157,8 @@ __device__ __forceinline__ void test_candidate(const DgDirectArgs& A, const Src&
     m += __popc(mask);
 }
 
-template <bool FILL>
-__global__ void __launch_bounds__(256, 3) k_direct(const DgDirectArgs A) {
+template <bool FILL, int MINB>
+__global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -145,77 +166,105 @@ __global__ void __launch_bounds__(256, 3) k_direct(const DgDirectArgs A) {
     if (FILL) rb = dg_rowbuf_carve(smem_raw + (size_t)warp * dg_rowbuf_bytes(A.row_cap, A.n_buckets), A.row_cap);
     unsigned near = 0;
     int maxdeg = 0;
+    const long long n_chunks = (A.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
 
-    for (long long a = (long long)blockIdx.x * nwarps + warp; a < A.n_atoms; a += (long long)gridDim.x * nwarps) {
-        const DgSmall* __restrict__ G = A.small + A.astruct[a];
-        const int mode = G->mode;
-        if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;  // the cell-list path owns this structure
-        const long long base = G->atom_base;
-        const int N = G->natoms, nimg = G->nimg;
-        Src S;
-        S.x = A.x[a]; S.y = A.y[a]; S.z = A.z[a];
-        S.iloc = (int)(a - base);
-#pragma unroll
-        for (int i = 0; i < 9; ++i) S.L[i] = G->L[i];
-        const double fi0 = A.fa[a], fi1 = A.fb[a], fi2 = A.fc[a];
-        const double w0 = G->w[0], w1 = G->w[1], w2 = G->w[2];
-        int m = 0;
-        if (mode == DG_MODE_ATOMPAR) {
-            // lanes over candidate atoms; slot loop over each lane's image window
-            for (int jb = 0; jb < N; jb += 32) {
-                const int j = jb + lane;
-                const bool valid = j < N;
-                const int jj = valid ? j : N - 1;
-                const long long gj = base + jj;
-                const double xj = A.x[gj], yj = A.y[gj], zj = A.z[gj];
-                int lo0, lo1, lo2;
-                const int c0 = dg_axis_window(fi0 - A.fa[gj], w0, nimg, &lo0);
-                const int c1 = dg_axis_window(fi1 - A.fb[gj], w1, nimg, &lo1);
-                const int c2 = dg_axis_window(fi2 - A.fc[gj], w2, nimg, &lo2);
-                const int cnt = valid ? c0 * c1 * c2 : 0;
-                const int maxcnt = __reduce_max_sync(FULL_MASK, cnt);
-                int ia = 0, ib = 0, ic = 0;
-                for (int sl = 0; sl < maxcnt; ++sl) {
-                    test_candidate<FILL>(A, S, rb, sl < cnt, jj, xj, yj, zj, lo0 + ia, lo1 + ib, lo2 + ic, lt_mask, m,
-                                         near);
-                    if (++ic == c2) {
-                        ic = 0;
-                        if (++ib == c1) {
-                            ib = 0;
-                            ++ia;
+    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const long long a_end = (chunk + 1) * DG_ROW_CHUNK < A.n_atoms ? (chunk + 1) * DG_ROW_CHUNK : A.n_atoms;
+        for (long long a = chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
+            const DgSmall* __restrict__ G = A.small + A.astruct[a];
+            const int mode = G->mode;
+            if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;  // the cell-list path owns this structure
+            const long long base = G->atom_base;
+            const int N = G->natoms, nimg = G->nimg;
+            Src S;
+            S.x = A.x[a]; S.y = A.y[a]; S.z = A.z[a];
+            S.iloc = (int)(a - base);
+            const double fi0 = A.fa[a], fi1 = A.fb[a], fi2 = A.fc[a];
+            const double w0 = G->w[0], w1 = G->w[1], w2 = G->w[2];
+            const double L20 = G->L[6], L21 = G->L[7], L22 = G->L[8];
+            int m = 0;
+            if (mode == DG_MODE_ATOMPAR) {
+                const double L00 = G->L[0], L01 = G->L[1], L02 = G->L[2];
+                const double L10 = G->L[3], L11 = G->L[4], L12 = G->L[5];
+                // lanes over candidate atoms (next chunk's loads in flight while this one is tested); nested loops
+                // over the warp-wide image window, per-lane windows masked
+                long long gj = base + (lane < N ? lane : N - 1);
+                double nx = A.x[gj], ny = A.y[gj], nz = A.z[gj];
+                double nfa = A.fa[gj], nfb = A.fb[gj], nfc = A.fc[gj];
+                for (int jb = 0; jb < N; jb += 32) {
+                    const int j = jb + lane;
+                    const bool valid = j < N;
+                    const int jj = valid ? j : N - 1;
+                    const double xj = nx, yj = ny, zj = nz;
+                    const double t0 = fi0 - nfa, t1 = fi1 - nfb, t2 = fi2 - nfc;
+                    if (jb + 32 < N) {
+                        const int jn = j + 32;
+                        gj = base + (jn < N ? jn : N - 1);
+                        nx = A.x[gj]; ny = A.y[gj]; nz = A.z[gj];
+                        nfa = A.fa[gj]; nfb = A.fb[gj]; nfc = A.fc[gj];
+                    }
+                    int lo0, lo1, lo2;
+                    int c0 = axis_window_fast(t0, w0, nimg, &lo0);
+                    int c1 = axis_window_fast(t1, w1, nimg, &lo1);
+                    int c2 = axis_window_fast(t2, w2, nimg, &lo2);
+                    if (!valid) c0 = 0;
+                    const int mc0 = __reduce_max_sync(FULL_MASK, c0);
+                    const int mc1 = __reduce_max_sync(FULL_MASK, c0 ? c1 : 0);
+                    const int mc2 = __reduce_max_sync(FULL_MASK, c0 ? c2 : 0);
+                    double nad = (double)lo0;
+                    for (int sa = 0; sa < mc0; ++sa, nad += 1.0) {
+                        const double oa0 = DG_MUL(nad, L00), oa1 = DG_MUL(nad, L01), oa2 = DG_MUL(nad, L02);
+                        double nbd = (double)lo1;
+                        for (int sb = 0; sb < mc1; ++sb, nbd += 1.0) {
+                            // offset = (n_a*row0 + n_b*row1) + n_c*row2, neighbor_list.cpp:82-84
+                            const double ob0 = DG_ADD(oa0, DG_MUL(nbd, L10));
+                            const double ob1 = DG_ADD(oa1, DG_MUL(nbd, L11));
+                            const double ob2 = DG_ADD(oa2, DG_MUL(nbd, L12));
+                            const bool act_ab = sa < c0 && sb < c1;
+                            double ncd = (double)lo2;
+                            for (int sc = 0; sc < mc2; ++sc, ncd += 1.0) {
+                                const double px = DG_ADD(xj, DG_ADD(ob0, DG_MUL(ncd, L20)));
+                                const double py = DG_ADD(yj, DG_ADD(ob1, DG_MUL(ncd, L21)));
+                                const double pz = DG_ADD(zj, DG_ADD(ob2, DG_MUL(ncd, L22)));
+                                test_point<FILL>(A, S, rb, act_ab && sc < c2, jj, px, py, pz, lo0 + sa, lo1 + sb,
+                                                 lo2 + sc, lt_mask, m, near);
+                            }
                         }
                     }
                 }
-            }
-        } else {
-            // lanes over the image window of one candidate atom at a time
-            for (int j = 0; j < N; ++j) {
-                const long long gj = base + j;
-                const double xj = A.x[gj], yj = A.y[gj], zj = A.z[gj];
-                int lo0, lo1, lo2;
-                const int c0 = dg_axis_window(fi0 - A.fa[gj], w0, nimg, &lo0);
-                const int c1 = dg_axis_window(fi1 - A.fb[gj], w1, nimg, &lo1);
-                const int c2 = dg_axis_window(fi2 - A.fc[gj], w2, nimg, &lo2);
-                const int T = c0 * c1 * c2;
-                for (int tb = 0; tb < T; tb += 32) {
-                    const int t = tb + lane;
-                    const bool active = t < T;
-                    const int tt = active ? t : 0;
-                    const int ic = tt % c2, tq = tt / c2;
-                    const int ib = tq % c1, ia = tq / c1;
-                    test_candidate<FILL>(A, S, rb, active, j, xj, yj, zj, lo0 + ia, lo1 + ib, lo2 + ic, lt_mask, m,
-                                         near);
+            } else {
+                // lanes over the image window of one candidate atom at a time
+                for (int j = 0; j < N; ++j) {
+                    const long long gj = base + j;
+                    const double xj = A.x[gj], yj = A.y[gj], zj = A.z[gj];
+                    int lo0, lo1, lo2;
+                    const int c0 = axis_window_fast(fi0 - A.fa[gj], w0, nimg, &lo0);
+                    const int c1 = axis_window_fast(fi1 - A.fb[gj], w1, nimg, &lo1);
+                    const int c2 = axis_window_fast(fi2 - A.fc[gj], w2, nimg, &lo2);
+                    const int T = c0 * c1 * c2;
+                    for (int tb = 0; tb < T; tb += 32) {
+                        const int t = tb + lane;
+                        const bool active = t < T;
+                        const int tt = active ? t : 0;
+                        const int ic = tt % c2, tq = tt / c2;
+                        const int na = lo0 + tq / c1, nb = lo1 + tq % c1, nc = lo2 + ic;
+                        const double px = DG_ADD(xj, dg_image_offset(G->L, 0, na, nb, nc));
+                        const double py = DG_ADD(yj, dg_image_offset(G->L, 1, na, nb, nc));
+                        const double pz = DG_ADD(zj, dg_image_offset(G->L, 2, na, nb, nc));
+                        test_point<FILL>(A, S, rb, active, j, px, py, pz, na, nb, nc, lt_mask, m, near);
+                    }
                 }
             }
-        }
-        maxdeg = m > maxdeg ? m : maxdeg;
-        const int keep = m < A.max_neighbors ? m : A.max_neighbors;
-        if (!FILL) {
-            if (lane == 0) A.deg_capped[a] = keep;
-        } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
-            if (lane == 0) atomicExch(&A.stats->overflow, 1);
-        } else {
-            dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.row_ptr[a], A.dst, A.image, A.dist, A.stats, lane);
+            maxdeg = m > maxdeg ? m : maxdeg;
+            const int keep = m < A.max_neighbors ? m : A.max_neighbors;
+            if (!FILL) {
+                if (lane == 0) A.deg_capped[a] = keep;
+            } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
+                if (lane == 0) atomicExch(&A.stats->overflow, 1);
+            } else {
+                dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.row_ptr[a], A.dst, A.image, A.dist, A.stats,
+                                 lane, A.rbf);
+            }
         }
     }
     if (!FILL) {
@@ -232,29 +281,30 @@ size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {
     return fill ? (size_t)a.n_warps * dg_rowbuf_bytes(a.row_cap, a.n_buckets) : 0;
 }
 
-cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count) {
+template <bool FILL, int MINB>
+static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
+    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB>, threads, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin
+    const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    long long grid = (long long)sm_count * occ;
+    if (grid > want) grid = want;
+    k_direct<FILL, MINB><<<(unsigned)grid, threads, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks) {
     if (a.n_atoms <= 0) return cudaSuccess;
     const size_t smem = dg_direct_smem_bytes(a, fill);
     const int threads = a.n_warps * 32;
-    cudaError_t e;
-    int occ = 1;
-    if (fill) {
-        e = cudaFuncSetAttribute(k_direct<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<true>, threads, smem);
-    } else {
-        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<false>, threads, smem);
-    }
-    if (e != cudaSuccess) return e;
-    if (occ < 1) occ = 1;
-    // persistent grid: every SM full, rows handed out round-robin (consecutive atoms to the warps of one CTA)
-    const long long want = (a.n_atoms + a.n_warps - 1) / a.n_warps;
-    long long grid = (long long)sm_count * occ;
-    if (grid > want) grid = want;
-    if (fill)
-        k_direct<true><<<(unsigned)grid, threads, smem, st>>>(a);
-    else
-        k_direct<false><<<(unsigned)grid, threads, smem, st>>>(a);
     ++g_direct_launches;
-    return cudaGetLastError();
+    if (min_blocks <= 2)
+        return fill ? launch_direct_t<true, 2>(st, a, sm_count, smem, threads)
+                    : launch_direct_t<false, 2>(st, a, sm_count, smem, threads);
+    return fill ? launch_direct_t<true, 3>(st, a, sm_count, smem, threads)
+                : launch_direct_t<false, 3>(st, a, sm_count, smem, threads);
 }

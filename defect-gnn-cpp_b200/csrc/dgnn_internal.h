@@ -23,6 +23,17 @@ struct DgStats {
     int n_cell_structs;          // non-empty structures routed to the cell-list path
 };
 
+// Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
+struct DgRbfEpi {
+    float dr;      // bin spacing
+    float coef;    // -0.5 / sigma^2 * log2(e)
+    float norm;    // 1 / (sigma * sqrt(2 pi))
+    float inv_k4;  // 1 / (K/4)
+    int K4;        // K / 4
+    float4* out;   // E x K fp32 row-major
+};
+DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out);  // dgnn_rbf.cu
+
 struct DgTraverseArgs {
     // inputs
     const DgGeom* geoms;
@@ -51,6 +62,7 @@ struct DgTraverseArgs {
     uint32_t* image;
     double* dist;
     DgStats* stats;
+    DgRbfEpi rbf;
 };
 
 #define DG_ROWS_CAP 1024  // tile rows (td_a * td_b) <= 32 * 32
@@ -108,14 +120,15 @@ struct DgDirectArgs {
     uint32_t* image;
     double* dist;
     DgStats* stats;
+    DgRbfEpi rbf;
 };
 void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
                           double r_cutoff, int direct_max_atoms, DgSmall* small, DgStats* stats);
 void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
                            const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
-                           double* fa, double* fb, double* fc);
+                           double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
-cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count);
+cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
 int dg_direct_launch_count_reset();
 
 // ---- dgnn_rbf.cu ----

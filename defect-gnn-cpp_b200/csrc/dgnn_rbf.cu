@@ -87,6 +87,18 @@ static RbfParams make_params(int K, double r_cutoff, double dr) {
     return P;
 }
 
+DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out) {
+    const RbfParams P = make_params(K, r_cutoff, dr);
+    DgRbfEpi e;
+    e.dr = P.dr;
+    e.coef = P.coef;
+    e.norm = P.norm;
+    e.inv_k4 = P.inv_k4;
+    e.K4 = P.K4;
+    e.out = reinterpret_cast<float4*>(out);
+    return e;
+}
+
 void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff, double dr,
                        float* out, int sm_count) {
     if (n_edges <= 0 || K <= 0) return;

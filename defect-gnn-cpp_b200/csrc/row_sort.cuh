@@ -24,13 +24,16 @@ struct RowBuf {
     uint32_t* rn;         // packed image
     uint32_t* bs;         // bucket | slot << 16
     unsigned short* ord;  // bucket-ordered entry ids
-    unsigned short* fin;  // final rank -> entry id
-    int* cnt;             // [n_buckets + 1]
+    float* fd;            // distances in final row order (fp32), input of the fused RBF epilogue
+    int* cnt;             // bucket counters / starts, padded: index(b) = b + b / per  (+ 2 words for the tie check)
 };
 
+// counters live at b + (b >> log2(per)), per = n_buckets / 32: every lane's segment starts on its own bank
+__host__ __device__ inline size_t dg_cnt_words(int n_buckets) { return (size_t)n_buckets + 32 + 4; }
+
 __host__ __device__ inline size_t dg_rowbuf_bytes(int row_cap, int n_buckets) {
-    return dg_align16((size_t)row_cap * 8) + dg_align16((size_t)row_cap * 4) * 3 + dg_align16((size_t)row_cap * 2) * 2 +
-           dg_align16((size_t)(n_buckets + 1) * 4);
+    return dg_align16((size_t)row_cap * 8) + dg_align16((size_t)row_cap * 4) * 4 + dg_align16((size_t)row_cap * 2) +
+           dg_align16(dg_cnt_words(n_buckets) * 4);
 }
 
 __device__ __forceinline__ RowBuf dg_rowbuf_carve(unsigned char* p, int row_cap) {
@@ -40,17 +43,24 @@ __device__ __forceinline__ RowBuf dg_rowbuf_carve(unsigned char* p, int row_cap)
     r.rn = (uint32_t*)p; p += dg_align16((size_t)row_cap * 4);
     r.bs = (uint32_t*)p; p += dg_align16((size_t)row_cap * 4);
     r.ord = (unsigned short*)p; p += dg_align16((size_t)row_cap * 2);
-    r.fin = (unsigned short*)p; p += dg_align16((size_t)row_cap * 2);
+    r.fd = (float*)p; p += dg_align16((size_t)row_cap * 4);
     r.cnt = (int*)p;
     return r;
 }
 
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
-// NBk (number of buckets) is a multiple of 32 and <= 512.  All 32 lanes must call.
+// NBk (number of buckets) is a power of two, 32 <= NBk <= 2048.  All 32 lanes must call.
+// rbf.K4 > 0: fused Gaussian RBF epilogue (edge_features.cpp:7-24 applied per edge as crystal_graph.cpp:32-40 does):
+// the row's keep x K fp32 features are one contiguous span of the E x K tensor, written with flat float4 indexing
+// (every warp store covers 512 contiguous bytes) straight from the sorted distances in shared memory.
 __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
                                                  long long o, int* __restrict__ dst, uint32_t* __restrict__ image,
-                                                 double* __restrict__ dist, DgStats* __restrict__ stats, int lane) {
-    for (int b = lane; b <= NBk; b += 32) sm.cnt[b] = 0;
+                                                 double* __restrict__ dist, DgStats* __restrict__ stats, int lane,
+                                                 const DgRbfEpi& rbf) {
+    const int per = NBk >> 5;
+    const int lper = 31 - __clz(per);
+    const int nwords = NBk + 32 + 1;
+    for (int b = lane; b < nwords; b += 32) sm.cnt[b] = 0;
     __syncwarp();
     const float scale = (float)NBk;
     for (int e = lane; e < m; e += 32) {
@@ -59,14 +69,14 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
         const float t = (float)d * inv_rc;
         int b = (int)(t * t * t * scale);
         b = b < 0 ? 0 : (b >= NBk ? NBk - 1 : b);
-        const int slot = atomicAdd(&sm.cnt[b], 1);
+        const int slot = atomicAdd(&sm.cnt[b + (b >> lper)], 1);
         sm.bs[e] = (uint32_t)b | ((uint32_t)slot << 16);
     }
     __syncwarp();
-    {   // exclusive scan of cnt[0..NBk) in place, cnt[NBk] = m
-        const int per = NBk >> 5;
+    {   // exclusive scan of the counters in place (lane owns buckets [lane*per, (lane+1)*per)); index(NBk) = m
+        const int base = lane * per + lane;
         int sum = 0;
-        for (int i = 0; i < per; ++i) sum += sm.cnt[lane * per + i];
+        for (int i = 0; i < per; ++i) sum += sm.cnt[base + i];
         int inc = sum;
 #pragma unroll
         for (int off = 1; off < 32; off <<= 1) {
@@ -75,50 +85,71 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
         }
         int run = inc - sum;
         for (int i = 0; i < per; ++i) {
-            const int c = sm.cnt[lane * per + i];
-            sm.cnt[lane * per + i] = run;
+            const int c = sm.cnt[base + i];
+            sm.cnt[base + i] = run;
             run += c;
         }
-        if (lane == 31) sm.cnt[NBk] = run;
+        if (lane == 31) sm.cnt[NBk + 32] = run;  // index(NBk) = NBk + (NBk >> lper)
     }
     __syncwarp();
     for (int e = lane; e < m; e += 32) {
         const uint32_t v = sm.bs[e];
-        sm.ord[sm.cnt[v & 0xffffu] + (v >> 16)] = (unsigned short)e;
+        const int b = v & 0xffffu;
+        sm.ord[sm.cnt[b + (b >> lper)] + (v >> 16)] = (unsigned short)e;
     }
     __syncwarp();
+    int* tie = sm.cnt + NBk + 33;  // two words: entry ids ranked keep-1 and keep
     for (int e = lane; e < m; e += 32) {
-        const int b = sm.bs[e] & 0xffffu;
-        const int q0 = sm.cnt[b], q1 = sm.cnt[b + 1];
+        const int b = sm.bs[e] & 0xffffu, b1 = b + 1;
+        const int q0 = sm.cnt[b + (b >> lper)], q1 = sm.cnt[b1 + (b1 >> lper)];
+        const double de = sm.rd[e];
         int rank = q0;
-        if (q1 - q0 > 1) {
-            const double de = sm.rd[e];
-            const unsigned long long ke =
-                ((unsigned long long)(uint32_t)sm.rj[e] << 32) | dg_image_sort_key(sm.rn[e]);
-            for (int q = q0; q < q1; ++q) {
-                const int f = sm.ord[q];
-                if (f == e) continue;
-                const double df = sm.rd[f];
-                if (df < de) {
-                    ++rank;
-                } else if (df == de) {
-                    const unsigned long long kf =
-                        ((unsigned long long)(uint32_t)sm.rj[f] << 32) | dg_image_sort_key(sm.rn[f]);
-                    if (kf < ke) ++rank;
-                }
+        for (int q = q0; q < q1; ++q) {
+            const int f = sm.ord[q];
+            const double df = sm.rd[f];
+            if (df < de) {
+                ++rank;
+            } else if (df == de && f != e) {  // rare: exact distance tie -> canonical (dst, n_a, n_b, n_c)
+                const unsigned long long ke =
+                    ((unsigned long long)(uint32_t)sm.rj[e] << 32) | dg_image_sort_key(sm.rn[e]);
+                const unsigned long long kf =
+                    ((unsigned long long)(uint32_t)sm.rj[f] << 32) | dg_image_sort_key(sm.rn[f]);
+                if (kf < ke) ++rank;
             }
         }
-        sm.fin[rank] = (unsigned short)e;
+        if (rank < keep) {  // scattered inside the row's contiguous range; L2 merges the sectors
+            dst[o + rank] = sm.rj[e];
+            image[o + rank] = sm.rn[e];
+            dist[o + rank] = de;
+            sm.fd[rank] = (float)de;
+        }
+        if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+    }
+    if (m > keep && keep > 0) {
+        __syncwarp();
+        if (lane == 0 && sm.rd[tie[0]] == sm.rd[tie[1]]) atomicAdd(&stats->n_tie_rows, 1);
     }
     __syncwarp();
-    for (int r = lane; r < keep; r += 32) {
-        const int e = sm.fin[r];
-        dst[o + r] = sm.rj[e];
-        image[o + r] = sm.rn[e];
-        dist[o + r] = sm.rd[e];
+    if (rbf.K4 > 0) {
+        float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
+        const int nq = keep * rbf.K4;
+#pragma unroll 4
+        for (int q = lane; q < nq; q += 32) {
+            const int e = (int)(((float)q + 0.5f) * rbf.inv_k4);  // q / K4, exact for q < 2^22
+            const int k = (q - e * rbf.K4) << 2;
+            const float d = sm.fd[e];
+            const float c0 = (float)k * rbf.dr;
+            const float x0 = c0 - d;
+            const float x1 = (c0 + rbf.dr) - d;
+            const float x2 = (c0 + 2.0f * rbf.dr) - d;
+            const float x3 = (c0 + 3.0f * rbf.dr) - d;
+            float4 v;
+            v.x = rbf.norm * exp2f(rbf.coef * x0 * x0);
+            v.y = rbf.norm * exp2f(rbf.coef * x1 * x1);
+            v.z = rbf.norm * exp2f(rbf.coef * x2 * x2);
+            v.w = rbf.norm * exp2f(rbf.coef * x3 * x3);
+            __stcs(o4 + q, v);
+        }
+        __syncwarp();
     }
-    if (m > keep && keep > 0 && lane == 0) {
-        if (sm.rd[sm.fin[keep - 1]] == sm.rd[sm.fin[keep]]) atomicAdd(&stats->n_tie_rows, 1);
-    }
-    __syncwarp();
 }

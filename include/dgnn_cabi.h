@@ -132,6 +132,8 @@ typedef struct {
     int32_t row_cap;         /* shared-memory row buffer capacity used */
     int32_t n_cell_structs;  /* structures routed to the cell-list path (the rest took the direct path) */
     int32_t direct_warps;    /* warps per CTA of the direct fill pass */
+    int32_t rbf_fused;       /* 1: features were written by the fill pass's fused epilogue (rbf_ms is then 0) */
+    int32_t reserved;
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 
