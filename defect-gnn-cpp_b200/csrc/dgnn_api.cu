@@ -143,6 +143,30 @@ int fetch_stats(dgnn_ctx* ctx) {
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
+// The near-cutoff band  fabs(sqrt(d2) - r_c) <= 1e-6  (evaluated in fp64 exactly like the oracle) as an interval of
+// d2: sqrt and the subtraction are monotone, so the band is [lo, hi] in the ordering of non-negative doubles; both ends
+// are found by bisection on the bit pattern.  Lets the count pass test the band without a square root.
+void near_band_d2(double rc, double* lo_out, double* hi_out) {
+    auto f = [rc](double d2) { return std::sqrt(d2) - rc; };
+    auto from_bits = [](unsigned long long u) { double d; memcpy(&d, &u, 8); return d; };
+    auto to_bits = [](double d) { unsigned long long u; memcpy(&u, &d, 8); return u; };
+    const unsigned long long top = to_bits((rc + 1.0) * (rc + 1.0));
+    // lo = smallest d2 >= 0 with f(d2) >= -1e-6
+    unsigned long long a = 0, b = top;
+    while (a < b) {
+        const unsigned long long mid = a + (b - a) / 2;
+        if (f(from_bits(mid)) >= -1e-6) b = mid; else a = mid + 1;
+    }
+    *lo_out = from_bits(a);
+    // hi = largest d2 with f(d2) <= 1e-6
+    a = 0; b = top;
+    while (a < b) {
+        const unsigned long long mid = a + (b - a + 1) / 2;
+        if (f(from_bits(mid)) <= 1e-6) a = mid; else b = mid - 1;
+    }
+    *hi_out = from_bits(a);
+}
+
 }  // namespace
 
 extern "C" {
@@ -350,7 +374,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     CU(cudaMemsetAsync(ctx->stats.p, 0, sizeof(DgStats), st));
     DgStats* d_stats = (DgStats*)ctx->stats.p;
     DgSmall* small = (DgSmall*)ctx->small.p;
-    dg_launch_small_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->direct_max_atoms, small, d_stats);
+    const int eps_mode = !(b->epsilon > 0.0) ? 0 : (b->epsilon <= DG_EPS_FAST ? 1 : 2);
+    dg_launch_small_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->direct_max_atoms, eps_mode == 1 ? b->epsilon : 0.0,
+                         small, d_stats);
     dg_launch_direct_prep(st, N, S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p, (double*)ctx->fa.p,
                           (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
     CU(cudaEventRecord(ctx->ev.e[2], st));
@@ -383,6 +409,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.inv_rc = (float)(1.0 / b->r_cutoff);
     D.near_lo_hi = near_lo_hi;
     D.near_hi_hi = near_hi_hi;
+    D.eps_mode = eps_mode;
+    near_band_d2(b->r_cutoff, &D.near_d2_lo, &D.near_d2_hi);
     D.max_neighbors = max_nb;
     D.n_warps = 8;
     D.n_buckets = 32;

@@ -31,8 +31,8 @@ int dg_direct_launch_count_reset() {
 // ---------------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long* __restrict__ atom_offsets,
                                                     const double* __restrict__ lattice, double r_cutoff,
-                                                    int direct_max_atoms, DgSmall* __restrict__ small,
-                                                    DgStats* __restrict__ stats) {
+                                                    int direct_max_atoms, double eps_fast,
+                                                    DgSmall* __restrict__ small, DgStats* __restrict__ stats) {
     const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= S) return;
     double L[9];
@@ -41,6 +41,13 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
     const long long a0 = atom_offsets[s], a1 = atom_offsets[s + 1];
     DgSmall G;
     dg_small_init(&G, L, a0, (int)(a1 - a0), r_cutoff, direct_max_atoms);
+    if (G.status == DG_ST_OK && G.mode != DG_MODE_CELL && eps_fast > 0.0) {
+        // fast self-exclusion (EPS = 1) assumes no periodic self-image is closer than epsilon: every lattice
+        // translation is at least one perpendicular height h_k = rcm / w_k long
+        const double rcm = DG_RCM(r_cutoff);
+        const double wmax = fmax(G.w[0], fmax(G.w[1], G.w[2]));
+        if (!(rcm > 2.0 * eps_fast * wmax)) G.status = DG_ST_GEOMETRY;
+    }
     small[s] = G;
     if (G.status != DG_ST_OK) {
         if (atomicCAS(&stats->err_status, 0, G.status) == 0) stats->err_struct = (int)s;
@@ -50,10 +57,10 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
 }
 
 void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
-                          double r_cutoff, int direct_max_atoms, DgSmall* small, DgStats* stats) {
+                          double r_cutoff, int direct_max_atoms, double eps_fast, DgSmall* small, DgStats* stats) {
     if (S <= 0) return;
     k_small_geom<<<(unsigned)((S + 127) / 128), 128, 0, st>>>(S, atom_offsets, lattice, r_cutoff, direct_max_atoms,
-                                                               small, stats);
+                                                               eps_fast, small, stats);
     ++g_direct_launches;
 }
 
@@ -124,40 +131,46 @@ struct Src {
 };
 
 // One candidate image point (px,py,pz) of atom jloc per lane; compacts hits into the row buffer.
-template <bool FILL>
-__device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb, bool active, int jloc,
-                                           double px, double py, double pz, int na, int nb, int nc,
-                                           unsigned lt_mask, int& m, unsigned& near) {
+// EPS selects the self-exclusion rule `orig == i && sqrt(d2) < epsilon` (neighbor_list.cpp:47-49):
+//   0: epsilon <= 0, nothing is excluded;  1: 0 < epsilon <= DG_EPS_FAST: only the atom's own n = (0,0,0) image can
+//   qualify (its d2 is exactly 0; k_small_geom rejects cells whose perpendicular height is below 2 epsilon), so the
+//   test is the branch-free `self && d2 == 0`;  2: any epsilon, exact sqrt test behind a (rare) branch.
+template <bool FILL, int EPS>
+__device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb, bool active,
+                                           bool self, int jloc, double px, double py, double pz, int na, int nb,
+                                           int nc, unsigned lt_mask, int& m, unsigned& near) {
     const double dx = DG_SUB(S.x, px);
     const double dy = DG_SUB(S.y, py);
     const double dz = DG_SUB(S.z, pz);
     // nanoflann evalMetric: result = 0; result += dx*dx; += dy*dy; += dz*dz
     const double d2 = DG_ADD(DG_ADD(DG_MUL(dx, dx), DG_MUL(dy, dy)), DG_MUL(dz, dz));
     bool hit = active && (d2 < A.r2);
-    if (hit && jloc == S.iloc) {
-        if (__dsqrt_rn(d2) < A.epsilon) hit = false;  // neighbor_list.cpp:47-49
-    }
-    if (!FILL) {
-        const int hi = __double2hiint(d2);
-        if (active && hi >= A.near_lo_hi && hi <= A.near_hi_hi) {
-            if (fabs(__dsqrt_rn(d2) - A.r_cutoff) <= 1e-6) near++;
+    if (EPS == 1) hit = hit && !(self && d2 == 0.0);
+    if (EPS == 2) {
+        if (hit && self) {
+            if (__dsqrt_rn(d2) < A.epsilon) hit = false;
         }
     }
+    if (!FILL) {
+        // count pass: per-lane tallies, reduced once per row (no ballot per candidate).  near-cutoff band
+        // |sqrt(d2) - r_c| <= 1e-6 as two thresholds on d2 (sqrt is monotone; thresholds bisected on the host)
+        near += (active && d2 >= A.near_d2_lo && d2 <= A.near_d2_hi) ? 1u : 0u;
+        m += hit ? 1 : 0;
+        return;
+    }
     const unsigned mask = __ballot_sync(FULL_MASK, hit);
-    if (FILL) {
-        if (hit) {
-            const int pos = m + __popc(mask & lt_mask);
-            if (pos < A.row_cap) {
-                rb.rd[pos] = d2;
-                rb.rj[pos] = jloc;
-                rb.rn[pos] = dg_pack_image(na, nb, nc);
-            }
+    if (hit) {
+        const int pos = m + __popc(mask & lt_mask);
+        if (pos < A.row_cap) {
+            rb.rd[pos] = d2;
+            rb.rj[pos] = jloc;
+            rb.rn[pos] = dg_pack_image(na, nb, nc);
         }
     }
     m += __popc(mask);
 }
 
-template <bool FILL, int MINB>
+template <bool FILL, int MINB, int EPS>
 __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -196,6 +209,7 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                     const bool valid = j < N;
                     const int jj = valid ? j : N - 1;
                     const double xj = nx, yj = ny, zj = nz;
+                    const bool self = jj == S.iloc;
                     const double t0 = fi0 - nfa, t1 = fi1 - nfb, t2 = fi2 - nfc;
                     if (jb + 32 < N) {
                         const int jn = j + 32;
@@ -226,8 +240,8 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                                 const double px = DG_ADD(xj, DG_ADD(ob0, DG_MUL(ncd, L20)));
                                 const double py = DG_ADD(yj, DG_ADD(ob1, DG_MUL(ncd, L21)));
                                 const double pz = DG_ADD(zj, DG_ADD(ob2, DG_MUL(ncd, L22)));
-                                test_point<FILL>(A, S, rb, act_ab && sc < c2, jj, px, py, pz, lo0 + sa, lo1 + sb,
-                                                 lo2 + sc, lt_mask, m, near);
+                                test_point<FILL, EPS>(A, S, rb, act_ab && sc < c2, self, jj, px, py, pz, lo0 + sa,
+                                                      lo1 + sb, lo2 + sc, lt_mask, m, near);
                             }
                         }
                     }
@@ -251,10 +265,12 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                         const double px = DG_ADD(xj, dg_image_offset(G->L, 0, na, nb, nc));
                         const double py = DG_ADD(yj, dg_image_offset(G->L, 1, na, nb, nc));
                         const double pz = DG_ADD(zj, dg_image_offset(G->L, 2, na, nb, nc));
-                        test_point<FILL>(A, S, rb, active, j, px, py, pz, na, nb, nc, lt_mask, m, near);
+                        test_point<FILL, EPS>(A, S, rb, active, j == S.iloc, j, px, py, pz, na, nb, nc, lt_mask, m,
+                                              near);
                     }
                 }
             }
+            if (!FILL) m = __reduce_add_sync(FULL_MASK, m);
             maxdeg = m > maxdeg ? m : maxdeg;
             const int keep = m < A.max_neighbors ? m : A.max_neighbors;
             if (!FILL) {
@@ -281,20 +297,30 @@ size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {
     return fill ? (size_t)a.n_warps * dg_rowbuf_bytes(a.row_cap, a.n_buckets) : 0;
 }
 
-template <bool FILL, int MINB>
+template <bool FILL, int MINB, int EPS>
 static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e =
+        cudaFuncSetAttribute(k_direct<FILL, MINB, EPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int occ = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB>, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS>, threads, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin
     const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
     long long grid = (long long)sm_count * occ;
     if (grid > want) grid = want;
-    k_direct<FILL, MINB><<<(unsigned)grid, threads, smem, st>>>(a);
+    k_direct<FILL, MINB, EPS><<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
+}
+
+template <bool FILL, int MINB>
+static cudaError_t launch_direct_e(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
+    switch (a.eps_mode) {
+        case 0: return launch_direct_t<FILL, MINB, 0>(st, a, sm_count, smem, threads);
+        case 1: return launch_direct_t<FILL, MINB, 1>(st, a, sm_count, smem, threads);
+        default: return launch_direct_t<FILL, MINB, 2>(st, a, sm_count, smem, threads);
+    }
 }
 
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks) {
@@ -303,8 +329,8 @@ cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, 
     const int threads = a.n_warps * 32;
     ++g_direct_launches;
     if (min_blocks <= 2)
-        return fill ? launch_direct_t<true, 2>(st, a, sm_count, smem, threads)
-                    : launch_direct_t<false, 2>(st, a, sm_count, smem, threads);
-    return fill ? launch_direct_t<true, 3>(st, a, sm_count, smem, threads)
-                : launch_direct_t<false, 3>(st, a, sm_count, smem, threads);
+        return fill ? launch_direct_e<true, 2>(st, a, sm_count, smem, threads)
+                    : launch_direct_e<false, 2>(st, a, sm_count, smem, threads);
+    return fill ? launch_direct_e<true, 3>(st, a, sm_count, smem, threads)
+                : launch_direct_e<false, 3>(st, a, sm_count, smem, threads);
 }

@@ -27,7 +27,7 @@ struct DgStats {
 struct DgRbfEpi {
     float dr;      // bin spacing
     float coef;    // -0.5 / sigma^2 * log2(e)
-    float norm;    // 1 / (sigma * sqrt(2 pi))
+    float lognorm; // log2(1 / (sigma * sqrt(2 pi)))
     float inv_k4;  // 1 / (K/4)
     int K4;        // K / 4
     float4* out;   // E x K fp32 row-major
@@ -114,6 +114,8 @@ struct DgDirectArgs {
     int near_lo_hi, near_hi_hi;  // high words of (r_c -+ 2e-6)^2
     int max_neighbors;           // clamped to INT_MAX
     int row_cap, n_buckets, n_warps;
+    int eps_mode;                // self-exclusion rule: 0 none (eps <= 0), 1 fast (0 < eps <= DG_EPS_FAST), 2 generic
+    double near_d2_lo, near_d2_hi;  // |sqrt(d2) - r_c| <= 1e-6  <=>  near_d2_lo <= d2 <= near_d2_hi
     int* deg_capped;             // [N] (count pass)
     const long long* row_ptr;    // [N+1] (fill pass)
     int* dst;
@@ -122,8 +124,10 @@ struct DgDirectArgs {
     DgStats* stats;
     DgRbfEpi rbf;
 };
+#define DG_EPS_FAST 1.0e-3
+// eps_fast > 0: the traversal will use the fast self-exclusion (eps_mode 1); cells thinner than 2 eps are rejected
 void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
-                          double r_cutoff, int direct_max_atoms, DgSmall* small, DgStats* stats);
+                          double r_cutoff, int direct_max_atoms, double eps_fast, DgSmall* small, DgStats* stats);
 void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
                            const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
                            double* fa, double* fb, double* fc, DgStats* stats);

@@ -11,7 +11,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <cmath>
+
 #include "dgnn_internal.h"
+#include "rbf_math.cuh"
 
 static int g_rbf_launches = 0;
 int dg_rbf_launch_count_reset() {
@@ -23,16 +26,8 @@ int dg_rbf_launch_count_reset() {
 #define RBF_THREADS 256
 #define RBF_TILE_EDGES 512  // edges per tile: 512 * K/4 float4 per tile (5120 at K = 40 -> 20 per thread)
 
-struct RbfParams {
-    float dr;      // bin spacing
-    float coef;    // -0.5 / sigma^2 * log2(e)
-    float norm;    // 1 / (sigma * sqrt(2 pi))
-    float inv_k4;  // 1 / (K/4)
-    int K4;        // K / 4
-};
-
 __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_vec4(const double* __restrict__ dist, long long n_edges,
-                                                              float4* __restrict__ out, RbfParams P) {
+                                                              float4* __restrict__ out, DgRbfEpi P) {
     __shared__ float s_d[RBF_TILE_EDGES];
     const long long n_tiles = (n_edges + RBF_TILE_EDGES - 1) / RBF_TILE_EDGES;
     for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -47,62 +42,39 @@ __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_vec4(const double* __re
         for (int q = threadIdx.x; q < nq; q += RBF_THREADS) {
             const int e = (int)(((float)q + 0.5f) * P.inv_k4);  // q / K4, exact for q < 2^22
             const int k = (q - e * P.K4) << 2;
-            const float d = s_d[e];
-            const float c0 = (float)k * P.dr;
-            const float x0 = c0 - d;
-            const float x1 = (c0 + P.dr) - d;
-            const float x2 = (c0 + 2.0f * P.dr) - d;
-            const float x3 = (c0 + 3.0f * P.dr) - d;
-            float4 v;
-            v.x = P.norm * exp2f(P.coef * x0 * x0);
-            v.y = P.norm * exp2f(P.coef * x1 * x1);
-            v.z = P.norm * exp2f(P.coef * x2 * x2);
-            v.w = P.norm * exp2f(P.coef * x3 * x3);
-            __stcs(o + q, v);
+            __stcs(o + q, dg_rbf4(s_d[e], k, P));
         }
     }
 }
 
 // general K (not a multiple of 4): scalar stores, still flat-indexed and coalesced
 __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_scalar(const double* __restrict__ dist, long long n_edges,
-                                                                int K, float* __restrict__ out, RbfParams P) {
+                                                                int K, float* __restrict__ out, DgRbfEpi P) {
     const long long total = n_edges * K;
     const long long stride = (long long)gridDim.x * blockDim.x;
     for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < total; q += stride) {
         const long long e = q / K;
         const int k = (int)(q - e * K);
-        const float x = (float)k * P.dr - (float)dist[e];
-        out[q] = P.norm * exp2f(P.coef * x * x);
+        out[q] = dg_rbf1((float)dist[e], k, P);
     }
 }
 
-static RbfParams make_params(int K, double r_cutoff, double dr) {
-    RbfParams P;
+DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out) {
+    DgRbfEpi P;
     const double sigma = r_cutoff / 3.0;
     P.dr = (float)dr;
     P.coef = (float)(-0.5 / (sigma * sigma) * 1.4426950408889634074);
-    P.norm = (float)(1.0 / (sigma * 2.5066282746310005024));
+    P.lognorm = (float)std::log2(1.0 / (sigma * 2.5066282746310005024));
     P.K4 = K / 4;
     P.inv_k4 = P.K4 > 0 ? 1.0f / (float)P.K4 : 0.0f;
+    P.out = reinterpret_cast<float4*>(out);
     return P;
-}
-
-DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out) {
-    const RbfParams P = make_params(K, r_cutoff, dr);
-    DgRbfEpi e;
-    e.dr = P.dr;
-    e.coef = P.coef;
-    e.norm = P.norm;
-    e.inv_k4 = P.inv_k4;
-    e.K4 = P.K4;
-    e.out = reinterpret_cast<float4*>(out);
-    return e;
 }
 
 void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff, double dr,
                        float* out, int sm_count) {
     if (n_edges <= 0 || K <= 0) return;
-    const RbfParams P = make_params(K, r_cutoff, dr);
+    const DgRbfEpi P = dg_make_rbf_epi(K, r_cutoff, dr, out);
     if (sm_count <= 0) sm_count = 148;
     if ((K & 3) == 0 && (long long)RBF_TILE_EDGES * (K / 4) < (1 << 22) && ((uintptr_t)out & 15) == 0) {
         const long long n_tiles = (n_edges + RBF_TILE_EDGES - 1) / RBF_TILE_EDGES;

@@ -11,6 +11,7 @@
 #include <stdint.h>
 
 #include "dgnn_internal.h"
+#include "rbf_math.cuh"
 
 #ifndef FULL_MASK
 #define FULL_MASK 0xffffffffu
@@ -133,22 +134,18 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
     if (rbf.K4 > 0) {
         float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
         const int nq = keep * rbf.K4;
+        // (edge, bin group) of float4 q = lane, lane + 32, ... walked incrementally: no division in the loop
+        const int de = 32 / rbf.K4, dk = 32 - de * rbf.K4;
+        int e = lane / rbf.K4, k4 = lane - e * rbf.K4;
 #pragma unroll 4
         for (int q = lane; q < nq; q += 32) {
-            const int e = (int)(((float)q + 0.5f) * rbf.inv_k4);  // q / K4, exact for q < 2^22
-            const int k = (q - e * rbf.K4) << 2;
-            const float d = sm.fd[e];
-            const float c0 = (float)k * rbf.dr;
-            const float x0 = c0 - d;
-            const float x1 = (c0 + rbf.dr) - d;
-            const float x2 = (c0 + 2.0f * rbf.dr) - d;
-            const float x3 = (c0 + 3.0f * rbf.dr) - d;
-            float4 v;
-            v.x = rbf.norm * exp2f(rbf.coef * x0 * x0);
-            v.y = rbf.norm * exp2f(rbf.coef * x1 * x1);
-            v.z = rbf.norm * exp2f(rbf.coef * x2 * x2);
-            v.w = rbf.norm * exp2f(rbf.coef * x3 * x3);
-            __stcs(o4 + q, v);
+            __stcs(o4 + q, dg_rbf4(sm.fd[e], k4 << 2, rbf));
+            k4 += dk;
+            e += de;
+            if (k4 >= rbf.K4) {
+                k4 -= rbf.K4;
+                ++e;
+            }
         }
         __syncwarp();
     }

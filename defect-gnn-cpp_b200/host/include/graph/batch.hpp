@@ -1,0 +1,72 @@
+// graph/batch.hpp -- NEW surface (not in the reference, which builds one Structure per constructor call): the batched
+// entry point the B200 path is designed around.  Structures are repacked once into SoA coordinate / lattice buffers
+// (pinned host memory), one dgnn_build call constructs every graph of the batch on the device, and the result is a
+// view of device-resident CSR + fp32 feature buffers; only counts / offsets come back to the host unless asked.
+#pragma once
+
+#include "crystal/structure.hpp"
+
+#include <cstddef>
+#include <cstdint>
+#include <memory>
+#include <vector>
+
+namespace defect_gnn::graph {
+
+struct BatchParams {
+    double r_cutoff = 10.0;         // NeighborList default (neighbor_list.hpp:20)
+    size_t max_neighbors = 20;      // NeighborList default; SIZE_MAX = uncapped (betti_features.cpp:107)
+    double epsilon = 1e-10;
+    double rbf_r_cutoff = 10.0;     // CrystalGraph default (crystal_graph.hpp:18)
+    double dr = 0.1;                // CrystalGraph default; <= 0: no features
+    int device = 0;
+};
+
+// SoA repack of crystal::Structure objects (include/crystal/structure.hpp:12-38): Cartesian positions exactly as
+// stored (never wrapped), lattice rows a, b, c.
+struct SoABatch {
+    std::vector<int64_t> atom_offsets;  // [S+1]
+    std::vector<double> x, y, z;        // [N]
+    std::vector<double> lattice;        // [9 S] row-major
+    void add(const crystal::Structure& s);
+    [[nodiscard]] int64_t n_structs() const { return (int64_t)atom_offsets.size() - 1; }
+    [[nodiscard]] int64_t n_atoms() const { return atom_offsets.empty() ? 0 : atom_offsets.back(); }
+    SoABatch() : atom_offsets{0} {}
+};
+
+// Device-resident result of one batched build.  Pointers are DEVICE pointers owned by the builder; they stay valid
+// until the next build() on the same builder or its destruction.
+struct BatchedGraphs {
+    int64_t n_structs = 0, n_atoms = 0, n_edges = 0;
+    int32_t K = 0, max_degree = 0;
+    const int64_t* row_ptr = nullptr;              // [N+1] CSR by global source atom
+    const int32_t* dst = nullptr;                  // [E] neighbour atom, local to its structure
+    const int32_t* image = nullptr;                // [E] int8 n_a | n_b << 8 | n_c << 16
+    const double* dist = nullptr;                  // [E]
+    const float* rbf = nullptr;                    // [E*K] row-major fp32
+    const int64_t* struct_edge_offsets = nullptr;  // [S+1]
+    int64_t n_near_cutoff = 0, n_tie_rows = 0;
+    std::vector<int64_t> host_struct_edge_offsets;  // copied back: the only D2H of the hot path
+};
+
+class BatchBuilder {
+public:
+    explicit BatchBuilder(int device = 0);
+    ~BatchBuilder();
+    BatchBuilder(const BatchBuilder&) = delete;
+    BatchBuilder& operator=(const BatchBuilder&) = delete;
+
+    // Throws std::runtime_error with the C-ABI error text on failure; there is no CPU fallback.
+    BatchedGraphs build(const SoABatch& batch, const BatchParams& params);
+    BatchedGraphs build(const std::vector<const crystal::Structure*>& structures, const BatchParams& params);
+
+    // Host copies of the last result (any pointer may be null).
+    void copy_edges_to_host(const BatchedGraphs& g, int64_t* row_ptr, int32_t* dst, int32_t* image, double* dist,
+                            float* rbf) const;
+
+private:
+    struct Impl;
+    std::unique_ptr<Impl> impl_;
+};
+
+}  // namespace defect_gnn::graph

@@ -1,0 +1,102 @@
+// graph::BatchBuilder -- batched, device-resident graph construction (new surface, see graph/batch.hpp).
+#include "graph/batch.hpp"
+
+#include "context.hpp"
+
+#include <limits>
+#include <stdexcept>
+
+namespace defect_gnn::graph {
+
+void SoABatch::add(const crystal::Structure& s) {
+    for (const crystal::Atom& a : s.atoms()) {
+        x.push_back(a.position[0]);
+        y.push_back(a.position[1]);
+        z.push_back(a.position[2]);
+    }
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) lattice.push_back(s.lattice()(r, c));
+    atom_offsets.push_back(atom_offsets.back() + static_cast<int64_t>(s.num_atoms()));
+}
+
+struct BatchBuilder::Impl {
+    dgnn_ctx* ctx = nullptr;
+};
+
+BatchBuilder::BatchBuilder(int device) : impl_(new Impl) {
+    const int rc = dgnn_create(device, 0, &impl_->ctx);
+    if (rc != DGNN_OK)
+        throw std::runtime_error(std::string("BatchBuilder: cannot create the B200 context (") + dgnn_strerror(rc) +
+                                 "); this build has no CPU fallback");
+}
+
+BatchBuilder::~BatchBuilder() {
+    if (impl_ && impl_->ctx) dgnn_destroy(impl_->ctx);
+}
+
+BatchedGraphs BatchBuilder::build(const SoABatch& batch, const BatchParams& p) {
+    dgnn_batch b{};
+    b.n_structs = batch.n_structs();
+    b.atom_offsets = batch.atom_offsets.data();
+    b.x = batch.x.data();
+    b.y = batch.y.data();
+    b.z = batch.z.data();
+    b.lattice = batch.lattice.data();
+    b.r_cutoff = p.r_cutoff;
+    b.max_neighbors = p.max_neighbors >= std::numeric_limits<uint64_t>::max() ? DGNN_UNCAPPED
+                                                                             : static_cast<uint64_t>(p.max_neighbors);
+    b.epsilon = p.epsilon;
+    b.rbf_r_cutoff = p.rbf_r_cutoff;
+    b.dr = p.dr;
+    b.flags = p.dr > 0.0 ? 0u : DGNN_SKIP_RBF;
+    dgnn_graphs g{};
+    int rc = dgnn_build(impl_->ctx, &b, &g);
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::build");
+    BatchedGraphs out;
+    out.n_structs = g.n_structs;
+    out.n_atoms = g.n_atoms;
+    out.n_edges = g.n_edges;
+    out.K = g.K;
+    out.max_degree = g.max_degree;
+    out.row_ptr = g.row_ptr;
+    out.dst = g.dst;
+    out.image = g.image;
+    out.dist = g.dist;
+    out.rbf = g.rbf;
+    out.struct_edge_offsets = g.struct_edge_offsets;
+    out.n_near_cutoff = g.n_near_cutoff;
+    out.n_tie_rows = g.n_tie_rows;
+    out.host_struct_edge_offsets.resize(static_cast<size_t>(g.n_structs) + 1);
+    rc = dgnn_copy_to_host(impl_->ctx, &g, nullptr, nullptr, nullptr, nullptr, nullptr,
+                           out.host_struct_edge_offsets.data());
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::build");
+    return out;
+}
+
+BatchedGraphs BatchBuilder::build(const std::vector<const crystal::Structure*>& structures, const BatchParams& p) {
+    SoABatch b;
+    for (const crystal::Structure* s : structures) {
+        if (!s) throw std::invalid_argument("BatchBuilder::build: null structure");
+        b.add(*s);
+    }
+    return build(b, p);
+}
+
+void BatchBuilder::copy_edges_to_host(const BatchedGraphs& g, int64_t* row_ptr, int32_t* dst, int32_t* image,
+                                      double* dist, float* rbf) const {
+    dgnn_graphs v{};
+    v.n_structs = g.n_structs;
+    v.n_atoms = g.n_atoms;
+    v.n_edges = g.n_edges;
+    v.K = g.K;
+    v.row_ptr = g.row_ptr;
+    v.dst = g.dst;
+    v.image = g.image;
+    v.dist = g.dist;
+    v.rbf = g.rbf;
+    v.struct_edge_offsets = g.struct_edge_offsets;
+    const int rc = dgnn_copy_to_host(impl_->ctx, &v, row_ptr, dst, image, dist, rbf, nullptr);
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::copy_edges_to_host");
+}
+
+}  // namespace defect_gnn::graph

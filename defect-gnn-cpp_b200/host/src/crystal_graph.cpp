@@ -1,0 +1,58 @@
+// graph::CrystalGraph on the B200 path (reference: src/graph/crystal_graph.cpp:9-75).
+#include "graph/crystal_graph.hpp"
+
+#include "context.hpp"
+
+#include <cmath>
+#include <vector>
+
+namespace defect_gnn::graph {
+
+CrystalGraph::CrystalGraph(const crystal::Structure& structure, const NeighborList& neighbors,
+                           const std::map<int, Eigen::VectorXd>& atom_embeddings, int atom_embedding_dims,
+                           double r_cutoff, double dr) {
+    const int num_atoms = static_cast<int>(structure.num_atoms());
+
+    // node part (crystal_graph.cpp:15-21): row i = embedding of atoms[i].element; map::at throws std::out_of_range
+    node_features_.resize(num_atoms, atom_embedding_dims);
+    for (int i = 0; i < num_atoms; ++i) {
+        const Eigen::VectorXd& emb = atom_embeddings.at(structure.atoms()[static_cast<size_t>(i)].element);
+        for (int d = 0; d < atom_embedding_dims; ++d) node_features_(i, d) = emb[d];
+    }
+
+    // edge part (crystal_graph.cpp:23-40): COO edge_index in CSR-by-source order, all distances in one buffer
+    int edge_count = 0;
+    for (int i = 0; i < num_atoms; ++i) edge_count += static_cast<int>(neighbors.neighbors(static_cast<size_t>(i)).size());
+    edge_index_.resize(2, edge_count);
+    std::vector<double> dist(static_cast<size_t>(edge_count));
+    int e = 0;
+    for (int i = 0; i < num_atoms; ++i)
+        for (const Neighbor& nb : neighbors.neighbors(static_cast<size_t>(i))) {
+            edge_index_(0, e) = i;
+            edge_index_(1, e) = static_cast<int>(nb.idx);
+            dist[static_cast<size_t>(e)] = nb.distance;
+            ++e;
+        }
+    const int n_rbf = static_cast<int>(std::floor(r_cutoff / dr));
+    edge_attr_.resize(edge_count, n_rbf > 0 ? n_rbf : 0);
+    if (edge_count > 0 && n_rbf > 0) {
+        // one fp64 launch writes the reference's own storage: column-major E x K doubles
+        detail::DeviceCtx& dc = detail::device_ctx(0);
+        std::lock_guard<std::mutex> lock(dc.mu);
+        int32_t k = 0;
+        const int rc = dgnn_rbf_expand_f64(dc.ctx, dist.data(), edge_count, r_cutoff, dr, edge_attr_.data(), &k);
+        if (rc != DGNN_OK) detail::throw_status(dc.ctx, rc, "CrystalGraph");
+    }
+    target_ = 0;
+}
+
+const Eigen::MatrixXd& CrystalGraph::node_features() const { return node_features_; }
+const Eigen::MatrixXi& CrystalGraph::edge_index() const { return edge_index_; }
+const Eigen::MatrixXd& CrystalGraph::edge_attr() const { return edge_attr_; }
+double CrystalGraph::target() const { return target_; }
+void CrystalGraph::set_target(double y) { target_ = y; }
+void CrystalGraph::add_topo_features(const Eigen::MatrixXd& /*topo*/) {}
+size_t CrystalGraph::num_nodes() const { return static_cast<size_t>(node_features_.rows()); }
+size_t CrystalGraph::num_edges() const { return static_cast<size_t>(edge_index_.cols()); }
+
+}  // namespace defect_gnn::graph

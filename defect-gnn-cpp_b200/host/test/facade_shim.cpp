@@ -1,0 +1,172 @@
+// facade_shim.cpp -- TEST code: a C-callable window onto the C++ facade (defect_gnn::graph::NeighborList,
+// gaussian_rbf, CrystalGraph, BatchBuilder) so pytest can drive the reference-shaped API through ctypes and compare
+// it with the oracle.  It constructs the objects exactly the way a reference caller would
+// (VASPStructure -> crystal::Structure -> NeighborList -> CrystalGraph, ETL_PIPELINE_PLAN.md MAIN-PIPELINE).
+#include "crystal/structure.hpp"
+#include "graph/batch.hpp"
+#include "graph/crystal_graph.hpp"
+#include "graph/edge_features.hpp"
+#include "graph/neighbor_list.hpp"
+
+#include <cstring>
+#include <exception>
+#include <limits>
+#include <map>
+#include <stdexcept>
+#include <string>
+
+using namespace defect_gnn;
+
+namespace {
+thread_local std::string g_err;
+
+io::VASPStructure make_vasp(int64_t n, const double* frac, const double* lattice, const int* types) {
+    io::VASPStructure v;
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) v.lattice(r, c) = lattice[3 * r + c];
+    v.frac_coords.resize(n, 3);
+    int max_type = -1;
+    for (int64_t i = 0; i < n; ++i) {
+        for (int k = 0; k < 3; ++k) v.frac_coords(i, k) = frac[3 * i + k];
+        v.atom_types.push_back(types ? types[i] : 0);
+        if (v.atom_types.back() > max_type) max_type = v.atom_types.back();
+    }
+    v.counts.assign(static_cast<size_t>(max_type + 1), 0);
+    for (int t : v.atom_types) v.counts[static_cast<size_t>(t)]++;
+    v.elements.assign(v.counts.size(), "X");
+    return v;
+}
+
+template <class F>
+int guarded(F&& f) {
+    try {
+        f();
+        return 0;
+    } catch (const std::out_of_range& e) {
+        g_err = e.what();
+        return -20;
+    } catch (const std::invalid_argument& e) {
+        g_err = e.what();
+        return -21;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return -22;
+    }
+}
+}  // namespace
+
+extern "C" {
+
+const char* facade_last_error() { return g_err.c_str(); }
+
+// Cartesian positions as crystal::Structure computes them (for feeding the oracle the identical inputs).
+int facade_positions(int64_t n, const double* frac, const double* lattice, double* xyz /* n*3 */) {
+    return guarded([&] {
+        crystal::Structure s(make_vasp(n, frac, lattice, nullptr));
+        for (int64_t i = 0; i < n; ++i)
+            for (int k = 0; k < 3; ++k) xyz[3 * i + k] = s.atoms()[static_cast<size_t>(i)].position[k];
+    });
+}
+
+int facade_neighbor_list(int64_t n, const double* frac, const double* lattice, double r_cutoff, uint64_t max_neighbors,
+                         double epsilon, int use_defaults, int64_t edge_cap, int64_t* row_ptr, int32_t* dst,
+                         double* dist, double* disp, int8_t* image, int64_t* n_edges, int64_t* near, int64_t* ties) {
+    return guarded([&] {
+        crystal::Structure s(make_vasp(n, frac, lattice, nullptr));
+        const size_t cap = max_neighbors == std::numeric_limits<uint64_t>::max() ? std::numeric_limits<size_t>::max()
+                                                                                  : static_cast<size_t>(max_neighbors);
+        graph::NeighborList nl = use_defaults ? graph::NeighborList(s) : graph::NeighborList(s, r_cutoff, cap, epsilon);
+        int64_t e = 0;
+        for (int64_t i = 0; i < n; ++i) {
+            row_ptr[i] = e;
+            const auto& row = nl.neighbors(static_cast<size_t>(i));
+            const auto& img = nl.images(static_cast<size_t>(i));
+            for (size_t q = 0; q < row.size(); ++q, ++e) {
+                if (e >= edge_cap) throw std::runtime_error("edge_cap too small");
+                dst[e] = static_cast<int32_t>(row[q].idx);
+                dist[e] = row[q].distance;
+                for (int k = 0; k < 3; ++k) {
+                    disp[3 * e + k] = row[q].displacement[k];
+                    image[3 * e + k] = img[q][static_cast<size_t>(k)];
+                }
+            }
+        }
+        row_ptr[n] = e;
+        *n_edges = e;
+        *near = nl.near_cutoff_pairs();
+        *ties = nl.tie_rows();
+        if (static_cast<size_t>(e) != nl.num_edges()) throw std::runtime_error("num_edges mismatch");
+    });
+}
+
+// emb_keys: which species indices get an embedding (value = key + 0.25 * dim); a missing key must throw out_of_range.
+int facade_crystal_graph(int64_t n, const double* frac, const double* lattice, const int* types, double nl_cutoff,
+                         uint64_t max_neighbors, double rbf_cutoff, double dr, int emb_dims, int n_emb_keys,
+                         const int* emb_keys, int64_t edge_cap, int32_t* edge_index /* 2*E col-major */,
+                         double* edge_attr /* E*K col-major */, double* node_features /* N*dims col-major */,
+                         int64_t* n_edges, int32_t* K, int64_t* n_nodes) {
+    return guarded([&] {
+        crystal::Structure s(make_vasp(n, frac, lattice, types));
+        const size_t cap = max_neighbors == std::numeric_limits<uint64_t>::max() ? std::numeric_limits<size_t>::max()
+                                                                                  : static_cast<size_t>(max_neighbors);
+        graph::NeighborList nl(s, nl_cutoff, cap);
+        std::map<int, Eigen::VectorXd> emb;
+        for (int q = 0; q < n_emb_keys; ++q) {
+            Eigen::VectorXd v;
+            v.resize(emb_dims);
+            for (int d = 0; d < emb_dims; ++d) v[d] = emb_keys[q] + 0.25 * d;
+            emb[emb_keys[q]] = v;
+        }
+        graph::CrystalGraph g(s, nl, emb, emb_dims, rbf_cutoff, dr);
+        const auto E = static_cast<int64_t>(g.num_edges());
+        if (E > edge_cap) throw std::runtime_error("edge_cap too small");
+        *n_edges = E;
+        *K = static_cast<int32_t>(g.edge_attr().cols());
+        *n_nodes = static_cast<int64_t>(g.num_nodes());
+        std::memcpy(edge_index, g.edge_index().data(), sizeof(int) * 2 * static_cast<size_t>(E));
+        std::memcpy(edge_attr, g.edge_attr().data(), sizeof(double) * static_cast<size_t>(E) * static_cast<size_t>(*K));
+        std::memcpy(node_features, g.node_features().data(),
+                    sizeof(double) * static_cast<size_t>(n) * static_cast<size_t>(emb_dims));
+        if (g.target() != 0.0) throw std::runtime_error("target must start at 0");
+        g.set_target(1.5);
+        if (g.target() != 1.5) throw std::runtime_error("set_target");
+    });
+}
+
+int facade_gaussian_rbf(double d, double r_cutoff, double dr, double* out, int32_t* K) {
+    return guarded([&] {
+        Eigen::VectorXd v = graph::gaussian_rbf(d, r_cutoff, dr);
+        *K = static_cast<int32_t>(v.size());
+        for (int i = 0; i < *K; ++i) out[i] = v[i];
+    });
+}
+
+// Batched surface: S structures given as concatenated frac coords; returns per-structure edge offsets and host copies.
+int facade_build_batch(int64_t n_structs, const int64_t* atom_offsets, const double* frac, const double* lattices,
+                       double r_cutoff, uint64_t max_neighbors, double rbf_cutoff, double dr, int64_t edge_cap,
+                       int64_t* struct_edge_offsets, int64_t* row_ptr, int32_t* dst, int32_t* image, double* dist,
+                       float* rbf, int64_t* n_edges, int32_t* K) {
+    return guarded([&] {
+        std::vector<crystal::Structure> structs;
+        for (int64_t s = 0; s < n_structs; ++s)
+            structs.emplace_back(make_vasp(atom_offsets[s + 1] - atom_offsets[s], frac + 3 * atom_offsets[s],
+                                           lattices + 9 * s, nullptr));
+        std::vector<const crystal::Structure*> ptrs;
+        for (const auto& st : structs) ptrs.push_back(&st);
+        graph::BatchParams p;
+        p.r_cutoff = r_cutoff;
+        p.max_neighbors = max_neighbors == std::numeric_limits<uint64_t>::max() ? std::numeric_limits<size_t>::max()
+                                                                                 : static_cast<size_t>(max_neighbors);
+        p.rbf_r_cutoff = rbf_cutoff;
+        p.dr = dr;
+        graph::BatchBuilder bb(0);
+        graph::BatchedGraphs g = bb.build(ptrs, p);
+        if (g.n_edges > edge_cap) throw std::runtime_error("edge_cap too small");
+        *n_edges = g.n_edges;
+        *K = g.K;
+        for (int64_t s = 0; s <= n_structs; ++s) struct_edge_offsets[s] = g.host_struct_edge_offsets[static_cast<size_t>(s)];
+        bb.copy_edges_to_host(g, row_ptr, dst, image, dist, g.K > 0 ? rbf : nullptr);
+    });
+}
+
+}  // extern "C"

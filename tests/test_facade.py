@@ -1,0 +1,204 @@
+"""The C++ facade that keeps the reference's graph-layer class API (defect-gnn-cpp_b200/host/): NeighborList,
+gaussian_rbf, CrystalGraph (drop-in signatures, include/graph/*.hpp of the reference) and the new BatchBuilder.
+pytest drives it through the C-callable test shim host/test/facade_shim.cpp, which builds the objects the way a
+reference caller does (VASPStructure -> crystal::Structure -> NeighborList -> CrystalGraph)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "defect-gnn-cpp_b200")
+UNC = 2**64 - 1
+
+
+@pytest.fixture(scope="session")
+def facade(pkg):
+    pkg.build_library()
+    pkg.build_host_facade()
+    F = C.CDLL(os.path.join(PKG, "libdgnn_facade_test.so"))
+    dp, i64p, i32p = C.POINTER(C.c_double), C.POINTER(C.c_int64), C.POINTER(C.c_int32)
+    F.facade_last_error.restype = C.c_char_p
+    F.facade_positions.argtypes = [C.c_int64, dp, dp, dp]
+    F.facade_neighbor_list.argtypes = [C.c_int64, dp, dp, C.c_double, C.c_uint64, C.c_double, C.c_int, C.c_int64, i64p,
+                                       i32p, dp, dp, C.POINTER(C.c_int8), i64p, i64p, i64p]
+    F.facade_crystal_graph.argtypes = [C.c_int64, dp, dp, i32p, C.c_double, C.c_uint64, C.c_double, C.c_double, C.c_int,
+                                       C.c_int, i32p, C.c_int64, i32p, dp, dp, i64p, i32p, i64p]
+    F.facade_gaussian_rbf.argtypes = [C.c_double, C.c_double, C.c_double, dp, i32p]
+    F.facade_build_batch.argtypes = [C.c_int64, i64p, dp, dp, C.c_double, C.c_uint64, C.c_double, C.c_double, C.c_int64,
+                                     i64p, i64p, i32p, i32p, dp, C.POINTER(C.c_float), i64p, i32p]
+    return F
+
+
+def _p(a, t):
+    return a.ctypes.data_as(C.POINTER(t))
+
+
+def positions(F, frac, L):
+    n = len(frac)
+    xyz = np.zeros((n, 3))
+    assert F.facade_positions(n, _p(frac, C.c_double), _p(L, C.c_double), _p(xyz, C.c_double)) == 0
+    return xyz
+
+
+def neighbor_list(F, frac, L, rc=10.0, cap=20, eps=1e-10, defaults=False, ecap=200_000):
+    n = len(frac)
+    rp = np.zeros(n + 1, np.int64)
+    dst = np.zeros(ecap, np.int32)
+    dist = np.zeros(ecap)
+    disp = np.zeros((ecap, 3))
+    img = np.zeros((ecap, 3), np.int8)
+    ne, near, ties = C.c_int64(), C.c_int64(), C.c_int64()
+    rc_ = F.facade_neighbor_list(n, _p(frac, C.c_double), _p(L, C.c_double), rc, C.c_uint64(cap), eps, int(defaults),
+                                 ecap, _p(rp, C.c_int64), _p(dst, C.c_int32), _p(dist, C.c_double),
+                                 _p(disp, C.c_double), _p(img, C.c_int8), C.byref(ne), C.byref(near), C.byref(ties))
+    return rc_, rp, dst[:ne.value], dist[:ne.value], disp[:ne.value], img[:ne.value], near.value, ties.value
+
+
+# ---- CPU: builds, exports the reference's symbols, input types behave, no silent fallback -----------------------------
+def test_facade_exports_reference_api(facade):
+    out = subprocess.run(["nm", "-DC", os.path.join(PKG, "libdefect_gnn_graph.so")], capture_output=True, text=True).stdout
+    for sym in ("defect_gnn::graph::NeighborList::NeighborList(defect_gnn::crystal::Structure const&, double, unsigned long, double)",
+                "defect_gnn::graph::NeighborList::neighbors(unsigned long) const",
+                "defect_gnn::graph::gaussian_rbf(double, double, double)",
+                "defect_gnn::graph::CrystalGraph::CrystalGraph(",
+                "defect_gnn::graph::CrystalGraph::edge_index() const",
+                "defect_gnn::graph::CrystalGraph::edge_attr() const",
+                "defect_gnn::graph::CrystalGraph::node_features() const",
+                "defect_gnn::graph::CrystalGraph::add_topo_features(",
+                "defect_gnn::graph::BatchBuilder::build(",
+                "defect_gnn::crystal::Structure::Structure(defect_gnn::io::VASPStructure const&)",
+                "defect_gnn::io::parse_vasp("):
+        assert sym in out, sym
+
+
+def test_structure_positions_match_oracle(facade, oracle, c1_structures):
+    for nm, (x, y, z, L, _, frac) in c1_structures.items():
+        xyz = positions(facade, np.ascontiguousarray(frac), np.ascontiguousarray(L))
+        ox, oy, oz = oracle.frac_to_cart(frac, L)
+        assert np.array_equal(xyz[:, 0], ox) and np.array_equal(xyz[:, 1], oy) and np.array_equal(xyz[:, 2], oz), nm
+        assert np.array_equal(xyz[:, 0], x)
+
+
+def test_facade_fails_loudly_without_gpu(facade, c1_structures):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    _, _, _, L, _, frac = next(iter(c1_structures.values()))
+    rc_, *_ = neighbor_list(facade, np.ascontiguousarray(frac), np.ascontiguousarray(L))
+    assert rc_ == -22 and b"no CPU fallback" in facade.facade_last_error()
+
+
+def test_poscar_parser_roundtrip(tmp_path, facade, c1_structures):
+    """io::parse_vasp + main_pipeline exist and parse a POSCAR written from a fixture (CPU part: up to the GPU call)."""
+    nm, (x, y, z, L, species, frac) = next(iter(c1_structures.items()))
+    path = tmp_path / "t.vasp"
+    counts = np.bincount(species)
+    with open(path, "w") as f:
+        f.write("fixture\n1.0\n")
+        for r in L:
+            f.write(" ".join(repr(float(v)) for v in r) + "\n")
+        f.write(" ".join(f"E{i}" for i in range(len(counts))) + "\n" + " ".join(str(int(c)) for c in counts) + "\nDirect\n")
+        for p in frac:
+            f.write(" ".join(repr(float(v)) for v in p) + "\n")
+    r = subprocess.run([os.path.join(PKG, "main_pipeline"), str(path)], capture_output=True, text=True)
+    import torch
+    if torch.cuda.is_available():
+        assert r.returncode == 0 and f"{len(frac)} atoms, {20 * len(frac)} edges, edge_attr {20 * len(frac)} x 100" in r.stdout
+    else:
+        assert r.returncode == 1 and "no CPU fallback" in r.stderr
+
+
+# ---- GPU: reference-shaped API against the oracle -------------------------------------------------------------------
+@pytest.mark.gpu
+def test_neighbor_list_facade_vs_oracle(facade, oracle, c1_structures):
+    for nm, (x, y, z, L, _, frac) in list(c1_structures.items())[:4]:
+        frac, L = np.ascontiguousarray(frac), np.ascontiguousarray(L)
+        for rc, cap, defaults in ((10.0, 20, True), (5.0, 12, False), (8.0, UNC, False)):
+            rc_, rp, dst, dist, disp, img, near, ties = neighbor_list(facade, frac, L, rc, cap, defaults=defaults)
+            assert rc_ == 0, facade.facade_last_error()
+            o = oracle.neighbor_list(x, y, z, L, rc, cap, 1e-10, oracle.ALGO_CELLLIST)
+            assert np.array_equal(rp, o.row_ptr) and np.array_equal(dst, o.dst)
+            assert np.array_equal(dist.view(np.int64), o.dist.view(np.int64))
+            assert np.array_equal(img, o.image[:, :3])
+            assert np.array_equal(disp.view(np.int64), o.disp.view(np.int64)), "displacement must be bit-identical"
+            assert near == o.n_near_cutoff and ties == o.n_tie_rows
+
+
+@pytest.mark.gpu
+def test_crystal_graph_facade_vs_oracle(facade, oracle, c1_structures):
+    nm, (x, y, z, L, species, frac) = next(iter(c1_structures.items()))
+    frac, L = np.ascontiguousarray(frac), np.ascontiguousarray(L)
+    types = np.ascontiguousarray(species, dtype=np.int32)
+    n, dims, ecap = len(frac), 92, 20 * len(frac)
+    keys = np.unique(types).astype(np.int32)
+    ei = np.zeros(2 * ecap, np.int32)
+    ea = np.zeros(ecap * 100)
+    nf = np.zeros(n * dims)
+    ne, K, nn = C.c_int64(), C.c_int32(), C.c_int64()
+    rc_ = facade.facade_crystal_graph(n, _p(frac, C.c_double), _p(L, C.c_double), _p(types, C.c_int32), 10.0,
+                                      C.c_uint64(20), 10.0, 0.1, dims, len(keys), _p(keys, C.c_int32), ecap,
+                                      _p(ei, C.c_int32), _p(ea, C.c_double), _p(nf, C.c_double), C.byref(ne),
+                                      C.byref(K), C.byref(nn))
+    assert rc_ == 0, facade.facade_last_error()
+    E = ne.value
+    assert E == 20 * n and K.value == 100 and nn.value == n
+    o = oracle.neighbor_list(x, y, z, L, 10.0, 20, 1e-10, oracle.ALGO_CELLLIST)
+    src = np.repeat(np.arange(n), np.diff(o.row_ptr))
+    # Eigen::MatrixXi 2 x E column-major: memory is [src0, dst0, src1, dst1, ...]  (crystal_graph.cpp:35-36)
+    assert np.array_equal(ei[0:2 * E:2], src) and np.array_equal(ei[1:2 * E:2], o.dst)
+    ref = oracle.edge_attr(o.dist, 10.0, 0.1)                       # E x K
+    got = ea[:E * 100].reshape(100, E).T                            # column-major E x K
+    assert np.max(np.abs(got - ref) / ref) <= 1e-12
+    want_nf = (types[:, None] + 0.25 * np.arange(dims)[None, :])    # N x dims, stored column-major
+    assert np.array_equal(nf.reshape(dims, n).T, want_nf)
+    # a missing embedding key throws std::out_of_range like the reference's map::at (crystal_graph.cpp:20)
+    rc_ = facade.facade_crystal_graph(n, _p(frac, C.c_double), _p(L, C.c_double), _p(types, C.c_int32), 10.0,
+                                      C.c_uint64(20), 10.0, 0.1, dims, len(keys) - 1, _p(keys, C.c_int32), ecap,
+                                      _p(ei, C.c_int32), _p(ea, C.c_double), _p(nf, C.c_double), C.byref(ne),
+                                      C.byref(K), C.byref(nn))
+    assert rc_ == -20
+    # gaussian_rbf(distance, r_cutoff, dr) one distance at a time
+    out = np.zeros(128)
+    k = C.c_int32()
+    for d, rc, dr in ((0.0, 10.0, 0.1), (4.0, 8.0, 0.2), (7.999999, 8.0, 0.2)):
+        assert facade.facade_gaussian_rbf(d, rc, dr, _p(out, C.c_double), C.byref(k)) == 0
+        ref = oracle.gaussian_rbf(d, rc, dr)
+        assert k.value == len(ref) and np.max(np.abs(out[:k.value] - ref) / ref) <= 1e-12
+
+
+@pytest.mark.gpu
+def test_batch_builder_facade(facade, oracle, c1_structures):
+    items = list(c1_structures.values())[:3]
+    fr = np.ascontiguousarray(np.concatenate([it[5] for it in items]))
+    Ls = np.ascontiguousarray(np.stack([it[3] for it in items]))
+    offs = np.zeros(len(items) + 1, np.int64)
+    offs[1:] = np.cumsum([len(it[5]) for it in items])
+    ecap = 120_000
+    seo = np.zeros(len(items) + 1, np.int64)
+    rp = np.zeros(int(offs[-1]) + 1, np.int64)
+    dst = np.zeros(ecap, np.int32)
+    img = np.zeros(ecap, np.int32)
+    dist = np.zeros(ecap)
+    rbf = np.zeros((ecap, 40), np.float32)
+    ne, K = C.c_int64(), C.c_int32()
+    rc_ = facade.facade_build_batch(len(items), _p(offs, C.c_int64), _p(fr, C.c_double), _p(Ls, C.c_double), 8.0,
+                                    C.c_uint64(UNC), 8.0, 0.2, ecap, _p(seo, C.c_int64), _p(rp, C.c_int64),
+                                    _p(dst, C.c_int32), _p(img, C.c_int32), _p(dist, C.c_double), _p(rbf, C.c_float),
+                                    C.byref(ne), C.byref(K))
+    assert rc_ == 0, facade.facade_last_error()
+    assert K.value == 40
+    e0 = 0
+    for s, (x, y, z, L, _, frac) in enumerate(items):
+        o = oracle.neighbor_list(x, y, z, L, 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
+        assert seo[s] == e0
+        e1 = e0 + o.n_edges
+        assert np.array_equal(dst[e0:e1], o.dst)
+        assert np.array_equal(dist[e0:e1].view(np.int64), o.dist.view(np.int64))
+        assert np.array_equal(img[e0:e1].view(np.int8).reshape(-1, 4), o.image)
+        ref = oracle.edge_attr(o.dist, 8.0, 0.2)
+        assert np.max(np.abs(rbf[e0:e1] - ref) / ref) <= 1e-5
+        e0 = e1
+    assert seo[-1] == e0 == ne.value
