@@ -407,6 +407,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.r_cutoff = b->r_cutoff;
     D.epsilon = b->epsilon;
     D.inv_rc = (float)(1.0 / b->r_cutoff);
+    D.key_scale = (4294967296.0 - 4096.0) / b->r_cutoff;
     D.near_lo_hi = near_lo_hi;
     D.near_hi_hi = near_hi_hi;
     D.eps_mode = eps_mode;
@@ -508,6 +509,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         A.rcm = DG_RCM(b->r_cutoff);
         A.epsilon = b->epsilon;
         A.inv_rc = (float)(1.0 / b->r_cutoff);
+        A.key_scale = D.key_scale;
         A.near_lo_hi = near_lo_hi;
         A.near_hi_hi = near_hi_hi;
         A.max_neighbors = max_nb;

@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
             } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
                 if (lane == 0) atomicExch(&A.stats->overflow, 1);
             } else {
-                dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.row_ptr[a], A.dst, A.image, A.dist, A.stats,
+                dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image, A.dist, A.stats,
                                  lane, A.rbf);
             }
         }

@@ -51,6 +51,7 @@ struct DgTraverseArgs {
     double rcm;                  // r_c * (1 + margin) for candidate generation
     double epsilon;
     float inv_rc;
+    double key_scale;            // (2^32 - 4096) / r_c: 32-bit sort keys of the row sort
     int near_lo_hi, near_hi_hi;  // high words of (r_c -+ 2e-6)^2
     int max_neighbors;           // clamped to INT_MAX
     // capacities (shared memory carve-up)
@@ -111,6 +112,7 @@ struct DgDirectArgs {
     double r_cutoff;
     double epsilon;
     float inv_rc;
+    double key_scale;            // (2^32 - 4096) / r_c: 32-bit sort keys of the row sort
     int near_lo_hi, near_hi_hi;  // high words of (r_c -+ 2e-6)^2
     int max_neighbors;           // clamped to INT_MAX
     int row_cap, n_buckets, n_warps;

@@ -552,7 +552,7 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
         if (lane == 0) atomicExch(&A.stats->overflow, 1);
         return;
     }
-    dg_row_sort_emit(sm.rb, m, keep, A.n_buckets, A.inv_rc, A.row_ptr[iglob], A.dst, A.image, A.dist, A.stats, lane, A.rbf);
+    dg_row_sort_emit(sm.rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[iglob], A.dst, A.image, A.dist, A.stats, lane, A.rbf);
 }
 
 template <bool FILL>

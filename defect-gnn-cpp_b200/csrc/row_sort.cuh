@@ -3,8 +3,14 @@
 //
 // Replaces the reference's per-row std::sort + resize (src/graph/neighbor_list.cpp:56-62).  Row order is the canonical
 // key (distance, dst, n_a, n_b, n_c) -- the reference's std::sort is unstable, so its tie order is unspecified (SURVEY
-// Appendix A, R8).  The sort is a monotone bucket of the distance (d/r_c)^3 -> histogram -> exclusive scan -> rank
-// inside the bucket; neighbour shells of crystals put ~1 entry in a bucket, so the quadratic in-bucket step is tiny.
+// Appendix A, R8).
+//
+// Sort = counting sort on a monotone bucket of the distance ((d/r_c)^3: equal-volume shells) followed by a rank inside
+// the bucket.  The in-bucket rank compares 32-bit fixed-point keys (d * 2^32 / r_c, resolution 2e-9 A) that were
+// scattered into bucket order, so the inner loop is LDS.32 + two integer compares on contiguous words; only entries
+// whose 32-bit keys collide (exact ties of symmetric crystals, or |delta d| < 2e-9 A) take the exact path that compares
+// the fp64 distances and then (dst, image).  Both the bucket and the key are monotone non-decreasing functions of the
+// fp64 distance, so the result is exactly the canonical order.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -20,12 +26,15 @@
 __host__ __device__ inline size_t dg_align16(size_t v) { return (v + 15) & ~(size_t)15; }
 
 struct RowBuf {
-    double* rd;           // d2 while collecting, distance after the sort prologue
-    int* rj;              // neighbour atom (local index)
-    uint32_t* rn;         // packed image
-    uint32_t* bs;         // bucket | slot << 16
-    unsigned short* ord;  // bucket-ordered entry ids
-    float* fd;            // distances in final row order (fp32), input of the fused RBF epilogue
+    double* rd;           // d2 while collecting, distance after the sort prologue            (by entry)
+    int* rj;              // neighbour atom (local index)                                       (by entry)
+    uint32_t* rn;         // packed image                                                       (by entry)
+    uint32_t* bs;         // bucket | slot << 16                                                (by entry)
+    uint32_t* sk;         // 32-bit distance keys                                               (bucket order)
+    unsigned short* ord;  // entry ids                                                          (bucket order)
+    unsigned short* sb;   // buckets                                                            (bucket order)
+    float* fd;            // keys by entry during the prologue (as uint32); then the distances in final row order
+                          // (fp32), input of the fused RBF epilogue
     int* cnt;             // bucket counters / starts, padded: index(b) = b + b / per  (+ 2 words for the tie check)
 };
 
@@ -33,7 +42,7 @@ struct RowBuf {
 __host__ __device__ inline size_t dg_cnt_words(int n_buckets) { return (size_t)n_buckets + 32 + 4; }
 
 __host__ __device__ inline size_t dg_rowbuf_bytes(int row_cap, int n_buckets) {
-    return dg_align16((size_t)row_cap * 8) + dg_align16((size_t)row_cap * 4) * 4 + dg_align16((size_t)row_cap * 2) +
+    return dg_align16((size_t)row_cap * 8) + dg_align16((size_t)row_cap * 4) * 5 + dg_align16((size_t)row_cap * 2) * 2 +
            dg_align16(dg_cnt_words(n_buckets) * 4);
 }
 
@@ -43,30 +52,91 @@ __device__ __forceinline__ RowBuf dg_rowbuf_carve(unsigned char* p, int row_cap)
     r.rj = (int*)p; p += dg_align16((size_t)row_cap * 4);
     r.rn = (uint32_t*)p; p += dg_align16((size_t)row_cap * 4);
     r.bs = (uint32_t*)p; p += dg_align16((size_t)row_cap * 4);
-    r.ord = (unsigned short*)p; p += dg_align16((size_t)row_cap * 2);
+    r.sk = (uint32_t*)p; p += dg_align16((size_t)row_cap * 4);
     r.fd = (float*)p; p += dg_align16((size_t)row_cap * 4);
+    r.ord = (unsigned short*)p; p += dg_align16((size_t)row_cap * 2);
+    r.sb = (unsigned short*)p; p += dg_align16((size_t)row_cap * 2);
     r.cnt = (int*)p;
     return r;
 }
 
+// canonical tie-break key of an entry: (dst, n_a, n_b, n_c)
+__device__ __forceinline__ unsigned long long dg_tie_key(const RowBuf& sm, int e) {
+    return ((unsigned long long)(uint32_t)sm.rj[e] << 32) | dg_image_sort_key(sm.rn[e]);
+}
+
+// Fused Gaussian RBF epilogue (edge_features.cpp:7-24 applied per edge as crystal_graph.cpp:32-40 does): the row's
+// keep x K fp32 features are one contiguous span of the E x K tensor starting at float4 index o * K4.
+//  - K4 groups fit a warp (G = 32 / K4 edges per step, >= 28 lanes busy): every lane owns one fixed float4 column, so
+//    the bin centres are loop constants and a warp store covers G whole feature rows (G * K * 4 contiguous bytes);
+//  - otherwise flat float4 indexing (every warp store covers 512 contiguous bytes).
+__device__ __forceinline__ void dg_rbf_row(const float* __restrict__ fd, int keep, long long o, int lane,
+                                           const DgRbfEpi& rbf) {
+    float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
+    const int G = 32 / rbf.K4;  // 0 when K4 > 32
+    if (G * rbf.K4 >= 28) {
+        const int es = lane / rbf.K4, k4 = lane - es * rbf.K4;
+        if (es < G) {
+            const float c0 = (float)(4 * k4) * rbf.dr, c1 = (float)(4 * k4 + 1) * rbf.dr;
+            const float c2 = (float)(4 * k4 + 2) * rbf.dr, c3 = (float)(4 * k4 + 3) * rbf.dr;
+            float4* __restrict__ p = o4 + es * rbf.K4 + k4;
+            const int step = G * rbf.K4;
+#pragma unroll 2
+            for (int e = es; e < keep; e += G, p += step) {
+                const float d = fd[e];
+                const float x0 = c0 - d, x1 = c1 - d, x2 = c2 - d, x3 = c3 - d;
+                float4 v;
+                v.x = dg_ex2(fmaf(rbf.coef * x0, x0, rbf.lognorm));
+                v.y = dg_ex2(fmaf(rbf.coef * x1, x1, rbf.lognorm));
+                v.z = dg_ex2(fmaf(rbf.coef * x2, x2, rbf.lognorm));
+                v.w = dg_ex2(fmaf(rbf.coef * x3, x3, rbf.lognorm));
+                __stcs(p, v);
+            }
+        }
+    } else {
+        const int nq = keep * rbf.K4;
+        // (edge, bin group) of float4 q = lane, lane + 32, ... walked incrementally: no division in the loop
+        const int de = 32 / rbf.K4, dk = 32 - de * rbf.K4;
+        int e = lane / rbf.K4, k4 = lane - e * rbf.K4;
+#pragma unroll 4
+        for (int q = lane; q < nq; q += 32) {
+            __stcs(o4 + q, dg_rbf4(fd[e], k4 << 2, rbf));
+            k4 += dk;
+            e += de;
+            if (k4 >= rbf.K4) {
+                k4 -= rbf.K4;
+                ++e;
+            }
+        }
+    }
+}
+
+// d * key_scale rounded to an integer in [0, 2^32): monotone non-decreasing in d (one rounding in the product, one in
+// the magic-number add).  key_scale = (2^32 - 4096) / r_c and d <= r_c (1 + 2^-52), so the value stays below 2^32.
+#define DG_KEY_MAGIC 4503599627370496.0  // 2^52
+__device__ __forceinline__ uint32_t dg_dist_key(double d, double key_scale) {
+    return (uint32_t)__double2loint(__dadd_rn(__dmul_rn(d, key_scale), DG_KEY_MAGIC));
+}
+
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
 // NBk (number of buckets) is a power of two, 32 <= NBk <= 2048.  All 32 lanes must call.
-// rbf.K4 > 0: fused Gaussian RBF epilogue (edge_features.cpp:7-24 applied per edge as crystal_graph.cpp:32-40 does):
-// the row's keep x K fp32 features are one contiguous span of the E x K tensor, written with flat float4 indexing
-// (every warp store covers 512 contiguous bytes) straight from the sorted distances in shared memory.
+// rbf.K4 > 0: fused Gaussian RBF epilogue straight from the sorted distances in shared memory.
 __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
-                                                 long long o, int* __restrict__ dst, uint32_t* __restrict__ image,
-                                                 double* __restrict__ dist, DgStats* __restrict__ stats, int lane,
-                                                 const DgRbfEpi& rbf) {
+                                                 double key_scale, long long o, int* __restrict__ dst,
+                                                 uint32_t* __restrict__ image, double* __restrict__ dist,
+                                                 DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     const int per = NBk >> 5;
     const int lper = 31 - __clz(per);
     const int nwords = NBk + 32 + 1;
+    uint32_t* kk = reinterpret_cast<uint32_t*>(sm.fd);  // keys by entry (dead before fd is written)
     for (int b = lane; b < nwords; b += 32) sm.cnt[b] = 0;
     __syncwarp();
+    // ---- A: distance, key, bucket histogram ----
     const float scale = (float)NBk;
     for (int e = lane; e < m; e += 32) {
         const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
         sm.rd[e] = d;
+        kk[e] = dg_dist_key(d, key_scale);
         const float t = (float)d * inv_rc;
         int b = (int)(t * t * t * scale);
         b = b < 0 ? 0 : (b >= NBk ? NBk - 1 : b);
@@ -74,7 +144,7 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
         sm.bs[e] = (uint32_t)b | ((uint32_t)slot << 16);
     }
     __syncwarp();
-    {   // exclusive scan of the counters in place (lane owns buckets [lane*per, (lane+1)*per)); index(NBk) = m
+    {   // ---- B: exclusive scan of the counters in place (lane owns buckets [lane*per, (lane+1)*per)); index(NBk) = m
         const int base = lane * per + lane;
         int sum = 0;
         for (int i = 0; i < per; ++i) sum += sm.cnt[base + i];
@@ -93,38 +163,49 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
         if (lane == 31) sm.cnt[NBk + 32] = run;  // index(NBk) = NBk + (NBk >> lper)
     }
     __syncwarp();
+    // ---- C: scatter keys / entry ids / buckets into bucket order ----
     for (int e = lane; e < m; e += 32) {
         const uint32_t v = sm.bs[e];
         const int b = v & 0xffffu;
-        sm.ord[sm.cnt[b + (b >> lper)] + (v >> 16)] = (unsigned short)e;
+        const int p = sm.cnt[b + (b >> lper)] + (int)(v >> 16);
+        sm.sk[p] = kk[e];
+        sm.ord[p] = (unsigned short)e;
+        sm.sb[p] = (unsigned short)b;
     }
     __syncwarp();
+    // ---- D: rank inside the bucket, emit ----
     int* tie = sm.cnt + NBk + 33;  // two words: entry ids ranked keep-1 and keep
-    for (int e = lane; e < m; e += 32) {
-        const int b = sm.bs[e] & 0xffffu, b1 = b + 1;
+    for (int p = lane; p < m; p += 32) {
+        const uint32_t kp = sm.sk[p];
+        const int e = sm.ord[p];
+        const int b = sm.sb[p], b1 = b + 1;
         const int q0 = sm.cnt[b + (b >> lper)], q1 = sm.cnt[b1 + (b1 >> lper)];
-        const double de = sm.rd[e];
-        int rank = q0;
+        int lt = 0, eq = 0;
+#pragma unroll 4
         for (int q = q0; q < q1; ++q) {
-            const int f = sm.ord[q];
-            const double df = sm.rd[f];
-            if (df < de) {
-                ++rank;
-            } else if (df == de && f != e) {  // rare: exact distance tie -> canonical (dst, n_a, n_b, n_c)
-                const unsigned long long ke =
-                    ((unsigned long long)(uint32_t)sm.rj[e] << 32) | dg_image_sort_key(sm.rn[e]);
-                const unsigned long long kf =
-                    ((unsigned long long)(uint32_t)sm.rj[f] << 32) | dg_image_sort_key(sm.rn[f]);
-                if (kf < ke) ++rank;
+            const uint32_t kq = sm.sk[q];
+            lt += kq < kp ? 1 : 0;
+            eq += kq == kp ? 1 : 0;
+        }
+        int rank = q0 + lt;
+        const double de = sm.rd[e];
+        if (eq > 1) {  // rare: 32-bit keys collide -> exact order on (distance, dst, n_a, n_b, n_c)
+            const unsigned long long ke = dg_tie_key(sm, e);
+            for (int q = q0; q < q1; ++q) {
+                if (q == p || sm.sk[q] != kp) continue;
+                const int f = sm.ord[q];
+                const double df = sm.rd[f];
+                if (df < de || (df == de && dg_tie_key(sm, f) < ke)) ++rank;
             }
         }
         if (rank < keep) {  // scattered inside the row's contiguous range; L2 merges the sectors
             dst[o + rank] = sm.rj[e];
             image[o + rank] = sm.rn[e];
             dist[o + rank] = de;
-            sm.fd[rank] = (float)de;
         }
         if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+        // fd aliases the by-entry keys, which phase C consumed; sk / ord / sb stay live for the other lanes
+        if (rank < keep) sm.fd[rank] = (float)de;
     }
     if (m > keep && keep > 0) {
         __syncwarp();
@@ -132,21 +213,7 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
     }
     __syncwarp();
     if (rbf.K4 > 0) {
-        float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
-        const int nq = keep * rbf.K4;
-        // (edge, bin group) of float4 q = lane, lane + 32, ... walked incrementally: no division in the loop
-        const int de = 32 / rbf.K4, dk = 32 - de * rbf.K4;
-        int e = lane / rbf.K4, k4 = lane - e * rbf.K4;
-#pragma unroll 4
-        for (int q = lane; q < nq; q += 32) {
-            __stcs(o4 + q, dg_rbf4(sm.fd[e], k4 << 2, rbf));
-            k4 += dk;
-            e += de;
-            if (k4 >= rbf.K4) {
-                k4 -= rbf.K4;
-                ++e;
-            }
-        }
+        dg_rbf_row(sm.fd, keep, o, lane, rbf);
         __syncwarp();
     }
 }
