@@ -114,8 +114,89 @@ __device__ __forceinline__ void dg_rbf_row(const float* __restrict__ fd, int kee
 // d * key_scale rounded to an integer in [0, 2^32): monotone non-decreasing in d (one rounding in the product, one in
 // the magic-number add).  key_scale = (2^32 - 4096) / r_c and d <= r_c (1 + 2^-52), so the value stays below 2^32.
 #define DG_KEY_MAGIC 4503599627370496.0  // 2^52
+#ifndef DG_BITONIC_MAX
+#define DG_BITONIC_MAX 512  // rows up to this many entries try the register bitonic sort first
+#endif
 __device__ __forceinline__ uint32_t dg_dist_key(double d, double key_scale) {
     return (uint32_t)__double2loint(__dadd_rn(__dmul_rn(d, key_scale), DG_KEY_MAGIC));
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Fast path: bitonic sort in registers.  Entry e of the row becomes the word (key & ~mask) | e, key = 32-bit distance
+// key, mask = 32 * EPL - 1 (the entry id needs log2(32 EPL) bits); EPL words per lane, 32 * EPL >= m, padding
+// 0xffffffff.  The network is lane-major (position p = lane * EPL + r): strides below EPL are compare-exchanges between
+// a lane's own registers, larger strides one shuffle + one min/max per word.  Afterwards neighbouring positions whose
+// truncated keys are equal (exact ties of symmetric cells, or |delta d| < r_c 2^-(32 - log2(32 EPL))) cannot be ordered
+// by the word alone: the row then takes the counting-sort path below, which resolves them exactly.  Returns false in
+// that case (warp-uniform); rd[] already holds the distances either way.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int EPL>
+__device__ __forceinline__ bool dg_row_sort_bitonic(const RowBuf& sm, int m, int keep, double key_scale, long long o,
+                                                    int* __restrict__ dst, uint32_t* __restrict__ image,
+                                                    double* __restrict__ dist, int lane) {
+    constexpr uint32_t IDMASK = 32u * EPL - 1u;
+    uint32_t v[EPL];
+#pragma unroll
+    for (int t = 0; t < EPL; ++t) {
+        v[t] = 0xffffffffu;
+        if (32 * t < m) {  // warp-uniform
+            const int e = lane + 32 * t;
+            if (e < m) {
+                const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
+                sm.rd[e] = d;
+                v[t] = (dg_dist_key(d, key_scale) & ~IDMASK) | (uint32_t)e;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 2; k <= 32 * EPL; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= EPL) {
+                const int lj = j / EPL;
+                const bool up = (lane & (k / EPL)) == 0;  // k / EPL == 32 in the last merge: always ascending
+                const bool take_min = ((lane & lj) == 0) == up;
+#pragma unroll
+                for (int r = 0; r < EPL; ++r) {
+                    const uint32_t w = __shfl_xor_sync(FULL_MASK, v[r], lj);
+                    v[r] = take_min ? min(v[r], w) : max(v[r], w);
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < EPL; ++r) {
+                    if ((r & j) == 0) {
+                        const bool up = k < EPL ? ((r & k) == 0) : ((lane & (k / EPL)) == 0);
+                        const uint32_t lo = min(v[r], v[r | j]), hi = max(v[r], v[r | j]);
+                        v[r] = up ? lo : hi;
+                        v[r | j] = up ? hi : lo;
+                    }
+                }
+            }
+        }
+    }
+    // ties the truncated key cannot order?  (positions >= m hold padding)
+    bool clash = false;
+    const uint32_t nxt = __shfl_down_sync(FULL_MASK, v[0], 1);
+#pragma unroll
+    for (int r = 0; r < EPL; ++r) {
+        const uint32_t w = r + 1 < EPL ? v[r + 1] : nxt;
+        const int p1 = lane * EPL + r + 1;
+        clash |= p1 < m && ((v[r] ^ w) & ~IDMASK) == 0u;
+    }
+    if (__any_sync(FULL_MASK, clash)) return false;
+    // transpose through shared memory so that the CSR stores are coalesced
+#pragma unroll
+    for (int r = 0; r < EPL; ++r) sm.ord[lane * EPL + r] = (unsigned short)(v[r] & IDMASK);
+    __syncwarp();
+    for (int p = lane; p < keep; p += 32) {
+        const int e = sm.ord[p];
+        const double d = sm.rd[e];
+        dst[o + p] = sm.rj[e];
+        image[o + p] = sm.rn[e];
+        dist[o + p] = d;
+        sm.fd[p] = (float)d;
+    }
+    return true;
 }
 
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
@@ -125,6 +206,23 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
                                                  double key_scale, long long o, int* __restrict__ dst,
                                                  uint32_t* __restrict__ image, double* __restrict__ dist,
                                                  DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
+    bool have_dist = false;  // rd[] holds distances (the fast path converted them before giving up)
+    if (m <= 32 * 16 && m <= DG_BITONIC_MAX) {
+        bool done;
+        if (m <= 128) done = dg_row_sort_bitonic<4>(sm, m, keep, key_scale, o, dst, image, dist, lane);
+        else if (m <= 256) done = dg_row_sort_bitonic<8>(sm, m, keep, key_scale, o, dst, image, dist, lane);
+        else done = dg_row_sort_bitonic<16>(sm, m, keep, key_scale, o, dst, image, dist, lane);
+        if (done) {
+            __syncwarp();
+            if (rbf.K4 > 0) {
+                dg_rbf_row(sm.fd, keep, o, lane, rbf);
+                __syncwarp();
+            }
+            return;
+        }
+        have_dist = true;
+        __syncwarp();
+    }
     const int per = NBk >> 5;
     const int lper = 31 - __clz(per);
     const int nwords = NBk + 32 + 1;
@@ -134,7 +232,8 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
     // ---- A: distance, key, bucket histogram ----
     const float scale = (float)NBk;
     for (int e = lane; e < m; e += 32) {
-        const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
+        // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
+        const double d = have_dist ? sm.rd[e] : __dsqrt_rn(sm.rd[e]);
         sm.rd[e] = d;
         kk[e] = dg_dist_key(d, key_scale);
         const float t = (float)d * inv_rc;
