@@ -148,27 +148,46 @@ __device__ __forceinline__ bool dg_row_sort_bitonic(const RowBuf& sm, int m, int
             }
         }
     }
+    // all-ascending bitonic network: the first step of every merge pairs position i with its mirror i ^ (k - 1), the
+    // remaining steps with i ^ j; the smaller word always goes to the lower position, so no direction bookkeeping
 #pragma unroll
     for (int k = 2; k <= 32 * EPL; k <<= 1) {
+        if (k <= EPL) {
 #pragma unroll
-        for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int r = 0; r < EPL; ++r) {
+                const int q = r ^ (k - 1);
+                if (r < q) {
+                    const uint32_t lo = min(v[r], v[q]), hi = max(v[r], v[q]);
+                    v[r] = lo;
+                    v[q] = hi;
+                }
+            }
+        } else {  // mirror across lanes: partner lane = lane ^ (k / EPL - 1), partner register = EPL - 1 - r
+            const int lm = k / EPL - 1;
+            const bool lower = (lane & (k / (2 * EPL))) == 0;
+            uint32_t w[EPL];
+#pragma unroll
+            for (int r = 0; r < EPL; ++r) w[r] = __shfl_xor_sync(FULL_MASK, v[EPL - 1 - r], lm);
+#pragma unroll
+            for (int r = 0; r < EPL; ++r) v[r] = lower ? min(v[r], w[r]) : max(v[r], w[r]);
+        }
+#pragma unroll
+        for (int j = k >> 2; j > 0; j >>= 1) {
             if (j >= EPL) {
                 const int lj = j / EPL;
-                const bool up = (lane & (k / EPL)) == 0;  // k / EPL == 32 in the last merge: always ascending
-                const bool take_min = ((lane & lj) == 0) == up;
+                const bool lower = (lane & lj) == 0;
 #pragma unroll
                 for (int r = 0; r < EPL; ++r) {
                     const uint32_t w = __shfl_xor_sync(FULL_MASK, v[r], lj);
-                    v[r] = take_min ? min(v[r], w) : max(v[r], w);
+                    v[r] = lower ? min(v[r], w) : max(v[r], w);
                 }
             } else {
 #pragma unroll
                 for (int r = 0; r < EPL; ++r) {
                     if ((r & j) == 0) {
-                        const bool up = k < EPL ? ((r & k) == 0) : ((lane & (k / EPL)) == 0);
                         const uint32_t lo = min(v[r], v[r | j]), hi = max(v[r], v[r | j]);
-                        v[r] = up ? lo : hi;
-                        v[r | j] = up ? hi : lo;
+                        v[r] = lo;
+                        v[r | j] = hi;
                     }
                 }
             }
