@@ -67,7 +67,7 @@ class DgnnBuildInfo(C.Structure):
         ("rbf_ms", C.c_float), ("total_ms", C.c_float),
         ("kernel_launches", C.c_int32), ("n_items", C.c_int32), ("cloud_points", C.c_int64),
         ("staged_tile_cap", C.c_int32), ("row_cap", C.c_int32),
-        ("n_cell_structs", C.c_int32), ("direct_warps", C.c_int32), ("rbf_fused", C.c_int32), ("reserved", C.c_int32),
+        ("n_cell_structs", C.c_int32), ("direct_warps", C.c_int32), ("rbf_fused", C.c_int32), ("hit_cap", C.c_int32),
     ]
 
 

@@ -38,7 +38,7 @@ struct dgnn_ctx {
     DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
     DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
     // results
-    DevBuf deg, row_ptr, seo, dst, image, dist, rbf;
+    DevBuf deg, deg_raw, hits, hits_d2, row_ptr, seo, dst, image, dist, rbf;
     // stand-alone rbf staging
     DevBuf tmp_in, tmp_out;
     DevBuf stats;
@@ -55,6 +55,8 @@ struct dgnn_ctx {
     int direct_min_blocks = 2;
     int sort_buckets = 0;
     int fuse_rbf = 1;
+    int hit_cap_opt = -1;                 // -1: auto (density estimate), 0: off, > 0: fixed slots per row
+    double hits_max_bytes = 16e9;         // no hit lists beyond this much scratch
 };
 
 namespace {
@@ -142,6 +144,7 @@ int fetch_stats(dgnn_ctx* ctx) {
 }
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+inline long long max_nb_for_est(uint64_t mn) { return mn > 0x7fffffffULL ? 0x7fffffffLL : (long long)mn; }
 
 // The near-cutoff band  fabs(sqrt(d2) - r_c) <= 1e-6  (evaluated in fp64 exactly like the oracle) as an interval of
 // d2: sqrt and the subtraction are monotone, so the band is [lo, hi] in the ordering of non-negative doubles; both ends
@@ -237,7 +240,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
-                      &ctx->deg, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats};
     for (DevBuf* b : bufs) release(*b);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
@@ -276,6 +279,12 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sort_buckets = v;
     } else if (!strcmp(name, "fuse_rbf")) {
         ctx->fuse_rbf = value != 0.0;  // 0: separate K3 launch after the fill pass (phase-separated timing)
+    } else if (!strcmp(name, "hit_cap")) {
+        if (!(value >= -1 && value <= DGNN_MAX_DEGREE)) return fail(ctx, DGNN_ERR_INVALID_ARG, "hit_cap out of range");
+        ctx->hit_cap_opt = (int)value;  // per-row hit-list slots written by the count pass (-1 auto, 0 off)
+    } else if (!strcmp(name, "hits_max_bytes")) {
+        if (!(value >= 0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "hits_max_bytes out of range");
+        ctx->hits_max_bytes = value;
     } else if (!strcmp(name, "direct_max_atoms")) {
         if (!(value >= 0 && value <= 65535)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_max_atoms out of range");
         ctx->direct_max_atoms = (int)value;  // 0 sends every structure to the cell-list path
@@ -366,6 +375,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     ENSURE(ctx->fc, (size_t)(N + 1) * 8);
     ENSURE(ctx->row_ptr, (size_t)(N + 2) * 8);
     ENSURE(ctx->deg, (size_t)(N + 1) * 4);
+    ENSURE(ctx->deg_raw, (size_t)(N + 1) * 4);
     ENSURE(ctx->seo, (size_t)(S + 2) * 8);
     {
         const long long mx = (N > S ? N : S) + 1;
@@ -379,6 +389,29 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
                          small, d_stats);
     dg_launch_direct_prep(st, N, S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p, (double*)ctx->fa.p,
                           (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+    // hit lists: the count pass records every accepted (atom, image) pair so that the fill pass does not repeat the
+    // traversal.  Slots per row come from the density estimate of the degree (rows that outgrow them, and structures
+    // whose image range does not fit the 5-bit fields, are filled by the traversal pass instead).
+    int hit_cap = ctx->hit_cap_opt > 0 ? round_up(ctx->hit_cap_opt, 32) : 0;  // rows stay 16-byte aligned
+    if (ctx->hit_cap_opt < 0 && N > 0) {
+        int r = fetch_stats(ctx);  // sync: density estimate
+        if (r != DGNN_OK) return r;
+        const long long est = ctx->h_stats->est_deg;
+        // Worth it only where the fill pass is bound by the traversal, not by the bytes it writes: the lists cost the
+        // count pass ~35 % more time and the fill pass 12 B of extra reads per accepted pair.  Measured on C2: uncapped
+        // rows with K = 40 features (176 B written per pair) are HBM-bound either way (traversal fill 8.5 ms vs hit-list
+        // fill 9.1 ms + 0.8 ms in the count pass); capped or feature-less rows are 3-5x faster from the lists.
+        const double keep_est = (double)(est < max_nb_for_est(b->max_neighbors) ? est : max_nb_for_est(b->max_neighbors));
+        const double bytes_per_pair = est > 0 ? keep_est * (16.0 + 4.0 * K) / (double)est : 1e9;
+        if (est > 0 && bytes_per_pair < 64.0)
+            hit_cap = round_up((int)(est + est / 4 + 16 < DGNN_MAX_DEGREE ? est + est / 4 + 16 : DGNN_MAX_DEGREE), 32);
+    }
+    if (hit_cap > 512) hit_cap = 512;  // the hit-list fill pass sorts in registers: rows of up to 512 entries
+    if (hit_cap > 0 && (double)N * (double)hit_cap * 12.0 > ctx->hits_max_bytes) hit_cap = 0;
+    if (hit_cap > 0) {
+        ENSURE(ctx->hits, (size_t)N * (size_t)hit_cap * 4 + 16);
+        ENSURE(ctx->hits_d2, (size_t)N * (size_t)hit_cap * 8 + 16);
+    }
     CU(cudaEventRecord(ctx->ev.e[2], st));
 
     // ---- common traversal parameters -------------------------------------------------------------------------
@@ -416,6 +449,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.n_warps = 8;
     D.n_buckets = 32;
     D.deg_capped = (int*)ctx->deg.p;
+    D.deg_raw = (int*)ctx->deg_raw.p;
+    D.hits = hit_cap > 0 ? (uint32_t*)ctx->hits.p : nullptr;
+    D.hits_d2 = hit_cap > 0 ? (double*)ctx->hits_d2.p : nullptr;
+    D.hit_cap = hit_cap;
     D.stats = d_stats;
     CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
     dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
@@ -429,6 +466,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
+    const int n_fallback_rows = ctx->h_stats->n_fallback_rows;
 
     // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
     DgTraverseArgs A;
@@ -552,7 +590,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     ENSURE(ctx->image, (size_t)(E + 1) * 4);
     ENSURE(ctx->dist, (size_t)(E + 1) * 8);
     const int row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
-    const int n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 1024 ? 512 : 1024);
+    const int n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 256 ? 256 : (row_cap <= 1024 ? 512 : 1024));
     D.row_ptr = (const long long*)ctx->row_ptr.p;
     D.dst = (int*)ctx->dst.p;
     D.image = (uint32_t*)ctx->image.p;
@@ -569,7 +607,18 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     while (D.n_warps > 1 && (int)dg_direct_smem_bytes(D, true) > ctx->smem_optin) D.n_warps >>= 1;
     if ((int)dg_direct_smem_bytes(D, true) > ctx->smem_optin)
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
-    if (E > 0) CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+    // rows with a stored hit list are filled from it; the traversal fill pass takes whatever is left
+    DgDirectArgs H = D;
+    bool use_hits = hit_cap > 0;
+    if (use_hits) {
+        H.n_warps = 8;
+        while (H.n_warps > 1 && (int)dg_fill_hits_smem_bytes(H) > ctx->smem_optin) H.n_warps >>= 1;
+        if ((int)dg_fill_hits_smem_bytes(H) > ctx->smem_optin) use_hits = false;
+    }
+    if (!use_hits) D.hit_cap = 0;
+    if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
+    if (E > 0 && (!use_hits || n_fallback_rows > 0))
+        CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
     if (n_cell_structs > 0 && E > 0) {
         A.row_ptr = (const long long*)ctx->row_ptr.p;
         A.dst = (int*)ctx->dst.p;
@@ -632,6 +681,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.n_cell_structs = n_cell_structs;
     I.direct_warps = D.n_warps;
     I.rbf_fused = fuse_rbf ? 1 : 0;
+    I.hit_cap = use_hits ? hit_cap : 0;
     return DGNN_OK;
 }
 

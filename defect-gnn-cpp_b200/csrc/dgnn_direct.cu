@@ -53,6 +53,13 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
         if (atomicCAS(&stats->err_status, 0, G.status) == 0) stats->err_struct = (int)s;
     } else if (G.mode == DG_MODE_CELL && G.natoms > 0) {
         atomicAdd(&stats->n_cell_structs, 1);
+    } else if (G.natoms > 0) {
+        // density estimate of the degree: N * (4/3) pi r^3 / V, V = h_0 h_1 h_2 / (the sines) >= rcm^3 / (w0 w1 w2)
+        const double rcm = DG_RCM(r_cutoff);
+        const double det = fabs(L[0] * (L[4] * L[8] - L[5] * L[7]) + L[1] * (L[5] * L[6] - L[3] * L[8]) +
+                                L[2] * (L[3] * L[7] - L[4] * L[6]));
+        const double est = (double)G.natoms * 4.18879020478639 * rcm * rcm * rcm / det;
+        atomicMax(&stats->est_deg, est < 1.0e6 ? (int)est + 1 : 1000000);
     }
 }
 
@@ -135,10 +142,17 @@ struct Src {
 //   0: epsilon <= 0, nothing is excluded;  1: 0 < epsilon <= DG_EPS_FAST: only the atom's own n = (0,0,0) image can
 //   qualify (its d2 is exactly 0; k_small_geom rejects cells whose perpendicular height is below 2 epsilon), so the
 //   test is the branch-free `self && d2 == 0`;  2: any epsilon, exact sqrt test behind a (rare) branch.
-template <bool FILL, int EPS>
-__device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb, bool active,
-                                           bool self, int jloc, double px, double py, double pz, int na, int nb,
-                                           int nc, unsigned lt_mask, int& m, unsigned& near) {
+__device__ __forceinline__ uint32_t dg_pack_hit(int j, int na, int nb, int nc) {
+    return (uint32_t)j | ((uint32_t)(na + 16) << 17) | ((uint32_t)(nb + 16) << 22) | ((uint32_t)(nc + 16) << 27);
+}
+
+// HITS (count pass only): in-cutoff candidates are also compacted (ballot/popc) into the row's hit list in global
+// memory, so that the fill pass recomputes only the ~deg accepted pairs instead of repeating the traversal.
+template <bool FILL, int EPS, bool HITS>
+__device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb,
+                                           uint32_t* __restrict__ hrow, double* __restrict__ hd2, bool active,
+                                           bool self, int jloc, double px, double py, double pz, int na, int nb, int nc,
+                                           unsigned lt_mask, int& m, unsigned& near) {
     const double dx = DG_SUB(S.x, px);
     const double dy = DG_SUB(S.y, py);
     const double dz = DG_SUB(S.z, pz);
@@ -155,7 +169,19 @@ __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, 
         // count pass: per-lane tallies, reduced once per row (no ballot per candidate).  near-cutoff band
         // |sqrt(d2) - r_c| <= 1e-6 as two thresholds on d2 (sqrt is monotone; thresholds bisected on the host)
         near += (active && d2 >= A.near_d2_lo && d2 <= A.near_d2_hi) ? 1u : 0u;
-        m += hit ? 1 : 0;
+        if (HITS) {
+            const unsigned mask = __ballot_sync(FULL_MASK, hit);
+            if (hit) {
+                const int pos = m + __popc(mask & lt_mask);
+                if (pos < A.hit_cap) {
+                    hrow[pos] = dg_pack_hit(jloc, na, nb, nc);
+                    hd2[pos] = d2;
+                }
+            }
+            m += __popc(mask);  // warp-uniform in this mode
+        } else {
+            m += hit ? 1 : 0;
+        }
         return;
     }
     const unsigned mask = __ballot_sync(FULL_MASK, hit);
@@ -170,7 +196,7 @@ __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, 
     m += __popc(mask);
 }
 
-template <bool FILL, int MINB, int EPS>
+template <bool FILL, int MINB, int EPS, bool HITS>
 __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -189,6 +215,11 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
             if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;  // the cell-list path owns this structure
             const long long base = G->atom_base;
             const int N = G->natoms, nimg = G->nimg;
+            // rows the hit-list fill pass (k_fill_hits) owns are skipped here; this pass takes the rest
+            if (FILL && A.hit_cap > 0 && nimg <= DG_HIT_NMAX && A.deg_raw[a] <= A.hit_cap) continue;  // (row_cap >= deg)
+            const bool store_hits = HITS && nimg <= DG_HIT_NMAX;
+            uint32_t* __restrict__ hrow = HITS ? A.hits + (size_t)a * (size_t)A.hit_cap : nullptr;
+            double* __restrict__ hd2 = HITS ? A.hits_d2 + (size_t)a * (size_t)A.hit_cap : nullptr;
             Src S;
             S.x = A.x[a]; S.y = A.y[a]; S.z = A.z[a];
             S.iloc = (int)(a - base);
@@ -240,8 +271,8 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                                 const double px = DG_ADD(xj, DG_ADD(ob0, DG_MUL(ncd, L20)));
                                 const double py = DG_ADD(yj, DG_ADD(ob1, DG_MUL(ncd, L21)));
                                 const double pz = DG_ADD(zj, DG_ADD(ob2, DG_MUL(ncd, L22)));
-                                test_point<FILL, EPS>(A, S, rb, act_ab && sc < c2, self, jj, px, py, pz, lo0 + sa,
-                                                      lo1 + sb, lo2 + sc, lt_mask, m, near);
+                                test_point<FILL, EPS, HITS>(A, S, rb, hrow, hd2, act_ab && sc < c2, self, jj, px, py, pz,
+                                                            lo0 + sa, lo1 + sb, lo2 + sc, lt_mask, m, near);
                             }
                         }
                     }
@@ -265,16 +296,20 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                         const double px = DG_ADD(xj, dg_image_offset(G->L, 0, na, nb, nc));
                         const double py = DG_ADD(yj, dg_image_offset(G->L, 1, na, nb, nc));
                         const double pz = DG_ADD(zj, dg_image_offset(G->L, 2, na, nb, nc));
-                        test_point<FILL, EPS>(A, S, rb, active, j == S.iloc, j, px, py, pz, na, nb, nc, lt_mask, m,
-                                              near);
+                        test_point<FILL, EPS, HITS>(A, S, rb, hrow, hd2, active, j == S.iloc, j, px, py, pz, na, nb, nc,
+                                                    lt_mask, m, near);
                     }
                 }
             }
-            if (!FILL) m = __reduce_add_sync(FULL_MASK, m);
+            if (!FILL && !HITS) m = __reduce_add_sync(FULL_MASK, m);
             maxdeg = m > maxdeg ? m : maxdeg;
             const int keep = m < A.max_neighbors ? m : A.max_neighbors;
             if (!FILL) {
-                if (lane == 0) A.deg_capped[a] = keep;
+                if (lane == 0) {
+                    A.deg_capped[a] = keep;
+                    A.deg_raw[a] = m;
+                    if (HITS && (m > A.hit_cap || !store_hits)) atomicAdd(&A.stats->n_fallback_rows, 1);
+                }
             } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
                 if (lane == 0) atomicExch(&A.stats->overflow, 1);
             } else {
@@ -297,29 +332,29 @@ size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {
     return fill ? (size_t)a.n_warps * dg_rowbuf_bytes(a.row_cap, a.n_buckets) : 0;
 }
 
-template <bool FILL, int MINB, int EPS>
+template <bool FILL, int MINB, int EPS, bool HITS>
 static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e =
-        cudaFuncSetAttribute(k_direct<FILL, MINB, EPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB, EPS, HITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem);
     if (e != cudaSuccess) return e;
     int occ = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS>, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS, HITS>, threads, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin
     const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
     long long grid = (long long)sm_count * occ;
     if (grid > want) grid = want;
-    k_direct<FILL, MINB, EPS><<<(unsigned)grid, threads, smem, st>>>(a);
+    k_direct<FILL, MINB, EPS, HITS><<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
-template <bool FILL, int MINB>
+template <bool FILL, int MINB, bool HITS>
 static cudaError_t launch_direct_e(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
     switch (a.eps_mode) {
-        case 0: return launch_direct_t<FILL, MINB, 0>(st, a, sm_count, smem, threads);
-        case 1: return launch_direct_t<FILL, MINB, 1>(st, a, sm_count, smem, threads);
-        default: return launch_direct_t<FILL, MINB, 2>(st, a, sm_count, smem, threads);
+        case 0: return launch_direct_t<FILL, MINB, 0, HITS>(st, a, sm_count, smem, threads);
+        case 1: return launch_direct_t<FILL, MINB, 1, HITS>(st, a, sm_count, smem, threads);
+        default: return launch_direct_t<FILL, MINB, 2, HITS>(st, a, sm_count, smem, threads);
     }
 }
 
@@ -328,9 +363,154 @@ cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, 
     const size_t smem = dg_direct_smem_bytes(a, fill);
     const int threads = a.n_warps * 32;
     ++g_direct_launches;
-    if (min_blocks <= 2)
-        return fill ? launch_direct_e<true, 2>(st, a, sm_count, smem, threads)
-                    : launch_direct_e<false, 2>(st, a, sm_count, smem, threads);
-    return fill ? launch_direct_e<true, 3>(st, a, sm_count, smem, threads)
-                : launch_direct_e<false, 3>(st, a, sm_count, smem, threads);
+    if (fill)
+        return min_blocks <= 2 ? launch_direct_e<true, 2, false>(st, a, sm_count, smem, threads)
+                               : launch_direct_e<true, 3, false>(st, a, sm_count, smem, threads);
+    if (a.hit_cap > 0 && a.hits)
+        return min_blocks <= 2 ? launch_direct_e<false, 2, true>(st, a, sm_count, smem, threads)
+                               : launch_direct_e<false, 3, true>(st, a, sm_count, smem, threads);
+    return min_blocks <= 2 ? launch_direct_e<false, 2, false>(st, a, sm_count, smem, threads)
+                           : launch_direct_e<false, 3, false>(st, a, sm_count, smem, threads);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// fill pass from hit lists: one warp per row reads the row's accepted (atom, image) pairs written by the count pass,
+// recomputes their d2 with the reference arithmetic (bit-identical to what the count pass tested), sorts and emits.
+// No traversal state: few registers, more resident warps to overlap the sort with the feature stores.
+// ---------------------------------------------------------------------------------------------------------------------
+// Row schedule of one warp: rows warp, warp + nwarps, ... of chunk blockIdx.x, then of chunk blockIdx.x + gridDim.x ...
+struct RowIter {
+    long long chunk, a;
+};
+__device__ __forceinline__ bool row_iter_valid(const RowIter& it, long long n_chunks) { return it.chunk < n_chunks; }
+__device__ __forceinline__ void row_iter_first(RowIter& it, long long n_atoms, int warp) {
+    it.chunk = blockIdx.x;
+    it.a = it.chunk * DG_ROW_CHUNK + warp;
+    (void)n_atoms;
+}
+__device__ __forceinline__ void row_iter_next(RowIter& it, long long n_atoms, long long n_chunks, int warp, int nwarps) {
+    it.a += nwarps;
+    while (true) {
+        const long long end = (it.chunk + 1) * DG_ROW_CHUNK < n_atoms ? (it.chunk + 1) * DG_ROW_CHUNK : n_atoms;
+        if (it.a < end) return;
+        it.chunk += gridDim.x;
+        if (it.chunk >= n_chunks) return;
+        it.a = it.chunk * DG_ROW_CHUNK + warp;
+    }
+}
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+// per-row scalars fetched one row ahead
+struct RowHead {
+    int s, m;
+    long long o;
+};
+__device__ __forceinline__ RowHead row_head_load(const DgDirectArgs& A, long long a) {
+    RowHead h;
+    h.s = A.astruct[a];
+    h.m = A.deg_raw[a];
+    h.o = A.row_ptr[a];
+    return h;
+}
+
+// shared memory of one warp of k_fill_hits: d2 / hit words double buffered (the next row streams in with cp.async while
+// this one is sorted and emitted), sorted words, fp32 distances in row order, tie scratch
+__host__ __device__ inline size_t dg_fill_hits_warp_bytes(int W) {
+    return (size_t)2 * W * 8 + (size_t)2 * W * 4 + (size_t)W * 4 + (size_t)W * 4 + 16 + (size_t)2 * DG_STAGE_Q * 16;
+}
+
+__global__ void __launch_bounds__(256, 3) k_fill_hits(const DgDirectArgs A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    // rows are hit_cap entries apart in global memory (a multiple of 32: 16-byte aligned); only the first row_cap of a
+    // row can be in use
+    const int W = A.hit_cap < A.row_cap ? A.hit_cap : A.row_cap;
+    unsigned char* base = smem_raw + (size_t)warp * dg_fill_hits_warp_bytes(W);
+    double* rd = reinterpret_cast<double*>(base);                      // [2][W]
+    uint32_t* hw = reinterpret_cast<uint32_t*>(base + (size_t)2 * W * 8);  // [2][W]
+    uint32_t* sk = hw + 2 * W;
+    float* fd = reinterpret_cast<float*>(sk + W);
+    int* tie = reinterpret_cast<int*>(fd + W);
+    float4* stage = reinterpret_cast<float4*>(base + (size_t)32 * W + 16);  // 2 x DG_STAGE_Q float4 (TMA source)
+    unsigned seq = 0;
+    const long long n_chunks = (A.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+
+    RowIter it;
+    row_iter_first(it, A.n_atoms, warp);
+    if (!row_iter_valid(it, n_chunks) || it.a >= A.n_atoms) return;  // (only when the grid exceeds the chunk count)
+    RowHead cur = row_head_load(A, it.a);
+    {
+        const uint32_t* src = A.hits + (size_t)it.a * (size_t)A.hit_cap;
+        const double* srcd = A.hits_d2 + (size_t)it.a * (size_t)A.hit_cap;
+        for (int c = lane * 4; c < W; c += 128) cp_async16(hw + c, src + c);
+        for (int c = lane * 2; c < W; c += 64) cp_async16(rd + c, srcd + c);
+        cp_async_commit();
+    }
+    int buf = 0;
+    while (true) {
+        RowIter nx = it;
+        row_iter_next(nx, A.n_atoms, n_chunks, warp, nwarps);
+        const bool have_next = row_iter_valid(nx, n_chunks);
+        cp_async_wait_all();
+        __syncwarp();
+        RowHead nxt = cur;
+        if (have_next) {
+            nxt = row_head_load(A, nx.a);
+            const uint32_t* src = A.hits + (size_t)nx.a * (size_t)A.hit_cap;
+            const double* srcd = A.hits_d2 + (size_t)nx.a * (size_t)A.hit_cap;
+            uint32_t* hwn = hw + (buf ^ 1) * W;
+            double* rdn = rd + (buf ^ 1) * W;
+            for (int c = lane * 4; c < W; c += 128) cp_async16(hwn + c, src + c);
+            for (int c = lane * 2; c < W; c += 64) cp_async16(rdn + c, srcd + c);
+            cp_async_commit();
+        }
+        const DgSmall* __restrict__ G = A.small + cur.s;
+        const int m = cur.m;
+        // rows this pass does not own (cell-list structures, image range beyond the 5-bit fields, more hits than
+        // slots) are filled by the traversal pass
+        if (G->mode != DG_MODE_CELL && G->status == DG_ST_OK && G->nimg <= DG_HIT_NMAX && m <= W) {
+            const int keep = m < A.max_neighbors ? m : A.max_neighbors;
+            const HitWordPayload P{hw + buf * W};
+            dg_row_sort_bitonic_any(rd + buf * W, sk, fd, tie, P, m, keep, A.key_scale, cur.o, A.dst, A.image, A.dist,
+                                    A.stats, lane);
+            if (A.rbf.K4 > 0) {
+                dg_rbf_row_bulk(fd, keep, cur.o, lane, A.rbf, stage, seq);
+                __syncwarp();
+            }
+        }
+        if (!have_next) break;
+        it = nx;
+        cur = nxt;
+        buf ^= 1;
+    }
+    if (lane == 0) dg_bulk_wait_all();  // the stages must outlive the copies that read them
+}
+
+size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a) {
+    const int W = a.hit_cap < a.row_cap ? a.hit_cap : a.row_cap;
+    return (size_t)a.n_warps * dg_fill_hits_warp_bytes(W);
+}
+
+cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
+    if (a.n_atoms <= 0) return cudaSuccess;
+    const size_t smem = dg_fill_hits_smem_bytes(a);
+    const int threads = a.n_warps * 32;
+    cudaError_t e = cudaFuncSetAttribute(k_fill_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill_hits, threads, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    long long grid = (long long)sm_count * occ;
+    if (grid > want) grid = want;
+    ++g_direct_launches;
+    k_fill_hits<<<(unsigned)grid, threads, smem, st>>>(a);
+    return cudaGetLastError();
 }

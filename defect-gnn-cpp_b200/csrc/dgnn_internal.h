@@ -21,6 +21,8 @@ struct DgStats {
     int err_struct;              // and the structure it was seen on
     int overflow;                // a row did not fit the row buffer (must not happen)
     int n_cell_structs;          // non-empty structures routed to the cell-list path
+    int n_fallback_rows;         // direct-path rows whose hit list was not stored (degree > hit_cap or image range > 15)
+    int est_deg;                 // density estimate of the largest degree (sizes the hit lists of a ctx's first build)
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -119,6 +121,10 @@ struct DgDirectArgs {
     int eps_mode;                // self-exclusion rule: 0 none (eps <= 0), 1 fast (0 < eps <= DG_EPS_FAST), 2 generic
     double near_d2_lo, near_d2_hi;  // |sqrt(d2) - r_c| <= 1e-6  <=>  near_d2_lo <= d2 <= near_d2_hi
     int* deg_capped;             // [N] (count pass)
+    int* deg_raw;                // [N] uncapped degrees (count pass writes, fill passes read)
+    uint32_t* hits;              // [N * hit_cap] per-row hit lists written by the count pass (dg_pack_hit), or null
+    double* hits_d2;             // [N * hit_cap] the accepted pairs' d2 (bit-exact reference arithmetic)
+    int hit_cap;                 // slots per row (0: no hit lists, the fill pass repeats the traversal)
     const long long* row_ptr;    // [N+1] (fill pass)
     int* dst;
     uint32_t* image;
@@ -127,6 +133,9 @@ struct DgDirectArgs {
     DgRbfEpi rbf;
 };
 #define DG_EPS_FAST 1.0e-3
+// hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
+#define DG_HIT_NMAX 15
+#define DG_HIT_JMAX 0x1ffff
 // eps_fast > 0: the traversal will use the fast self-exclusion (eps_mode 1); cells thinner than 2 eps are rejected
 void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
                           double r_cutoff, int direct_max_atoms, double eps_fast, DgSmall* small, DgStats* stats);
@@ -135,6 +144,9 @@ void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long
                            double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
+// fill pass from the count pass's hit lists (rows with degree <= hit_cap and image range <= DG_HIT_NMAX)
+size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a);
+cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_count);
 int dg_direct_launch_count_reset();
 
 // ---- dgnn_rbf.cu ----

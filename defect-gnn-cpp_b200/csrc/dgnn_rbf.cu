@@ -23,8 +23,15 @@ int dg_rbf_launch_count_reset() {
     return v;
 }
 
+#ifndef RBF_THREADS
 #define RBF_THREADS 256
-#define RBF_TILE_EDGES 512  // edges per tile: 512 * K/4 float4 per tile (5120 at K = 40 -> 20 per thread)
+#endif
+#ifndef RBF_TILE_EDGES
+#define RBF_TILE_EDGES 512
+#endif
+#ifndef RBF_CTAS_PER_SM
+#define RBF_CTAS_PER_SM 8
+#endif  // edges per tile: 512 * K/4 float4 per tile (5120 at K = 40 -> 20 per thread)
 
 __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_vec4(const double* __restrict__ dist, long long n_edges,
                                                               float4* __restrict__ out, DgRbfEpi P) {
@@ -78,7 +85,7 @@ void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, i
     if (sm_count <= 0) sm_count = 148;
     if ((K & 3) == 0 && (long long)RBF_TILE_EDGES * (K / 4) < (1 << 22) && ((uintptr_t)out & 15) == 0) {
         const long long n_tiles = (n_edges + RBF_TILE_EDGES - 1) / RBF_TILE_EDGES;
-        long long grid = (long long)sm_count * 8;  // 8 resident CTAs of 256 threads per SM
+        long long grid = (long long)sm_count * RBF_CTAS_PER_SM;  // resident CTAs per SM
         if (grid > n_tiles) grid = n_tiles;
         k_rbf_f32_vec4<<<(unsigned)grid, RBF_THREADS, 0, st>>>(dist, n_edges, reinterpret_cast<float4*>(out), P);
     } else {

@@ -70,18 +70,40 @@ __device__ __forceinline__ unsigned long long dg_tie_key(const RowBuf& sm, int e
 //  - K4 groups fit a warp (G = 32 / K4 edges per step, >= 28 lanes busy): every lane owns one fixed float4 column, so
 //    the bin centres are loop constants and a warp store covers G whole feature rows (G * K * 4 contiguous bytes);
 //  - otherwise flat float4 indexing (every warp store covers 512 contiguous bytes).
+#ifndef DG_STORE_MODE
+#define DG_STORE_MODE 0
+#endif
+#ifndef DG_RBF_UNROLL
+#define DG_RBF_UNROLL 4  // independent float4 stores in flight per lane
+#endif
+#ifndef DG_RBF_SCHEME
+#define DG_RBF_SCHEME 0  // 0: fixed float4 column per lane; 1: flat float4 index, warp stores aligned to 128-byte lines
+#endif
+__device__ __forceinline__ void dg_store_f4(float4* p, const float4& v) {
+#if DG_STORE_MODE == 0
+    __stcs(p, v);
+#elif DG_STORE_MODE == 1
+    *p = v;
+#elif DG_STORE_MODE == 2
+    __stcg(p, v);
+#else
+    __stwt(p, v);
+#endif
+}
+
 __device__ __forceinline__ void dg_rbf_row(const float* __restrict__ fd, int keep, long long o, int lane,
                                            const DgRbfEpi& rbf) {
     float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
     const int G = 32 / rbf.K4;  // 0 when K4 > 32
-    if (G * rbf.K4 >= 28) {
+    if (DG_RBF_SCHEME == 0 && G * rbf.K4 >= 28) {
         const int es = lane / rbf.K4, k4 = lane - es * rbf.K4;
         if (es < G) {
             const float c0 = (float)(4 * k4) * rbf.dr, c1 = (float)(4 * k4 + 1) * rbf.dr;
             const float c2 = (float)(4 * k4 + 2) * rbf.dr, c3 = (float)(4 * k4 + 3) * rbf.dr;
             float4* __restrict__ p = o4 + es * rbf.K4 + k4;
             const int step = G * rbf.K4;
-#pragma unroll 2
+            constexpr int kUnroll = DG_RBF_UNROLL;
+#pragma unroll kUnroll
             for (int e = es; e < keep; e += G, p += step) {
                 const float d = fd[e];
                 const float x0 = c0 - d, x1 = c1 - d, x2 = c2 - d, x3 = c3 - d;
@@ -90,23 +112,125 @@ __device__ __forceinline__ void dg_rbf_row(const float* __restrict__ fd, int kee
                 v.y = dg_ex2(fmaf(rbf.coef * x1, x1, rbf.lognorm));
                 v.z = dg_ex2(fmaf(rbf.coef * x2, x2, rbf.lognorm));
                 v.w = dg_ex2(fmaf(rbf.coef * x3, x3, rbf.lognorm));
-                __stcs(p, v);
+                dg_store_f4(p, v);
             }
         }
     } else {
         const int nq = keep * rbf.K4;
-        // (edge, bin group) of float4 q = lane, lane + 32, ... walked incrementally: no division in the loop
+        // flat float4 index q = lane - shift, + 32, ...: the shift puts lane 0 on a 128-byte line boundary, so every
+        // warp store covers four whole lines; (edge, bin group) walked incrementally: no division in the loop
+        const int shift = DG_RBF_SCHEME == 1 ? (int)((o * (long long)rbf.K4) & 7) : 0;
         const int de = 32 / rbf.K4, dk = 32 - de * rbf.K4;
-        int e = lane / rbf.K4, k4 = lane - e * rbf.K4;
+        int q = lane - shift;
+        int e = 0, k4 = q;
+        if (q >= 0) {
+            e = q / rbf.K4;
+            k4 = q - e * rbf.K4;
+        } else {  // first step is a partial one for the lanes before the row start: they begin one round later
+            q += 32;
+            e = q / rbf.K4;
+            k4 = q - e * rbf.K4;
+        }
 #pragma unroll 4
-        for (int q = lane; q < nq; q += 32) {
-            __stcs(o4 + q, dg_rbf4(fd[e], k4 << 2, rbf));
+        for (; q < nq; q += 32) {
+            dg_store_f4(o4 + q, dg_rbf4(fd[e], k4 << 2, rbf));
             k4 += dk;
             e += de;
             if (k4 >= rbf.K4) {
                 k4 -= rbf.K4;
                 ++e;
             }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Same epilogue through the TMA: features are produced into a small shared-memory stage (the row-major layout of the
+// E x K tensor, so a stage is one contiguous span of it) and an elected lane hands every full stage to the bulk-copy
+// engine (cp.async.bulk shared -> global).  The feature stream -- 91 % of all bytes the path writes -- then never sits
+// in the LSU / MIO queues, so back-pressure from HBM does not block the shuffles and shared-memory traffic of the warps
+// that are sorting their next row.  Two stages per warp, used alternately across rows (`seq` persists).
+// ---------------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void dg_bulk_store(void* gdst, const void* ssrc, unsigned bytes) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(ssrc);
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(s), "r"(bytes)
+                 : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void dg_bulk_wait_read() {
+    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void dg_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void dg_fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// stage: 2 x DG_STAGE_Q float4 per warp (16-byte aligned).  A stage takes DG_STAGE_STEPS warp steps of `step` float4
+// (step = G * K4 <= 32 whole feature rows in the fixed-column scheme, else 32).  All 32 lanes must call.
+#define DG_STAGE_STEPS 4
+#define DG_STAGE_Q (32 * DG_STAGE_STEPS)
+__device__ __forceinline__ void dg_rbf_row_bulk(const float* __restrict__ fd, int keep, long long o, int lane,
+                                                const DgRbfEpi& rbf, float4* __restrict__ stage, unsigned& seq) {
+    float4* __restrict__ o4 = rbf.out + o * (long long)rbf.K4;
+    const int nq = keep * rbf.K4;
+    const int G = 32 / rbf.K4;  // 0 when K4 > 32
+    if (G * rbf.K4 >= 28) {
+        // every lane owns one fixed float4 column: bin centres are loop constants, a step is G whole feature rows
+        const int step = G * rbf.K4, cq = DG_STAGE_STEPS * step;
+        const int es = lane / rbf.K4, kc = lane - es * rbf.K4;
+        const float c0 = (float)(4 * kc) * rbf.dr, c1 = (float)(4 * kc + 1) * rbf.dr;
+        const float c2 = (float)(4 * kc + 2) * rbf.dr, c3 = (float)(4 * kc + 3) * rbf.dr;
+        int e = es;
+        for (int q0 = 0; q0 < nq; q0 += cq) {
+            float4* __restrict__ sb = stage + (seq & 1u) * DG_STAGE_Q + lane;
+            if (lane == 0) dg_bulk_wait_read<1>();  // the copy that last read this stage is two groups back
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < DG_STAGE_STEPS; ++it, e += G, sb += step) {
+                // branch-free: lanes past the row end (and the 32 - step idle lanes) recompute the last edge; what
+                // they write lies beyond the bytes this stage copies or is overwritten by the next step (same warp,
+                // program order)
+                const float d = fd[e < keep ? e : keep - 1];
+                const float x0 = c0 - d, x1 = c1 - d, x2 = c2 - d, x3 = c3 - d;
+                float4 v;
+                v.x = dg_ex2(fmaf(rbf.coef * x0, x0, rbf.lognorm));
+                v.y = dg_ex2(fmaf(rbf.coef * x1, x1, rbf.lognorm));
+                v.z = dg_ex2(fmaf(rbf.coef * x2, x2, rbf.lognorm));
+                v.w = dg_ex2(fmaf(rbf.coef * x3, x3, rbf.lognorm));
+                *sb = v;
+            }
+            dg_fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                const int nq_c = nq - q0 < cq ? nq - q0 : cq;
+                dg_bulk_store(o4 + q0, stage + (seq & 1u) * DG_STAGE_Q, (unsigned)nq_c * 16u);
+            }
+            ++seq;
+        }
+    } else {
+        // flat float4 index; (edge, bin group) walked incrementally: no division in the loop
+        const int de = 32 / rbf.K4, dk = 32 - de * rbf.K4;
+        int e = lane / rbf.K4, k4 = lane - e * rbf.K4;
+        for (int q0 = 0; q0 < nq; q0 += DG_STAGE_Q) {
+            float4* __restrict__ sb = stage + (seq & 1u) * DG_STAGE_Q + lane;
+            if (lane == 0) dg_bulk_wait_read<1>();
+            __syncwarp();
+#pragma unroll
+            for (int it = 0; it < DG_STAGE_STEPS; ++it, sb += 32) {
+                if (q0 + it * 32 + lane < nq) *sb = dg_rbf4(fd[e], k4 << 2, rbf);
+                k4 += dk;
+                e += de;
+                if (k4 >= rbf.K4) {
+                    k4 -= rbf.K4;
+                    ++e;
+                }
+            }
+            dg_fence_proxy_async();
+            __syncwarp();
+            if (lane == 0) {
+                const int nq_c = nq - q0 < DG_STAGE_Q ? nq - q0 : DG_STAGE_Q;
+                dg_bulk_store(o4 + q0, stage + (seq & 1u) * DG_STAGE_Q, (unsigned)nq_c * 16u);
+            }
+            ++seq;
         }
     }
 }
@@ -122,18 +246,49 @@ __device__ __forceinline__ uint32_t dg_dist_key(double d, double key_scale) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// Fast path: bitonic sort in registers.  Entry e of the row becomes the word (key & ~mask) | e, key = 32-bit distance
-// key, mask = 32 * EPL - 1 (the entry id needs log2(32 EPL) bits); EPL words per lane, 32 * EPL >= m, padding
-// 0xffffffff.  The network is lane-major (position p = lane * EPL + r): strides below EPL are compare-exchanges between
-// a lane's own registers, larger strides one shuffle + one min/max per word.  Afterwards neighbouring positions whose
-// truncated keys are equal (exact ties of symmetric cells, or |delta d| < r_c 2^-(32 - log2(32 EPL))) cannot be ordered
-// by the word alone: the row then takes the counting-sort path below, which resolves them exactly.  Returns false in
-// that case (warp-uniform); rd[] already holds the distances either way.
+// Register bitonic sort (rows of up to 512 entries).  Entry e of the row becomes the word (key & ~mask) | e, key =
+// 32-bit distance key, mask = 32 * EPL - 1 (the entry id needs log2(32 EPL) bits); EPL words per lane, 32 * EPL >= m,
+// padding 0xffffffff.  The network is lane-major (position p = lane * EPL + r): strides below EPL are compare-exchanges
+// between a lane's own registers, larger strides one shuffle + one min/max per word.  Positions whose truncated keys are
+// equal (exact ties of symmetric cells, or |delta d| < r_c 2^-(32 - log2(32 EPL))) form contiguous runs the word alone
+// cannot order: inside such runs the rank is recomputed with the exact canonical comparison (fp64 distance, then
+// (dst, n_a, n_b, n_c)).
+//
+// Payload policies give the sort access to an entry's (dst, packed image):
 // ---------------------------------------------------------------------------------------------------------------------
-template <int EPL>
-__device__ __forceinline__ bool dg_row_sort_bitonic(const RowBuf& sm, int m, int keep, double key_scale, long long o,
+struct RowBufPayload {  // traversal kernels: rj / rn arrays filled by the ballot compaction
+    const int* rj;
+    const uint32_t* rn;
+    __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
+        j = rj[e];
+        img = rn[e];
+    }
+};
+struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (dg_pack_hit in dgnn_direct.cu)
+    const uint32_t* hw;
+    __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
+        const uint32_t v = hw[e];
+        j = (int)(v & 0x1ffffu);
+        img = dg_pack_image((int)((v >> 17) & 31u) - 16, (int)((v >> 22) & 31u) - 16, (int)(v >> 27) - 16);
+    }
+};
+template <class Payload>
+__device__ __forceinline__ unsigned long long dg_payload_tie_key(const Payload& P, int e) {
+    int j;
+    uint32_t img;
+    P.get(e, j, img);
+    return ((unsigned long long)(uint32_t)j << 32) | dg_image_sort_key(img);
+}
+
+// rd: d2 by entry (replaced by the distance), sk: scratch for the sorted words, fd: distances in final order (fp32),
+// tie: two ints of scratch.  All 32 lanes must call; m <= 32 * EPL.
+template <int EPL, class Payload>
+__device__ __forceinline__ void dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
+                                                    float* __restrict__ fd, int* __restrict__ tie, const Payload& P,
+                                                    int m, int keep, double key_scale, long long o,
                                                     int* __restrict__ dst, uint32_t* __restrict__ image,
-                                                    double* __restrict__ dist, int lane) {
+                                                    double* __restrict__ dist, DgStats* __restrict__ stats,
+                                                    int lane) {
     constexpr uint32_t IDMASK = 32u * EPL - 1u;
     uint32_t v[EPL];
 #pragma unroll
@@ -142,8 +297,8 @@ __device__ __forceinline__ bool dg_row_sort_bitonic(const RowBuf& sm, int m, int
         if (32 * t < m) {  // warp-uniform
             const int e = lane + 32 * t;
             if (e < m) {
-                const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
-                sm.rd[e] = d;
+                const double d = __dsqrt_rn(rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
+                rd[e] = d;
                 v[t] = (dg_dist_key(d, key_scale) & ~IDMASK) | (uint32_t)e;
             }
         }
@@ -202,20 +357,70 @@ __device__ __forceinline__ bool dg_row_sort_bitonic(const RowBuf& sm, int m, int
         const int p1 = lane * EPL + r + 1;
         clash |= p1 < m && ((v[r] ^ w) & ~IDMASK) == 0u;
     }
-    if (__any_sync(FULL_MASK, clash)) return false;
-    // transpose through shared memory so that the CSR stores are coalesced
+    clash = __any_sync(FULL_MASK, clash);
+    // transpose through shared memory: coalesced CSR stores, and the run scan below needs random access
 #pragma unroll
-    for (int r = 0; r < EPL; ++r) sm.ord[lane * EPL + r] = (unsigned short)(v[r] & IDMASK);
+    for (int r = 0; r < EPL; ++r)
+        if (lane * EPL + r < m) sk[lane * EPL + r] = v[r];
     __syncwarp();
-    for (int p = lane; p < keep; p += 32) {
-        const int e = sm.ord[p];
-        const double d = sm.rd[e];
-        dst[o + p] = sm.rj[e];
-        image[o + p] = sm.rn[e];
-        dist[o + p] = d;
-        sm.fd[p] = (float)d;
+    if (!clash) {
+        for (int p = lane; p < keep; p += 32) {
+            const int e = (int)(sk[p] & IDMASK);
+            const double d = rd[e];
+            int j;
+            uint32_t img;
+            P.get(e, j, img);
+            dst[o + p] = j;
+            image[o + p] = img;
+            dist[o + p] = d;
+            fd[p] = (float)d;
+        }
+    } else {
+        for (int p = lane; p < m; p += 32) {
+            const uint32_t w = sk[p];
+            const uint32_t tk = w & ~IDMASK;
+            const int e = (int)(w & IDMASK);
+            const double de = rd[e];
+            int s = p, t = p + 1;
+            while (s > 0 && (sk[s - 1] & ~IDMASK) == tk) --s;
+            while (t < m && (sk[t] & ~IDMASK) == tk) ++t;
+            int rank = p;
+            if (t - s > 1) {  // run of equal truncated keys: exact canonical rank inside it
+                const unsigned long long ke = dg_payload_tie_key(P, e);
+                rank = s;
+                for (int q = s; q < t; ++q) {
+                    if (q == p) continue;
+                    const int f = (int)(sk[q] & IDMASK);
+                    const double df = rd[f];
+                    if (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ++rank;
+                }
+            }
+            if (rank < keep) {
+                int j;
+                uint32_t img;
+                P.get(e, j, img);
+                dst[o + rank] = j;
+                image[o + rank] = img;
+                dist[o + rank] = de;
+                fd[rank] = (float)de;
+            }
+            if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+        }
+        if (m > keep && keep > 0) {  // truncated through a distance tie?  (statistic of rule R8)
+            __syncwarp();
+            if (lane == 0 && rd[tie[0]] == rd[tie[1]]) atomicAdd(&stats->n_tie_rows, 1);
+        }
     }
-    return true;
+    __syncwarp();
+}
+
+template <class Payload>
+__device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk, float* fd, int* tie, const Payload& P,
+                                                        int m, int keep, double key_scale, long long o, int* dst,
+                                                        uint32_t* image, double* dist, DgStats* stats, int lane) {
+    if (m <= 128) dg_row_sort_bitonic<4>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
+    else if (m <= 256) dg_row_sort_bitonic<8>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
+    else dg_row_sort_bitonic<16>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
 }
 
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
@@ -225,22 +430,14 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
                                                  double key_scale, long long o, int* __restrict__ dst,
                                                  uint32_t* __restrict__ image, double* __restrict__ dist,
                                                  DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
-    bool have_dist = false;  // rd[] holds distances (the fast path converted them before giving up)
-    if (m <= 32 * 16 && m <= DG_BITONIC_MAX) {
-        bool done;
-        if (m <= 128) done = dg_row_sort_bitonic<4>(sm, m, keep, key_scale, o, dst, image, dist, lane);
-        else if (m <= 256) done = dg_row_sort_bitonic<8>(sm, m, keep, key_scale, o, dst, image, dist, lane);
-        else done = dg_row_sort_bitonic<16>(sm, m, keep, key_scale, o, dst, image, dist, lane);
-        if (done) {
+    if (m <= DG_BITONIC_MAX) {
+        const RowBufPayload P{sm.rj, sm.rn};
+        dg_row_sort_bitonic_any(sm.rd, sm.sk, sm.fd, sm.cnt, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
+        if (rbf.K4 > 0) {
+            dg_rbf_row(sm.fd, keep, o, lane, rbf);
             __syncwarp();
-            if (rbf.K4 > 0) {
-                dg_rbf_row(sm.fd, keep, o, lane, rbf);
-                __syncwarp();
-            }
-            return;
         }
-        have_dist = true;
-        __syncwarp();
+        return;
     }
     const int per = NBk >> 5;
     const int lper = 31 - __clz(per);
@@ -251,8 +448,7 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
     // ---- A: distance, key, bucket histogram ----
     const float scale = (float)NBk;
     for (int e = lane; e < m; e += 32) {
-        // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
-        const double d = have_dist ? sm.rd[e] : __dsqrt_rn(sm.rd[e]);
+        const double d = __dsqrt_rn(sm.rd[e]);  // Neighbor::distance = sqrt(match.second), neighbor_list.cpp:53
         sm.rd[e] = d;
         kk[e] = dg_dist_key(d, key_scale);
         const float t = (float)d * inv_rc;

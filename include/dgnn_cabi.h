@@ -49,7 +49,7 @@ enum {
     DGNN_ERR_UNSUPPORTED = -10
 };
 
-#define DGNN_MAX_DEGREE 8192
+#define DGNN_MAX_DEGREE 4096
 #define DGNN_UNCAPPED UINT64_MAX /* max_neighbors = SIZE_MAX: topology caller, betti_features.cpp:107 */
 
 /* dgnn_batch.flags */
@@ -133,7 +133,7 @@ typedef struct {
     int32_t n_cell_structs;  /* structures routed to the cell-list path (the rest took the direct path) */
     int32_t direct_warps;    /* warps per CTA of the direct fill pass */
     int32_t rbf_fused;       /* 1: features were written by the fill pass's fused epilogue (rbf_ms is then 0) */
-    int32_t reserved;
+    int32_t hit_cap;         /* per-row hit-list slots the count pass wrote (0: the fill pass repeated the traversal) */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 
@@ -141,7 +141,8 @@ int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 void* dgnn_stream(dgnn_ctx* ctx);
 
 /* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5);
- * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048). */
+ * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048);
+ * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off). */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus

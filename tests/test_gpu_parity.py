@@ -261,3 +261,25 @@ def test_determinism_and_symmetry_property(gpu_builder, oracle, syn):
     seg_start[h1.row_ptr[:-1][np.diff(h1.row_ptr) > 0]] = True
     dd = np.diff(h1.dist)
     assert np.all((dd >= 0) | seg_start[1:])
+
+
+@pytest.mark.parametrize("hit_cap", [-1, 0, 64, 160, 4096])
+def test_hit_list_and_traversal_fill_paths_agree(pkg, oracle, syn, hit_cap):
+    """The fill pass has two producers: the count pass's hit lists (k_fill_hits) and the repeated traversal
+    (k_direct<FILL>); rows that outgrow hit_cap take the latter.  Every split must give the same bit-exact graphs."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("hit_cap", hit_cap)
+    b = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=21)[:4], syn.triclinic_cell(3)[:4],
+                    syn.perovskite_supercell(3, 3, 3, seed=22)[:4], syn.triclinic_cell(5)[:4],
+                    syn.perovskite_supercell(4, 4, 4, seed=23)[:4]])
+    check_batch(gb, oracle, b, 8.0, None, dr=0.2)
+    info = gb.info()
+    assert info.hit_cap == (min(hit_cap, 512) if hit_cap >= 0 else info.hit_cap)
+    if hit_cap == 0:
+        assert info.hit_cap == 0
+    check_batch(gb, oracle, b, 10.0, 20, dr=0.1)
+    check_batch(gb, oracle, b, 5.0, 12)
+    gb.close()

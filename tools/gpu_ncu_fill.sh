@@ -1,13 +1,11 @@
 #!/bin/bash
-# ncu --set full of the dominant kernel only (k_direct, one count + one fill launch of a warmed-up bench run).
+# ncu --set full of the dominant kernels of a warmed-up bench run.  usage: gpu_ncu_fill.sh tag [kernel-regex] [skip] [count]
 set -u
-tag=${1:-run}
+tag=${1:-run}; rx=${2:-'^k_direct$|^k_fill_hits$'}; skip=${3:-6}; cnt=${4:-2}
 out=gpurun_out
 mkdir -p $out
 CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --e2e-steps 1"
 $CMD > $out/${tag}_plain.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k 'regex:^k_direct$' -s 6 -c 2 -f -o $out/${tag}_prof $CMD \
+ncu --set full --clock-control none --import-source on -k "regex:$rx" -s $skip -c $cnt -f -o $out/${tag}_prof $CMD \
     > $out/${tag}_ncu_full.log 2>&1
 echo "ncu full exit $?"
-bash tools/sweep.sh "fuse_rbf=1" "fuse_rbf=0" > $out/${tag}_sweep.log 2>&1
-cat $out/${tag}_sweep.log

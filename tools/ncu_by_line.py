@@ -23,10 +23,10 @@ print(f"{filt}: {ti} warp-instr, {ts} samples")
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:topn]:
     print(f"{k[0]:16s}:{k[1]:4d} instr {100*a[0]/ti:5.1f}% samp {100*a[1]/ts:5.1f}%  {a[2]}")
 # phase summary for the fill kernel (line ranges of row_sort.cuh / rbf_math.cuh / dgnn_direct.cu)
-PH = [("row_sort.cuh", 73, 112, "rbf epilogue"), ("row_sort.cuh", 113, 133, "sort: init"),
-      ("row_sort.cuh", 134, 146, "sort A: sqrt+key+histogram"), ("row_sort.cuh", 147, 165, "sort B: scan"),
-      ("row_sort.cuh", 166, 175, "sort C: bucket order"), ("row_sort.cuh", 176, 214, "sort D: rank+emit"),
-      ("row_sort.cuh", 215, 999, "rbf epilogue"),
+PH = [("row_sort.cuh", 73, 112, "rbf epilogue"), ("row_sort.cuh", 113, 150, "bitonic: sqrt+key"),
+      ("row_sort.cuh", 151, 195, "bitonic: network"), ("row_sort.cuh", 196, 205, "bitonic: clash check"),
+      ("row_sort.cuh", 206, 222, "bitonic: emit"), ("row_sort.cuh", 223, 250, "sort dispatch/init"),
+      ("row_sort.cuh", 251, 999, "counting sort (fallback)"),
       ("rbf_math.cuh", 0, 999, "rbf epilogue"), ("dgnn_direct.cu", 0, 9999, "traversal"), ("geom.h", 0, 9999, "traversal")]
 ph = collections.OrderedDict()
 for (f, l), a in agg.items():
