@@ -403,7 +403,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         // fill 9.1 ms + 0.8 ms in the count pass); capped or feature-less rows are 3-5x faster from the lists.
         const double keep_est = (double)(est < max_nb_for_est(b->max_neighbors) ? est : max_nb_for_est(b->max_neighbors));
         const double bytes_per_pair = est > 0 ? keep_est * (16.0 + 4.0 * K) / (double)est : 1e9;
-        if (est > 0 && bytes_per_pair < 64.0)
+        // ... and always for cell-list structures, whose tile-staged traversal is the expensive part
+        if (est > 0 && (bytes_per_pair < 64.0 || ctx->h_stats->n_cell_structs > 0))
             hit_cap = round_up((int)(est + est / 4 + 16 < DGNN_MAX_DEGREE ? est + est / 4 + 16 : DGNN_MAX_DEGREE), 32);
     }
     if (hit_cap > 512) hit_cap = 512;  // the hit-list fill pass sorts in registers: rows of up to 512 entries
@@ -466,7 +467,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
-    const int n_fallback_rows = ctx->h_stats->n_fallback_rows;
+    int n_fallback_rows = ctx->h_stats->n_fallback_rows;
 
     // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
     DgTraverseArgs A;
@@ -552,6 +553,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         A.near_hi_hi = near_hi_hi;
         A.max_neighbors = max_nb;
         A.deg_capped = (int*)ctx->deg.p;
+        A.deg_raw = (int*)ctx->deg_raw.p;
+        A.hits = D.hits;
+        A.hits_d2 = D.hits_d2;
+        A.hit_cap = hit_cap;
         A.stats = d_stats;
         // shared-memory plan: tile sized to the largest actual tile (bounded), rest goes the unstaged way
         int tile_cap = round_up(ctx->h_stats->max_tile_pts > 32 ? ctx->h_stats->max_tile_pts : 32, 32);
@@ -578,6 +583,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             int r = fetch_stats(ctx);  // sync: E and the largest row
             if (r != DGNN_OK) return r;
         }
+        n_fallback_rows = ctx->h_stats->n_fallback_rows;
     }
     CU(cudaEventRecord(ctx->ev.e[3], st));
     const long long E = ctx->h_stats->n_edges;
@@ -609,6 +615,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
     // rows with a stored hit list are filled from it; the traversal fill pass takes whatever is left
     DgDirectArgs H = D;
+    if (n_cell_structs > 0) {
+        H.cloud_j = (const int*)ctx->cj.p;
+        H.cloud_n = (const uint32_t*)ctx->cn.p;
+    }
     bool use_hits = hit_cap > 0;
     if (use_hits) {
         H.n_warps = 8;
@@ -619,7 +629,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
     if (E > 0 && (!use_hits || n_fallback_rows > 0))
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
-    if (n_cell_structs > 0 && E > 0) {
+    if (n_cell_structs > 0 && E > 0 && (!use_hits || n_fallback_rows > 0)) {
+        A.hit_cap = use_hits ? hit_cap : 0;
         A.row_ptr = (const long long*)ctx->row_ptr.p;
         A.dst = (int*)ctx->dst.p;
         A.image = (uint32_t*)ctx->image.p;

@@ -51,9 +51,8 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
     small[s] = G;
     if (G.status != DG_ST_OK) {
         if (atomicCAS(&stats->err_status, 0, G.status) == 0) stats->err_struct = (int)s;
-    } else if (G.mode == DG_MODE_CELL && G.natoms > 0) {
-        atomicAdd(&stats->n_cell_structs, 1);
     } else if (G.natoms > 0) {
+        if (G.mode == DG_MODE_CELL) atomicAdd(&stats->n_cell_structs, 1);
         // density estimate of the degree: N * (4/3) pi r^3 / V, V = h_0 h_1 h_2 / (the sines) >= rcm^3 / (w0 w1 w2)
         const double rcm = DG_RCM(r_cutoff);
         const double det = fabs(L[0] * (L[4] * L[8] - L[5] * L[7]) + L[1] * (L[5] * L[6] - L[3] * L[8]) +
@@ -472,13 +471,20 @@ __global__ void __launch_bounds__(256, 3) k_fill_hits(const DgDirectArgs A) {
         }
         const DgSmall* __restrict__ G = A.small + cur.s;
         const int m = cur.m;
-        // rows this pass does not own (cell-list structures, image range beyond the 5-bit fields, more hits than
-        // slots) are filled by the traversal pass
-        if (G->mode != DG_MODE_CELL && G->status == DG_ST_OK && G->nimg <= DG_HIT_NMAX && m <= W) {
+        // rows this pass does not own (image range beyond the 5-bit fields, more hits than slots) are filled by the
+        // traversal passes
+        const bool cell = G->mode == DG_MODE_CELL;
+        if (G->status == DG_ST_OK && m <= W && (cell ? A.cloud_j != nullptr : G->nimg <= DG_HIT_NMAX)) {
             const int keep = m < A.max_neighbors ? m : A.max_neighbors;
-            const HitWordPayload P{hw + buf * W};
-            dg_row_sort_bitonic_any(rd + buf * W, sk, fd, tie, P, m, keep, A.key_scale, cur.o, A.dst, A.image, A.dist,
-                                    A.stats, lane);
+            if (cell) {
+                const CloudPayload P{hw + buf * W, A.cloud_j, A.cloud_n};
+                dg_row_sort_bitonic_any(rd + buf * W, sk, fd, tie, P, m, keep, A.key_scale, cur.o, A.dst, A.image,
+                                        A.dist, A.stats, lane);
+            } else {
+                const HitWordPayload P{hw + buf * W};
+                dg_row_sort_bitonic_any(rd + buf * W, sk, fd, tie, P, m, keep, A.key_scale, cur.o, A.dst, A.image,
+                                        A.dist, A.stats, lane);
+            }
             if (A.rbf.K4 > 0) {
                 dg_rbf_row_bulk(fd, keep, cur.o, lane, A.rbf, stage, seq);
                 __syncwarp();

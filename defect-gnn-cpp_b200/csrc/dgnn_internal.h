@@ -60,6 +60,10 @@ struct DgTraverseArgs {
     int tile_cap, tcs_cap, src_cap, row_cap, n_buckets, n_warps;
     // outputs
     int* deg_capped;             // [N] (count pass)
+    int* deg_raw;                // [N] uncapped degrees
+    uint32_t* hits;              // [N * hit_cap] per-row hit lists (cloud point index of every accepted pair), or null
+    double* hits_d2;             // [N * hit_cap] their d2
+    int hit_cap;
     const long long* row_ptr;    // [N+1] (fill pass)
     int* dst;
     uint32_t* image;
@@ -124,6 +128,8 @@ struct DgDirectArgs {
     int* deg_raw;                // [N] uncapped degrees (count pass writes, fill passes read)
     uint32_t* hits;              // [N * hit_cap] per-row hit lists written by the count pass (dg_pack_hit), or null
     double* hits_d2;             // [N * hit_cap] the accepted pairs' d2 (bit-exact reference arithmetic)
+    const int* cloud_j;          // cell-list structures: hit word = cloud point index -> atom / packed image
+    const uint32_t* cloud_n;
     int hit_cap;                 // slots per row (0: no hit lists, the fill pass repeats the traversal)
     const long long* row_ptr;    // [N+1] (fill pass)
     int* dst;

@@ -428,6 +428,7 @@ struct Smem {
     uint32_t* tn;
     int* tcs;
     int* rowbase;
+    int* rowg;  // global cloud index of every tile row's first point (hit lists of the count pass)
     uint32_t* src;
     signed char* stn;
     RowBuf rb;  // per-warp (fill)
@@ -441,7 +442,7 @@ __host__ __device__ inline size_t warp_smem_bytes(int row_cap, int n_buckets) {
 
 __host__ __device__ inline size_t shared_part_bytes(int tile_cap, int tcs_cap, int src_cap) {
     return align16((size_t)tile_cap * 8) * 3 + align16((size_t)tile_cap * 4) * 2 + align16((size_t)tcs_cap * 4) +
-           align16((size_t)(DG_ROWS_CAP + 1) * 4) + align16((size_t)src_cap * 4) + align16((size_t)DG_STN_CAP * 2);
+           align16((size_t)(DG_ROWS_CAP + 1) * 4) * 2 + align16((size_t)src_cap * 4) + align16((size_t)DG_STN_CAP * 2);
 }
 
 size_t dg_traverse_smem_bytes(const DgTraverseArgs& a, bool fill) {
@@ -460,6 +461,7 @@ __device__ __forceinline__ Smem carve(unsigned char* base, const DgTraverseArgs&
     s.tn = (uint32_t*)p; p += align16((size_t)A.tile_cap * 4);
     s.tcs = (int*)p; p += align16((size_t)A.tcs_cap * 4);
     s.rowbase = (int*)p; p += align16((size_t)(DG_ROWS_CAP + 1) * 4);
+    s.rowg = (int*)p; p += align16((size_t)(DG_ROWS_CAP + 1) * 4);
     s.src = (uint32_t*)p; p += align16((size_t)A.src_cap * 4);
     s.stn = (signed char*)p; p += align16((size_t)DG_STN_CAP * 2);
     s.rb = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
@@ -492,6 +494,10 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
     const unsigned lt_mask = (1u << lane) - 1u;
     const int NBr = 2 * G.R[1] + 1;
     const int nst = (2 * G.R[0] + 1) * NBr;
+    // rows the hit-list fill pass owns are skipped by the traversal fill pass
+    if (FILL && A.hit_cap > 0 && A.deg_raw[iglob] <= A.hit_cap) return;
+    uint32_t* __restrict__ hrow = (!FILL && A.hits) ? A.hits + (size_t)iglob * (size_t)A.hit_cap : nullptr;
+    double* __restrict__ hd2 = (!FILL && A.hits) ? A.hits_d2 + (size_t)iglob * (size_t)A.hit_cap : nullptr;
     int m = 0;
     for (int q = 0; q < nst; ++q) {
         const int zlo = sm.stn[2 * q], zhi = sm.stn[2 * q + 1];
@@ -499,10 +505,13 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
         const int ra = ta + (q / NBr - G.R[0]);
         const int rb = tb + (q % NBr - G.R[1]);
         long long start, end;
+        long long gbase = 0;  // tile-local -> global cloud index (hit lists)
         if (STAGED) {
-            const int base = (ra * B.td[1] + rb) * (B.td[2] + 1) + tc;
+            const int r = ra * B.td[1] + rb;
+            const int base = r * (B.td[2] + 1) + tc;
             start = sm.tcs[base + zlo];
             end = sm.tcs[base + zhi + 1];
+            if (hrow != nullptr) gbase = (long long)sm.rowg[r] - (long long)sm.rowbase[r];
         } else {
             const long long g0 = G.cell_base + ((long long)(B.t0[0] + ra) * G.hd[1] + (B.t0[1] + rb)) * G.hd[2] +
                                  (B.t0[2] + tc + zlo);
@@ -538,6 +547,12 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
                         sm.rb.rn[pos] = pv.n[pc];
                     }
                 }
+            } else if (hrow != nullptr && hit) {  // hit list for the fill pass: global cloud index + d2
+                const int pos = m + __popc(mask & lt_mask);
+                if (pos < A.hit_cap) {
+                    hrow[pos] = (uint32_t)(gbase + pc);
+                    hd2[pos] = d2;
+                }
             }
             m += __popc(mask);
         }
@@ -545,7 +560,11 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
     acc.maxdeg = m > acc.maxdeg ? m : acc.maxdeg;
     const int keep = m < A.max_neighbors ? m : A.max_neighbors;
     if (!FILL) {
-        if (lane == 0) A.deg_capped[iglob] = keep;
+        if (lane == 0) {
+            A.deg_capped[iglob] = keep;
+            A.deg_raw[iglob] = m;
+            if (A.hits && m > A.hit_cap) atomicAdd(&A.stats->n_fallback_rows, 1);
+        }
         return;
     }
     if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
@@ -556,7 +575,7 @@ __device__ __forceinline__ void process_source(const DgTraverseArgs& A, const Dg
 }
 
 template <bool FILL>
-__global__ void __launch_bounds__(256) k_traverse(const DgTraverseArgs A) {
+__global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ DgGeom sG;
     __shared__ long long s_struct;
@@ -653,6 +672,7 @@ __global__ void __launch_bounds__(256) k_traverse(const DgTraverseArgs A) {
                 const long long g0 = G.cell_base + ((long long)(B.t0[0] + ra) * G.hd[1] + (B.t0[1] + rb)) * G.hd[2] + B.t0[2];
                 const long long gs = A.cellstart[g0];
                 const int lb = sm.rowbase[r], cnt = sm.rowbase[r + 1] - lb;
+                if (lane == 0) sm.rowg[r] = (int)gs;
                 for (int p = lane; p < cnt; p += 32) {
                     sm.tx[lb + p] = A.cx[gs + p];
                     sm.ty[lb + p] = A.cy[gs + p];

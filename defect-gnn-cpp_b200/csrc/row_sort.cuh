@@ -272,6 +272,16 @@ struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (d
         img = dg_pack_image((int)((v >> 17) & 31u) - 16, (int)((v >> 22) & 31u) - 16, (int)(v >> 27) - 16);
     }
 };
+struct CloudPayload {  // hit-list fill pass, cell-list structures: hit word = index into the binned image cloud
+    const uint32_t* hw;
+    const int* cj;
+    const uint32_t* cn;
+    __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
+        const uint32_t p = hw[e];
+        j = cj[p];
+        img = cn[p];
+    }
+};
 template <class Payload>
 __device__ __forceinline__ unsigned long long dg_payload_tie_key(const Payload& P, int e) {
     int j;
