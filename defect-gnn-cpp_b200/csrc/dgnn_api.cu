@@ -49,7 +49,7 @@ struct dgnn_ctx {
     double cell_frac = 0.5;
     int tile_target = 2048;
     int src_target = 512;
-    int tile_limit = 4096;
+    int tile_limit = 0;  // 0: candidates straight from the L2-resident cloud (faster than CTA-staged tiles: no barriers); > 0: stage tiles up to this many points
     int traverse_grid_mult = 16;
     int direct_max_atoms = 2048;
     int direct_min_blocks = 2;

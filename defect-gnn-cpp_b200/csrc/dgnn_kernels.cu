@@ -418,37 +418,42 @@ void dg_launch_item_stats(cudaStream_t st, long long n_items, long long S, const
 
 // =====================================================================================================================
 // K2: tile-staged pairwise distance traversal.  One CTA per work item: the item's neighbour tile (the cell-sorted
-// image points of its source block plus the stencil halo) is staged in shared memory; each warp takes source atoms,
-// sweeps the stencil rows with 32 candidates per step, and compacts in-cutoff pairs with ballot/popc.
-//   COUNT pass: row degrees.          FILL pass: row buffer -> sqrt -> bucket rank sort -> CSR arrays.
+// image points of its source block plus the stencil halo) is staged in shared memory.  A warp takes one source CELL at
+// a time: the cell's stencil (contiguous point ranges, one per stencil row) is flattened once into a per-warp candidate
+// list, and every source atom of the cell then sweeps that list 32 candidates per step at full lane occupancy,
+// compacting in-cutoff pairs with ballot/popc.
+//   COUNT pass: row degrees (+ the hit lists the fill pass sorts).     FILL pass: row buffer -> sort -> CSR arrays.
 // =====================================================================================================================
+#define DG_IDX_CAP 768   // candidate list entries per warp (a 5x5x5 stencil of r_c/2 cells holds ~500 points)
+#define DG_SRC_GROUP 64  // source points of one cell handled per sweep of the stencil
+
 struct Smem {
     double *tx, *ty, *tz;
     int* tj;
     uint32_t* tn;
+    uint32_t* tg;  // global cloud index of every tile point (hit lists of the count pass)
     int* tcs;
     int* rowbase;
-    int* rowg;  // global cloud index of every tile row's first point (hit lists of the count pass)
-    uint32_t* src;
     signed char* stn;
-    RowBuf rb;  // per-warp (fill)
+    uint32_t* idx;  // per-warp candidate list
+    int* msrc;      // per-warp running degrees of the current source group
+    RowBuf rb;      // per-warp (fill)
 };
 
 __host__ __device__ inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
 
-__host__ __device__ inline size_t warp_smem_bytes(int row_cap, int n_buckets) {
-    return dg_rowbuf_bytes(row_cap, n_buckets);
+__host__ __device__ inline size_t warp_smem_bytes(int row_cap, int n_buckets, bool fill) {
+    return align16((size_t)DG_IDX_CAP * 4) + align16((size_t)DG_SRC_GROUP * 4) +
+           (fill ? dg_rowbuf_bytes(row_cap, n_buckets) : 0);
 }
 
-__host__ __device__ inline size_t shared_part_bytes(int tile_cap, int tcs_cap, int src_cap) {
-    return align16((size_t)tile_cap * 8) * 3 + align16((size_t)tile_cap * 4) * 2 + align16((size_t)tcs_cap * 4) +
-           align16((size_t)(DG_ROWS_CAP + 1) * 4) * 2 + align16((size_t)src_cap * 4) + align16((size_t)DG_STN_CAP * 2);
+__host__ __device__ inline size_t shared_part_bytes(int tile_cap, int tcs_cap) {
+    return align16((size_t)tile_cap * 8) * 3 + align16((size_t)tile_cap * 4) * 3 + align16((size_t)tcs_cap * 4) +
+           align16((size_t)(DG_ROWS_CAP + 1) * 4) + align16((size_t)DG_STN_CAP * 2);
 }
 
 size_t dg_traverse_smem_bytes(const DgTraverseArgs& a, bool fill) {
-    size_t b = shared_part_bytes(a.tile_cap, a.tcs_cap, a.src_cap);
-    if (fill) b += (size_t)a.n_warps * warp_smem_bytes(a.row_cap, a.n_buckets);
-    return b;
+    return shared_part_bytes(a.tile_cap, a.tcs_cap) + (size_t)a.n_warps * warp_smem_bytes(a.row_cap, a.n_buckets, fill);
 }
 
 __device__ __forceinline__ Smem carve(unsigned char* base, const DgTraverseArgs& A, bool fill, int warp) {
@@ -459,13 +464,15 @@ __device__ __forceinline__ Smem carve(unsigned char* base, const DgTraverseArgs&
     s.tz = (double*)p; p += align16((size_t)A.tile_cap * 8);
     s.tj = (int*)p; p += align16((size_t)A.tile_cap * 4);
     s.tn = (uint32_t*)p; p += align16((size_t)A.tile_cap * 4);
+    s.tg = (uint32_t*)p; p += align16((size_t)A.tile_cap * 4);
     s.tcs = (int*)p; p += align16((size_t)A.tcs_cap * 4);
     s.rowbase = (int*)p; p += align16((size_t)(DG_ROWS_CAP + 1) * 4);
-    s.rowg = (int*)p; p += align16((size_t)(DG_ROWS_CAP + 1) * 4);
-    s.src = (uint32_t*)p; p += align16((size_t)A.src_cap * 4);
     s.stn = (signed char*)p; p += align16((size_t)DG_STN_CAP * 2);
-    s.rb = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
-    if (fill) s.rb = dg_rowbuf_carve(p + (size_t)warp * warp_smem_bytes(A.row_cap, A.n_buckets), A.row_cap);
+    p += (size_t)warp * warp_smem_bytes(A.row_cap, A.n_buckets, fill);
+    s.idx = (uint32_t*)p; p += align16((size_t)DG_IDX_CAP * 4);
+    s.msrc = (int*)p; p += align16((size_t)DG_SRC_GROUP * 4);
+    s.rb = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (fill) s.rb = dg_rowbuf_carve(p, A.row_cap);
     return s;
 }
 
@@ -475,6 +482,7 @@ struct PointView {
     const double *x, *y, *z;
     const int* j;
     const uint32_t* n;
+    const uint32_t* g;  // STAGED: tile point -> global cloud index
 };
 
 struct WarpAcc {
@@ -482,96 +490,178 @@ struct WarpAcc {
     int maxdeg;     // warp-uniform
 };
 
-// Process one source atom with a full warp.  p_src: index of the source's own (n = 0) point in the view.
-// (ta,tb,tc): its cell in tile coordinates.  Returns the uncapped degree.
-template <bool STAGED, bool FILL>
-__device__ __forceinline__ void process_source(const DgTraverseArgs& A, const DgGeom& G, const ItemBox& B,
-                                               const Smem& sm, const PointView<STAGED>& pv, long long p_src,
-                                               int ta, int tb, int tc, int lane, WarpAcc& acc) {
-    const double xi = pv.x[p_src], yi = pv.y[p_src], zi = pv.z[p_src];
-    const int iloc = pv.j[p_src];
-    const long long iglob = G.atom_base + iloc;
-    const unsigned lt_mask = (1u << lane) - 1u;
+// point range [s, e) of cells [z0, z1] of tile row (ra, rb) in view coordinates
+template <bool STAGED>
+__device__ __forceinline__ void row_range(const DgTraverseArgs& A, const DgGeom& G, const ItemBox& B, const Smem& sm,
+                                          int ra, int rb, int z0, int z1, long long& s, long long& e) {
+    if (STAGED) {
+        const int base = (ra * B.td[1] + rb) * (B.td[2] + 1);
+        s = sm.tcs[base + z0];
+        e = sm.tcs[base + z1 + 1];
+    } else {
+        const long long g0 = G.cell_base + ((long long)(B.t0[0] + ra) * G.hd[1] + (B.t0[1] + rb)) * G.hd[2] + B.t0[2];
+        s = A.cellstart[g0 + z0];
+        e = A.cellstart[g0 + z1 + 1];
+    }
+}
+
+// stencil cursor: row q of the (2R_a+1) x (2R_b+1) stencil, roff points of it already consumed
+struct StencilCursor {
+    int q;
+    long long roff;
+};
+
+// Append stencil ranges of the source cell (ta, tb, tc) to the warp's candidate list until it is full or the stencil
+// is exhausted.  Returns the number of candidates (0: done).
+template <bool STAGED>
+__device__ __forceinline__ int build_batch(const DgTraverseArgs& A, const DgGeom& G, const ItemBox& B, const Smem& sm,
+                                           int ta, int tb, int tc, int lane, StencilCursor& cur) {
     const int NBr = 2 * G.R[1] + 1;
     const int nst = (2 * G.R[0] + 1) * NBr;
-    // rows the hit-list fill pass owns are skipped by the traversal fill pass
-    if (FILL && A.hit_cap > 0 && A.deg_raw[iglob] <= A.hit_cap) return;
-    uint32_t* __restrict__ hrow = (!FILL && A.hits) ? A.hits + (size_t)iglob * (size_t)A.hit_cap : nullptr;
-    double* __restrict__ hd2 = (!FILL && A.hits) ? A.hits_d2 + (size_t)iglob * (size_t)A.hit_cap : nullptr;
-    int m = 0;
-    for (int q = 0; q < nst; ++q) {
-        const int zlo = sm.stn[2 * q], zhi = sm.stn[2 * q + 1];
-        if (zlo > zhi) continue;
-        const int ra = ta + (q / NBr - G.R[0]);
-        const int rb = tb + (q % NBr - G.R[1]);
-        long long start, end;
-        long long gbase = 0;  // tile-local -> global cloud index (hit lists)
-        if (STAGED) {
-            const int r = ra * B.td[1] + rb;
-            const int base = r * (B.td[2] + 1) + tc;
-            start = sm.tcs[base + zlo];
-            end = sm.tcs[base + zhi + 1];
-            if (hrow != nullptr) gbase = (long long)sm.rowg[r] - (long long)sm.rowbase[r];
-        } else {
-            const long long g0 = G.cell_base + ((long long)(B.t0[0] + ra) * G.hd[1] + (B.t0[1] + rb)) * G.hd[2] +
-                                 (B.t0[2] + tc + zlo);
-            start = A.cellstart[g0];
-            end = A.cellstart[g0 + (zhi - zlo) + 1];
+    int T = 0;
+    int qa = cur.q / NBr, qb = cur.q - qa * NBr;
+    while (cur.q < nst) {
+        const int zlo = sm.stn[2 * cur.q], zhi = sm.stn[2 * cur.q + 1];
+        if (zlo <= zhi) {
+            long long s, e;
+            row_range<STAGED>(A, G, B, sm, ta + qa - G.R[0], tb + qb - G.R[1], tc + zlo, tc + zhi, s, e);
+            s += cur.roff;
+            const long long len = e - s;
+            const int room = DG_IDX_CAP - T;
+            const int take = len < (long long)room ? (int)len : room;
+            for (int t = lane; t < take; t += 32) sm.idx[T + t] = (uint32_t)(s + t);
+            T += take;
+            if ((long long)take < len) {  // list full: resume inside this row
+                cur.roff += take;
+                break;
+            }
         }
-        for (long long pb = start; pb < end; pb += 32) {
-            const long long p = pb + lane;
-            const bool valid = p < end;
-            const long long pc = valid ? p : start;
-            const double dx = DG_SUB(xi, pv.x[pc]);
-            const double dy = DG_SUB(yi, pv.y[pc]);
-            const double dz = DG_SUB(zi, pv.z[pc]);
-            // nanoflann evalMetric: result = 0; result += dx*dx; += dy*dy; += dz*dz
-            const double d2 = DG_ADD(DG_ADD(DG_MUL(dx, dx), DG_MUL(dy, dy)), DG_MUL(dz, dz));
-            bool hit = valid && (d2 < A.r2);
-            if (hit && pv.j[pc] == iloc) {
-                if (__dsqrt_rn(d2) < A.epsilon) hit = false;  // neighbor_list.cpp:47-49
-            }
-            if (!FILL) {
-                const int hi = __double2hiint(d2);
-                if (valid && hi >= A.near_lo_hi && hi <= A.near_hi_hi) {
-                    if (fabs(__dsqrt_rn(d2) - A.r_cutoff) <= 1e-6) acc.near++;
-                }
-            }
-            const unsigned mask = __ballot_sync(FULL_MASK, hit);
-            if (FILL) {
-                if (hit) {
-                    const int pos = m + __popc(mask & lt_mask);
-                    if (pos < A.row_cap) {
-                        sm.rb.rd[pos] = d2;
-                        sm.rb.rj[pos] = pv.j[pc];
-                        sm.rb.rn[pos] = pv.n[pc];
-                    }
-                }
-            } else if (hrow != nullptr && hit) {  // hit list for the fill pass: global cloud index + d2
-                const int pos = m + __popc(mask & lt_mask);
-                if (pos < A.hit_cap) {
-                    hrow[pos] = (uint32_t)(gbase + pc);
-                    hd2[pos] = d2;
-                }
-            }
-            m += __popc(mask);
+        ++cur.q;
+        cur.roff = 0;
+        if (++qb == NBr) {
+            qb = 0;
+            ++qa;
         }
     }
-    acc.maxdeg = m > acc.maxdeg ? m : acc.maxdeg;
-    const int keep = m < A.max_neighbors ? m : A.max_neighbors;
-    if (!FILL) {
-        if (lane == 0) {
-            A.deg_capped[iglob] = keep;
+    __syncwarp();
+    return T;
+}
+
+// One source atom against the warp's candidate list idx[0, T).  m: running (uncapped) degree of the row.
+template <bool STAGED, bool FILL>
+__device__ __forceinline__ void sweep_list(const DgTraverseArgs& A, const Smem& sm, const PointView<STAGED>& pv, int T,
+                                           double xi, double yi, double zi, int iloc, uint32_t* __restrict__ hrow,
+                                           double* __restrict__ hd2, int lane, unsigned lt_mask, int& m,
+                                           WarpAcc& acc) {
+    for (int f0 = 0; f0 < T; f0 += 32) {
+        const int f = f0 + lane;
+        const bool valid = f < T;
+        const long long pc = sm.idx[valid ? f : 0];
+        const double dx = DG_SUB(xi, pv.x[pc]);
+        const double dy = DG_SUB(yi, pv.y[pc]);
+        const double dz = DG_SUB(zi, pv.z[pc]);
+        // nanoflann evalMetric: result = 0; result += dx*dx; += dy*dy; += dz*dz
+        const double d2 = DG_ADD(DG_ADD(DG_MUL(dx, dx), DG_MUL(dy, dy)), DG_MUL(dz, dz));
+        bool hit = valid && (d2 < A.r2);
+        if (hit && pv.j[pc] == iloc) {
+            if (__dsqrt_rn(d2) < A.epsilon) hit = false;  // neighbor_list.cpp:47-49
+        }
+        if (!FILL) {
+            const int hi = __double2hiint(d2);
+            if (valid && hi >= A.near_lo_hi && hi <= A.near_hi_hi) {
+                if (fabs(__dsqrt_rn(d2) - A.r_cutoff) <= 1e-6) acc.near++;
+            }
+        }
+        const unsigned mask = __ballot_sync(FULL_MASK, hit);
+        if (hit) {
+            const int pos = m + __popc(mask & lt_mask);
+            if (FILL) {
+                if (pos < A.row_cap) {
+                    sm.rb.rd[pos] = d2;
+                    sm.rb.rj[pos] = pv.j[pc];
+                    sm.rb.rn[pos] = pv.n[pc];
+                }
+            } else if (hrow != nullptr && pos < A.hit_cap) {  // hit list for the fill pass: cloud index + d2
+                hrow[pos] = STAGED ? pv.g[pc] : (uint32_t)pc;
+                hd2[pos] = d2;
+            }
+        }
+        m += __popc(mask);
+    }
+}
+
+// All source atoms of the block cell (ta, tb, tc) (tile coordinates).
+template <bool STAGED, bool FILL>
+__device__ __forceinline__ void process_cell(const DgTraverseArgs& A, const DgGeom& G, const ItemBox& B,
+                                             const Smem& sm, const PointView<STAGED>& pv, int ta, int tb, int tc,
+                                             int lane, WarpAcc& acc) {
+    long long p0, p1;
+    row_range<STAGED>(A, G, B, sm, ta, tb, tc, tc, p0, p1);
+    if (p0 >= p1) return;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int nst = (2 * G.R[0] + 1) * (2 * G.R[1] + 1);
+    if (FILL) {
+        // rows left to this pass are rare (hit-list overflow): one source at a time, rebuilding the list per batch
+        for (long long ps = p0; ps < p1; ++ps) {
+            if (pv.n[ps] != 0u) continue;  // a periodic image that shares the cell: not a source
+            const int iloc = pv.j[ps];
+            const long long iglob = G.atom_base + iloc;
+            if (A.hit_cap > 0 && A.deg_raw[iglob] <= A.hit_cap) continue;  // the hit-list fill pass owns this row
+            const double xi = pv.x[ps], yi = pv.y[ps], zi = pv.z[ps];
+            StencilCursor cur{0, 0};
+            int m = 0;
+            while (cur.q < nst) {
+                const int T = build_batch<STAGED>(A, G, B, sm, ta, tb, tc, lane, cur);
+                if (T == 0) break;
+                sweep_list<STAGED, true>(A, sm, pv, T, xi, yi, zi, iloc, nullptr, nullptr, lane, lt_mask, m, acc);
+                __syncwarp();
+            }
+            __syncwarp();
+            acc.maxdeg = m > acc.maxdeg ? m : acc.maxdeg;
+            const int keep = m < A.max_neighbors ? m : A.max_neighbors;
+            if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
+                if (lane == 0) atomicExch(&A.stats->overflow, 1);
+                continue;
+            }
+            dg_row_sort_emit(sm.rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[iglob], A.dst, A.image,
+                             A.dist, A.stats, lane, A.rbf);
+        }
+        return;
+    }
+    // COUNT: the stencil is flattened once per source group and shared by the group's atoms
+    for (long long g0 = p0; g0 < p1; g0 += DG_SRC_GROUP) {
+        const long long g1 = g0 + DG_SRC_GROUP < p1 ? g0 + DG_SRC_GROUP : p1;
+        for (int k = lane; k < (int)(g1 - g0); k += 32) sm.msrc[k] = 0;
+        __syncwarp();
+        StencilCursor cur{0, 0};
+        while (cur.q < nst) {
+            const int T = build_batch<STAGED>(A, G, B, sm, ta, tb, tc, lane, cur);
+            if (T == 0) break;
+            for (long long ps = g0; ps < g1; ++ps) {
+                if (pv.n[ps] != 0u) continue;
+                const int iloc = pv.j[ps];
+                const long long iglob = G.atom_base + iloc;
+                uint32_t* hrow = A.hits ? A.hits + (size_t)iglob * (size_t)A.hit_cap : nullptr;
+                double* hd2 = A.hits ? A.hits_d2 + (size_t)iglob * (size_t)A.hit_cap : nullptr;
+                int m = sm.msrc[ps - g0];
+                sweep_list<STAGED, false>(A, sm, pv, T, pv.x[ps], pv.y[ps], pv.z[ps], iloc, hrow, hd2, lane, lt_mask,
+                                          m, acc);
+                __syncwarp();
+                if (lane == 0) sm.msrc[ps - g0] = m;
+            }
+            __syncwarp();
+        }
+        for (long long ps = g0 + lane; ps < g1; ps += 32) {
+            if (pv.n[ps] != 0u) continue;
+            const long long iglob = G.atom_base + pv.j[ps];
+            const int m = sm.msrc[ps - g0];
+            A.deg_capped[iglob] = m < A.max_neighbors ? m : A.max_neighbors;
             A.deg_raw[iglob] = m;
             if (A.hits && m > A.hit_cap) atomicAdd(&A.stats->n_fallback_rows, 1);
+            acc.maxdeg = m > acc.maxdeg ? m : acc.maxdeg;  // per lane here; reduced at the end of the kernel
         }
-        return;
+        __syncwarp();
     }
-    if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
-        if (lane == 0) atomicExch(&A.stats->overflow, 1);
-        return;
-    }
-    dg_row_sort_emit(sm.rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[iglob], A.dst, A.image, A.dist, A.stats, lane, A.rbf);
 }
 
 template <bool FILL>
@@ -579,7 +669,7 @@ __global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ DgGeom sG;
     __shared__ long long s_struct;
-    __shared__ int s_T, s_nsrc, s_staged, s_maxdeg;
+    __shared__ int s_staged, s_maxdeg;
     __shared__ unsigned s_near;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -602,7 +692,6 @@ __global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
             int* dstw = reinterpret_cast<int*>(&sG);
             for (int i = tid; i < (int)(sizeof(DgGeom) / 4); i += nthreads) dstw[i] = src[i];
         }
-        if (tid == 0) s_nsrc = 0;
         __syncthreads();
         const DgGeom& G = sG;
         const ItemBox B = item_box(&G, (int)(item - G.item_base));
@@ -642,11 +731,10 @@ __global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
             const int total = __shfl_sync(FULL_MASK, inc, 31);
             if (lane == 0) {
                 sm.rowbase[nrows] = total;
-                s_T = total;
                 s_staged = (total <= A.tile_cap && tcs_need <= A.tcs_cap) ? 1 : 0;
             }
         }
-        // ---- stage 4 (independent): stencil row table ----
+        // ---- (independent) stencil row table ----
         {
             const int NBr = 2 * G.R[1] + 1;
             const int nst = (2 * G.R[0] + 1) * NBr;
@@ -664,69 +752,37 @@ __global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
 
         const int nbc0 = B.c1[0] - B.c0[0], nbc1 = B.c1[1] - B.c0[1], nbc2 = B.c1[2] - B.c0[2];
         const int nbcells = nbc0 * nbc1 * nbc2;
-
-        if (s_staged) {
+        const bool staged = s_staged != 0;
+        if (staged) {
             // ---- stage 2: copy the tile (cell-sorted image points) and its cell-start table ----
             for (int r = warp; r < nrows; r += nwarps) {
                 const int ra = r / B.td[1], rb = r % B.td[1];
                 const long long g0 = G.cell_base + ((long long)(B.t0[0] + ra) * G.hd[1] + (B.t0[1] + rb)) * G.hd[2] + B.t0[2];
                 const long long gs = A.cellstart[g0];
                 const int lb = sm.rowbase[r], cnt = sm.rowbase[r + 1] - lb;
-                if (lane == 0) sm.rowg[r] = (int)gs;
                 for (int p = lane; p < cnt; p += 32) {
                     sm.tx[lb + p] = A.cx[gs + p];
                     sm.ty[lb + p] = A.cy[gs + p];
                     sm.tz[lb + p] = A.cz[gs + p];
                     sm.tj[lb + p] = A.cj[gs + p];
                     sm.tn[lb + p] = A.cn[gs + p];
+                    sm.tg[lb + p] = (uint32_t)(gs + p);
                 }
                 for (int c = lane; c <= B.td[2]; c += 32)
                     sm.tcs[r * (B.td[2] + 1) + c] = lb + (int)(A.cellstart[g0 + c] - gs);
             }
             __syncthreads();
-            // ---- stage 3: source list = n = 0 points of the block's cells ----
+            PointView<true> pv{sm.tx, sm.ty, sm.tz, sm.tj, sm.tn, sm.tg};
             for (int bc = warp; bc < nbcells; bc += nwarps) {
                 const int c2 = bc % nbc2, c1 = (bc / nbc2) % nbc1, c0 = bc / (nbc2 * nbc1);
-                const int ta = c0 + G.R[0], tb = c1 + G.R[1], tc = c2 + G.R[2];
-                const int base = (ta * B.td[1] + tb) * (B.td[2] + 1) + tc;
-                const int p0 = sm.tcs[base], p1 = sm.tcs[base + 1];
-                for (int pb = p0; pb < p1; pb += 32) {
-                    const int p = pb + lane;
-                    const bool is_src = p < p1 && sm.tn[p] == 0u;
-                    const unsigned mask = __ballot_sync(FULL_MASK, is_src);
-                    int k0 = 0;
-                    if (lane == 0 && mask) k0 = atomicAdd(&s_nsrc, __popc(mask));
-                    k0 = __shfl_sync(FULL_MASK, k0, 0);
-                    if (is_src) {
-                        const int k = k0 + __popc(mask & ((1u << lane) - 1u));
-                        if (k < A.src_cap)
-                            sm.src[k] = (uint32_t)p | ((uint32_t)ta << 13) | ((uint32_t)tb << 18) | ((uint32_t)tc << 23);
-                    }
-                }
-            }
-            __syncthreads();
-        }
-        const bool staged = s_staged && s_nsrc <= A.src_cap;
-        if (staged) {
-            PointView<true> pv{sm.tx, sm.ty, sm.tz, sm.tj, sm.tn};
-            const int nsrc = s_nsrc;
-            for (int k = warp; k < nsrc; k += nwarps) {
-                const uint32_t v = sm.src[k];
-                process_source<true, FILL>(A, G, B, sm, pv, (long long)(v & 0x1fffu), (int)((v >> 13) & 31u),
-                                           (int)((v >> 18) & 31u), (int)((v >> 23) & 31u), lane, acc);
+                process_cell<true, FILL>(A, G, B, sm, pv, c0 + G.R[0], c1 + G.R[1], c2 + G.R[2], lane, acc);
             }
         } else {
             // ---- unstaged fallback: same traversal straight from the global cloud (L1/L2 cached) ----
-            PointView<false> pv{A.cx, A.cy, A.cz, A.cj, A.cn};
+            PointView<false> pv{A.cx, A.cy, A.cz, A.cj, A.cn, nullptr};
             for (int bc = warp; bc < nbcells; bc += nwarps) {
                 const int c2 = bc % nbc2, c1 = (bc / nbc2) % nbc1, c0 = bc / (nbc2 * nbc1);
-                const int ta = c0 + G.R[0], tb = c1 + G.R[1], tc = c2 + G.R[2];
-                const long long gc = G.cell_base + ((long long)(B.t0[0] + ta) * G.hd[1] + (B.t0[1] + tb)) * G.hd[2] + (B.t0[2] + tc);
-                const long long p0 = A.cellstart[gc], p1 = A.cellstart[gc + 1];
-                for (long long p = p0; p < p1; ++p) {
-                    if (A.cn[p] == 0u)
-                        process_source<false, FILL>(A, G, B, sm, pv, p, ta, tb, tc, lane, acc);
-                }
+                process_cell<false, FILL>(A, G, B, sm, pv, c0 + G.R[0], c1 + G.R[1], c2 + G.R[2], lane, acc);
             }
         }
     }
@@ -735,10 +791,11 @@ __global__ void __launch_bounds__(256, 2) k_traverse(const DgTraverseArgs A) {
         unsigned near = acc.near;
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) near += __shfl_xor_sync(FULL_MASK, near, o);
+        const int maxdeg = __reduce_max_sync(FULL_MASK, acc.maxdeg);
         __syncthreads();
         if (lane == 0) {
             if (near) atomicAdd(&s_near, near);
-            atomicMax(&s_maxdeg, acc.maxdeg);
+            atomicMax(&s_maxdeg, maxdeg);
         }
         __syncthreads();
         if (tid == 0) {

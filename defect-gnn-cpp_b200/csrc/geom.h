@@ -155,7 +155,12 @@ DG_HD void dg_geom_init(DgGeom* G, const double* L, int natoms, double r_cutoff,
             return;
         }
         const double h = 1.0 / cn;  // perpendicular height of the unit cell along axis k
-        double gf = floor(h / wt);
+        // target reach R_t = ceil(rcm / wt) cells; the widest grid that keeps it: cell width h / g >= rcm / R_t.
+        // (Dividing h by the target width instead lets a cell a hair below rcm / R_t push the reach to R_t + 1: 2.4x
+        // the stencil volume for a 236 A cell at r_c = 8 with 4 A cells.)
+        double rt = ceil(rcm / wt - 0.01);  // (the candidate margin in rcm must not add a cell to the reach)
+        if (rt < 1.0) rt = 1.0;
+        double gf = floor(h * rt / rcm);
         if (gf < 1.0) gf = 1.0;
         if (gf > 1024.0) gf = 1024.0;
         G->g[k] = (int)gf;

@@ -47,6 +47,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--only", default="")
+    ap.add_argument("--opt", action="append", default=[], help="name=value for dgnn_set_option")
     args = ap.parse_args()
     import torch
     pkg = entry.load_package()
@@ -56,6 +57,9 @@ def main():
     except Exception:
         peak = 6650.0
     gb = pkg.GraphBuilder(0)
+    for kv in args.opt:
+        k, v = kv.split("=")
+        gb.set_option(k, float(v))
     want = set(args.only.split(",")) if args.only else None
     def on(n):
         return want is None or n in want
