@@ -277,7 +277,9 @@ def main():
         # distance (8) + K fp32 features; inputs (positions) are < 0.1 % of that
         top_ms = statistics.mean(i.fill_ms for i in infos)
         top_bytes = E * (4 * K_BINS + 16)
-        top_name = "k_direct<FILL> (pair test + ballot compaction + in-warp row sort + fused Gaussian RBF write)"
+        top_name = ("k_direct<ONE> single-pass build (pair test + ballot compaction + look-back row offsets + in-warp row "
+                    "sort + CSR write + fused Gaussian RBF write)" if infos[-1].onepass else
+                    "k_direct<FILL> (pair test + ballot compaction + in-warp row sort + fused Gaussian RBF write)")
     else:
         top_ms = statistics.mean(i.rbf_ms for i in infos)
         top_bytes = E * (4 * K_BINS + 8)  # algorithmic: fp64 distance in, K fp32 out per edge
@@ -308,6 +310,8 @@ def main():
                 "note": "dgnn_build on pinned host SoA buffers + D2H of row_ptr and per-structure edge offsets; "
                         "graphs stay in HBM for the consumer"},
         "gpu_launches": launches,
+        "build": {"onepass": int(infos[-1].onepass), "onepass_fallback_rows": int(infos[-1].onepass_fallback_rows),
+                  "rbf_fused": int(infos[-1].rbf_fused), "row_cap": int(infos[-1].row_cap)},
         "clocks": clocks,
     }
 

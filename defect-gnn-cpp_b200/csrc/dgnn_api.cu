@@ -57,6 +57,10 @@ struct dgnn_ctx {
     int fuse_rbf = 1;
     int hit_cap_opt = -1;                 // -1: auto (density estimate), 0: off, > 0: fixed slots per row
     double hits_max_bytes = 16e9;         // no hit lists beyond this much scratch
+    int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
+    DevBuf lb_status;                     // per-row look-back status words of the single-pass build
+    int onepass_row_cap = 0;              // (testing) row buffer entries of the single-pass build, 0: density estimate
+    double onepass_arena_scale = 1.06;    // (testing) edge arena = scale * density estimate of the edge total
 };
 
 namespace {
@@ -240,7 +244,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
-                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats};
     for (DevBuf* b : bufs) release(*b);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
@@ -285,6 +289,15 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "hits_max_bytes")) {
         if (!(value >= 0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "hits_max_bytes out of range");
         ctx->hits_max_bytes = value;
+    } else if (!strcmp(name, "onepass")) {
+        if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass must be -1, 0 or 1");
+        ctx->onepass_opt = (int)value;  // single-pass build (look-back row offsets) instead of count + fill
+    } else if (!strcmp(name, "onepass_row_cap")) {
+        if (!(value >= 0 && value <= DGNN_MAX_DEGREE)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass_row_cap out of range");
+        ctx->onepass_row_cap = (int)value;
+    } else if (!strcmp(name, "onepass_arena_scale")) {
+        if (!(value > 0.0 && value <= 16.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass_arena_scale out of range");
+        ctx->onepass_arena_scale = value;
     } else if (!strcmp(name, "direct_max_atoms")) {
         if (!(value >= 0 && value <= 65535)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_max_atoms out of range");
         ctx->direct_max_atoms = (int)value;  // 0 sends every structure to the cell-list path
@@ -393,9 +406,13 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // traversal.  Slots per row come from the density estimate of the degree (rows that outgrow them, and structures
     // whose image range does not fit the 5-bit fields, are filled by the traversal pass instead).
     int hit_cap = ctx->hit_cap_opt > 0 ? round_up(ctx->hit_cap_opt, 32) : 0;  // rows stay 16-byte aligned
-    if (ctx->hit_cap_opt < 0 && N > 0) {
-        int r = fetch_stats(ctx);  // sync: density estimate
+    bool have_est = false;
+    if ((ctx->hit_cap_opt < 0 || ctx->onepass_opt != 0) && N > 0) {
+        int r = fetch_stats(ctx);  // sync: density estimate, classification, input errors
         if (r != DGNN_OK) return r;
+        have_est = true;
+    }
+    if (ctx->hit_cap_opt < 0 && N > 0) {
         const long long est = ctx->h_stats->est_deg;
         // Worth it only where the fill pass is bound by the traversal, not by the bytes it writes: the lists cost the
         // count pass ~35 % more time and the fill pass 12 B of extra reads per accepted pair.  Measured on C2: uncapped
@@ -404,7 +421,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         const double keep_est = (double)(est < max_nb_for_est(b->max_neighbors) ? est : max_nb_for_est(b->max_neighbors));
         const double bytes_per_pair = est > 0 ? keep_est * (16.0 + 4.0 * K) / (double)est : 1e9;
         // ... and always for cell-list structures, whose tile-staged traversal is the expensive part
-        if (est > 0 && (bytes_per_pair < 64.0 || ctx->h_stats->n_cell_structs > 0))
+        // (small direct-path batches take the single-pass build instead, see below)
+        const bool onepass_likely = ctx->onepass_opt > 0 ||
+                                    (ctx->onepass_opt < 0 && N <= (long long)ctx->sm_count * 2 * 8 * 2);
+        if (est > 0 && (ctx->h_stats->n_cell_structs > 0 || (bytes_per_pair < 64.0 && !onepass_likely)))
             hit_cap = round_up((int)(est + est / 4 + 16 < DGNN_MAX_DEGREE ? est + est / 4 + 16 : DGNN_MAX_DEGREE), 32);
     }
     if (hit_cap > 512) hit_cap = 512;  // the hit-list fill pass sorts in registers: rows of up to 512 entries
@@ -455,8 +475,68 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.hits_d2 = hit_cap > 0 ? (double*)ctx->hits_d2.p : nullptr;
     D.hit_cap = hit_cap;
     D.stats = d_stats;
-    CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
-    dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+    // ---- single-pass build (direct-path batches): traversal + look-back row offsets + sort + emit in one kernel --
+    // The edge arena and the row buffers are sized from the density estimate; rows that outgrow the buffer, or an
+    // arena that turns out too small, are completed by the regular fill pass afterwards (row_ptr is final either way).
+    bool onepass = false, onepass_fused_rbf = false;
+    int row_cap_1p = 0;
+    // Auto policy: the look-back couples every CTA to its predecessors with one step of slack, which costs large batches
+    // more than the count pass saves (C2 10 k structures: 11.8 ms vs 10.9 ms count + fill), but a batch of a few steps
+    // per CTA -- the reference's one-structure-per-call API above all -- finishes in one kernel and one sync less
+    // (9 shipped POSCARs: 0.31 ms vs 1.37 ms).
+    const long long onepass_auto_rows = (long long)ctx->sm_count * 2 * 8 * 2;  // two steps of a full grid
+    if (have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
+        ctx->h_stats->n_cell_structs == 0 &&
+        (ctx->onepass_opt > 0 || (N <= onepass_auto_rows && (hit_cap == 0 || ctx->hit_cap_opt < 0)))) {
+        const long long est = ctx->h_stats->est_deg;
+        long long rc = est + est / 8 + 8;
+        if (rc > DGNN_MAX_DEGREE) rc = DGNN_MAX_DEGREE;
+        if (ctx->onepass_row_cap > 0) rc = ctx->onepass_row_cap;
+        row_cap_1p = round_up((int)(rc > 32 ? rc : 32), 32);
+        double est_e = (double)ctx->h_stats->est_edges;
+        if (est_e > (double)N * (double)max_nb) est_e = (double)N * (double)max_nb;
+        est_e = est_e * ctx->onepass_arena_scale + (ctx->onepass_arena_scale >= 1.0 ? 64.0 * 1024.0 : 0.0);
+        DgDirectArgs O = D;
+        O.hit_cap = 0;
+        O.hits = nullptr;
+        O.hits_d2 = nullptr;
+        O.row_cap = row_cap_1p;
+        O.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap_1p <= 256 ? 256 : (row_cap_1p <= 1024 ? 512 : 1024));
+        O.n_warps = 8;
+        while (O.n_warps > 2 && (int)dg_direct_onepass_smem_bytes(O) > ctx->smem_optin) O.n_warps >>= 1;
+        // (an arena the device cannot hold fails in ENSURE with DGNN_ERR_OOM exactly as the two-pass build would: the
+        // estimate is within a few percent of the edge total the fill pass needs anyway)
+        if ((int)dg_direct_onepass_smem_bytes(O) <= ctx->smem_optin && est_e < 9.0e18) {
+            const size_t e_est = (size_t)est_e;
+            ENSURE(ctx->dst, (e_est + 1) * 4);
+            ENSURE(ctx->image, (e_est + 1) * 4);
+            ENSURE(ctx->dist, (e_est + 1) * 8);
+            if (want_rbf) ENSURE(ctx->rbf, e_est * (size_t)K * 4 + 16);
+            ENSURE(ctx->lb_status, (size_t)(N + 1) * 8);
+            size_t cap_e = ctx->dst.cap / 4;
+            if (ctx->image.cap / 4 < cap_e) cap_e = ctx->image.cap / 4;
+            if (ctx->dist.cap / 8 < cap_e) cap_e = ctx->dist.cap / 8;
+            if (want_rbf && (ctx->rbf.cap - 16) / ((size_t)K * 4) < cap_e) cap_e = (ctx->rbf.cap - 16) / ((size_t)K * 4);
+            O.edge_cap = (long long)cap_e - 1;
+            O.dst = (int*)ctx->dst.p;
+            O.image = (uint32_t*)ctx->image.p;
+            O.dist = (double*)ctx->dist.p;
+            O.lb_status = (unsigned long long*)ctx->lb_status.p;
+            O.row_ptr_out = (long long*)ctx->row_ptr.p;
+            const int keep_max_1p = row_cap_1p < max_nb ? row_cap_1p : max_nb;
+            onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 &&
+                                (long long)keep_max_1p * (K / 4) < (1LL << 22);
+            if (onepass_fused_rbf) O.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+            CU(cudaMemsetAsync(ctx->lb_status.p, 0, (size_t)(N + 1) * 8, st));
+            CU(cudaEventRecord(ctx->ev.e[3], st));
+            CU(dg_launch_direct_onepass(st, O, ctx->sm_count, ctx->direct_min_blocks));
+            onepass = true;
+        }
+    }
+    if (!onepass) {
+        CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+        dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+    }
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
     CU(cudaGetLastError());
     {
@@ -466,8 +546,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (ctx->h_stats->err_status != 0)
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
+    if (ctx->h_stats->lb_timeout) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
     int n_fallback_rows = ctx->h_stats->n_fallback_rows;
+    const bool onepass_redo_all = onepass && ctx->h_stats->cap_overflow != 0;
 
     // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
     DgTraverseArgs A;
@@ -585,7 +667,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         n_fallback_rows = ctx->h_stats->n_fallback_rows;
     }
-    CU(cudaEventRecord(ctx->ev.e[3], st));
+    if (!onepass) CU(cudaEventRecord(ctx->ev.e[3], st));
     const long long E = ctx->h_stats->n_edges;
     const int max_deg = ctx->h_stats->max_deg;
     if (max_deg > DGNN_MAX_DEGREE)
@@ -606,8 +688,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.n_warps = 8;
     // fused RBF epilogue: rows stream their K features right after the sort (needs K % 4 == 0 for the float4 stores)
     const int keep_max = max_deg < max_nb ? max_deg : max_nb;
-    const bool fuse_rbf = want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
-                          (long long)keep_max * (K / 4) < (1LL << 22);
+    const bool fuse_rbf = onepass ? (onepass_fused_rbf && E > 0)
+                                  : (want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
+                                     (long long)keep_max * (K / 4) < (1LL << 22));
     if (want_rbf && E > 0) ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
     if (fuse_rbf) D.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
     while (D.n_warps > 1 && (int)dg_direct_smem_bytes(D, true) > ctx->smem_optin) D.n_warps >>= 1;
@@ -619,7 +702,15 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         H.cloud_j = (const int*)ctx->cj.p;
         H.cloud_n = (const uint32_t*)ctx->cn.p;
     }
-    bool use_hits = hit_cap > 0;
+    bool use_hits = hit_cap > 0 && !onepass;
+    if (onepass) {
+        // everything is already written, except rows that outgrew the estimated row buffer (or all rows, when the
+        // estimated arena was too small and has just been regrown by the ENSUREs above)
+        D.hit_cap = 0;
+        D.skip_deg_le = onepass_redo_all ? 0 : row_cap_1p;
+        if (E > 0 && (onepass_redo_all || n_fallback_rows > 0))
+            CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+    }
     if (use_hits) {
         H.n_warps = 8;
         while (H.n_warps > 1 && (int)dg_fill_hits_smem_bytes(H) > ctx->smem_optin) H.n_warps >>= 1;
@@ -627,7 +718,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     if (!use_hits) D.hit_cap = 0;
     if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
-    if (E > 0 && (!use_hits || n_fallback_rows > 0))
+    if (E > 0 && !onepass && (!use_hits || n_fallback_rows > 0))
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
     if (n_cell_structs > 0 && E > 0 && (!use_hits || n_fallback_rows > 0)) {
         A.hit_cap = use_hits ? hit_cap : 0;
@@ -693,6 +784,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.direct_warps = D.n_warps;
     I.rbf_fused = fuse_rbf ? 1 : 0;
     I.hit_cap = use_hits ? hit_cap : 0;
+    I.onepass = onepass ? (onepass_redo_all ? 2 : 1) : 0;
+    I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
     return DGNN_OK;
 }
 

@@ -23,6 +23,9 @@ struct DgStats {
     int n_cell_structs;          // non-empty structures routed to the cell-list path
     int n_fallback_rows;         // direct-path rows whose hit list was not stored (degree > hit_cap or image range > 15)
     int est_deg;                 // density estimate of the largest degree (sizes the hit lists of a ctx's first build)
+    int cap_overflow;            // single-pass build: a row did not fit the (estimated) edge arena -> rerun as two passes
+    int lb_timeout;              // single-pass build: a look-back spin gave up (must not happen: all CTAs are resident)
+    unsigned long long est_edges;  // density estimate of the edge total, sum over structures of N_s * est_deg_s
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -137,6 +140,13 @@ struct DgDirectArgs {
     double* dist;
     DgStats* stats;
     DgRbfEpi rbf;
+    // single-pass build (k_direct<ONE>): traversal, row offsets by decoupled look-back over per-row status words, sort,
+    // emit -- no count pass.  Rows with more than row_cap hits only reserve their range (a fill pass with
+    // skip_deg_le = that row_cap completes them); rows ending beyond edge_cap set stats->cap_overflow.
+    unsigned long long* lb_status;  // [N] zeroed before the launch: flag (2 bits) | value (62 bits)
+    long long* row_ptr_out;         // [N+1]
+    long long edge_cap;             // edges the output arrays can hold
+    int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -150,6 +160,8 @@ void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long
                            double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
+size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
+cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 // fill pass from the count pass's hit lists (rows with degree <= hit_cap and image range <= DG_HIT_NMAX)
 size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a);
 cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_count);

@@ -292,13 +292,21 @@ __device__ __forceinline__ unsigned long long dg_payload_tie_key(const Payload& 
 
 // rd: d2 by entry (replaced by the distance), sk: scratch for the sorted words, fd: distances in final order (fp32),
 // tie: two ints of scratch.  All 32 lanes must call; m <= 32 * EPL.
-template <int EPL, class Payload>
-__device__ __forceinline__ void dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
-                                                    float* __restrict__ fd, int* __restrict__ tie, const Payload& P,
-                                                    int m, int keep, double key_scale, long long o,
-                                                    int* __restrict__ dst, uint32_t* __restrict__ image,
-                                                    double* __restrict__ dist, DgStats* __restrict__ stats,
-                                                    int lane) {
+// Where a row's edges go.  The two-pass builds know the offset up front (row_ptr from the scan); the single-pass build
+// learns it from the look-back while the row is being sorted, so the sort asks for it only when it starts to emit.
+// get() is called exactly once per row by all 32 lanes; a negative offset means "do not emit this row".
+struct DgFixedOffset {
+    long long o;
+    __device__ __forceinline__ long long get(int) { return o; }
+};
+
+template <int EPL, class Payload, class OP>
+__device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
+                                                         float* __restrict__ fd, int* __restrict__ tie,
+                                                         const Payload& P, int m, int keep, double key_scale, OP& op,
+                                                         int* __restrict__ dst, uint32_t* __restrict__ image,
+                                                         double* __restrict__ dist, DgStats* __restrict__ stats,
+                                                         int lane) {
     constexpr uint32_t IDMASK = 32u * EPL - 1u;
     uint32_t v[EPL];
 #pragma unroll
@@ -373,6 +381,8 @@ __device__ __forceinline__ void dg_row_sort_bitonic(double* __restrict__ rd, uin
     for (int r = 0; r < EPL; ++r)
         if (lane * EPL + r < m) sk[lane * EPL + r] = v[r];
     __syncwarp();
+    const long long o = op.get(keep);
+    if (o < 0) return o;
     if (!clash) {
         for (int p = lane; p < keep; p += 32) {
             const int e = (int)(sk[p] & IDMASK);
@@ -422,33 +432,46 @@ __device__ __forceinline__ void dg_row_sort_bitonic(double* __restrict__ rd, uin
         }
     }
     __syncwarp();
+    return o;
 }
 
+template <class Payload, class OP>
+__device__ __forceinline__ long long dg_row_sort_bitonic_any_op(double* rd, uint32_t* sk, float* fd, int* tie,
+                                                                const Payload& P, int m, int keep, double key_scale,
+                                                                OP& op, int* dst, uint32_t* image, double* dist,
+                                                                DgStats* stats, int lane) {
+    if (m <= 128) return dg_row_sort_bitonic<4>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    if (m <= 256) return dg_row_sort_bitonic<8>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    return dg_row_sort_bitonic<16>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+}
 template <class Payload>
 __device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk, float* fd, int* tie, const Payload& P,
                                                         int m, int keep, double key_scale, long long o, int* dst,
                                                         uint32_t* image, double* dist, DgStats* stats, int lane) {
-    if (m <= 128) dg_row_sort_bitonic<4>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
-    else if (m <= 256) dg_row_sort_bitonic<8>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
-    else dg_row_sort_bitonic<16>(rd, sk, fd, tie, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
+    DgFixedOffset op{o};
+    dg_row_sort_bitonic_any_op(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
 }
 
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
 // NBk (number of buckets) is a power of two, 32 <= NBk <= 2048.  All 32 lanes must call.
 // rbf.K4 > 0: fused Gaussian RBF epilogue straight from the sorted distances in shared memory.
-__device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
-                                                 double key_scale, long long o, int* __restrict__ dst,
-                                                 uint32_t* __restrict__ image, double* __restrict__ dist,
-                                                 DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
+template <class OP>
+__device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
+                                                    double key_scale, OP& op, int* __restrict__ dst,
+                                                    uint32_t* __restrict__ image, double* __restrict__ dist,
+                                                    DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     if (m <= DG_BITONIC_MAX) {
         const RowBufPayload P{sm.rj, sm.rn};
-        dg_row_sort_bitonic_any(sm.rd, sm.sk, sm.fd, sm.cnt, P, m, keep, key_scale, o, dst, image, dist, stats, lane);
-        if (rbf.K4 > 0) {
+        const long long o = dg_row_sort_bitonic_any_op(sm.rd, sm.sk, sm.fd, sm.cnt, P, m, keep, key_scale, op, dst,
+                                                       image, dist, stats, lane);
+        if (o >= 0 && rbf.K4 > 0) {
             dg_rbf_row(sm.fd, keep, o, lane, rbf);
             __syncwarp();
         }
         return;
     }
+    const long long o = op.get(keep);
+    if (o < 0) return;
     const int per = NBk >> 5;
     const int lper = 31 - __clz(per);
     const int nwords = NBk + 32 + 1;
@@ -540,4 +563,12 @@ __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int ke
         dg_rbf_row(sm.fd, keep, o, lane, rbf);
         __syncwarp();
     }
+}
+
+__device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
+                                                 double key_scale, long long o, int* __restrict__ dst,
+                                                 uint32_t* __restrict__ image, double* __restrict__ dist,
+                                                 DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
+    DgFixedOffset op{o};
+    dg_row_sort_emit_op(sm, m, keep, NBk, inv_rc, key_scale, op, dst, image, dist, stats, lane, rbf);
 }

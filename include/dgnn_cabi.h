@@ -134,6 +134,9 @@ typedef struct {
     int32_t direct_warps;    /* warps per CTA of the direct fill pass */
     int32_t rbf_fused;       /* 1: features were written by the fill pass's fused epilogue (rbf_ms is then 0) */
     int32_t hit_cap;         /* per-row hit-list slots the count pass wrote (0: the fill pass repeated the traversal) */
+    int32_t onepass;         /* 1: single-pass build (no count pass; row offsets by look-back), 2: its estimated edge
+                              * arena was too small and the fill pass rewrote every row, 0: count + fill */
+    int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 
@@ -142,7 +145,9 @@ void* dgnn_stream(dgnn_ctx* ctx);
 
 /* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5);
  * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048);
- * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off). */
+ * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off);
+ * onepass: single-pass build (no count pass) of batches without cell-list structures: -1 auto (small batches),
+ * 0 off (count + fill), 1 wherever legal. */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus

@@ -53,7 +53,8 @@ def test_c2_perovskite_batch_uncapped_with_rbf(gpu_builder, oracle, syn):
     h = check_batch(gpu_builder, oracle, b, 8.0, None, dr=0.2)
     assert h.K == 40 and h.n_edges > 24 * 25_000
     info = gpu_builder.info()
-    assert info.n_cell_structs == 0 and info.kernel_launches >= 7     # supercells take the direct path
+    assert info.n_cell_structs == 0 and info.kernel_launches >= 4     # supercells take the direct path
+    assert info.onepass == 1                                           # small batch: single-pass build
 
 
 def test_c2_perovskite_batch_cell_list_path(gpu_builder_cell, oracle, syn):
@@ -285,4 +286,42 @@ def test_hit_list_and_traversal_fill_paths_agree(pkg, oracle, syn, hit_cap):
         assert info.hit_cap == 0
     check_batch(gb, oracle, b, 10.0, 20, dr=0.1)
     check_batch(gb, oracle, b, 5.0, 12)
+    gb.close()
+
+
+@pytest.mark.parametrize("opts,expect", [
+    ({"onepass": 0, "hit_cap": 0}, 0),                       # count + traversal fill
+    ({"onepass": 0}, 0),                                      # count (+ hit lists where they pay) + fill
+    ({"onepass": 1}, 1),                                      # single pass, row buffer / arena from the density estimate
+    ({"onepass": 1, "onepass_row_cap": 64}, 1),               # most rows outgrow the row buffer -> completed by a fill pass
+    ({"onepass": 1, "onepass_arena_scale": 0.25}, 2),         # arena estimate too small -> every row rewritten
+    ({"onepass": 1, "direct_min_blocks": 3}, 1),
+])
+def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
+    """The single-pass build (k_direct<ONE>: look-back row offsets, no count pass) and its two recovery routes must
+    give the same bit-exact CSR, statistics and features as count + fill."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    for k, v in opts.items():
+        gb.set_option(k, v)
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    b = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=31)[:4], none, syn.triclinic_cell(13)[:4],
+                    syn.perovskite_supercell(3, 3, 3, seed=32)[:4], syn.triclinic_cell(15)[:4], none,
+                    syn.perovskite_supercell(4, 4, 4, seed=33)[:4], syn.perovskite_supercell(2, 2, 2, seed=34)[:4]])
+    check_batch(gb, oracle, b, 8.0, None, dr=0.2)
+    info = gb.info()
+    assert info.onepass == expect
+    if opts.get("onepass_row_cap"):
+        assert info.onepass_fallback_rows > 0
+    check_batch(gb, oracle, b, 10.0, 20, dr=0.1)           # capped rows, K = 100
+    check_batch(gb, oracle, b, 8.0, None, dr=0.3)           # K = 26: separate RBF launch (no float4 epilogue)
+    check_batch(gb, oracle, b, 5.0, 12)                     # no features
+    check_batch(gb, oracle, b, 8.0, 1)
+    h0 = build_and_fetch(gb, b, 8.0, 0)
+    assert h0.n_edges == 0
+    # a larger homogeneous batch: many chunks per CTA, look-back across CTAs
+    big = syn.c2_batch(96, seed0=31000)
+    check_batch(gb, oracle, big, 8.0, None, dr=0.2)
     gb.close()

@@ -36,7 +36,7 @@ def run(gb, torch, name, b, rc, cap, dr, reps, peak):
             "whole_path_gbs": bytes_all / (ms * 1e-3) / 1e9, "frac_of_measured_peak": bytes_all / (ms * 1e-3) / 1e9 / peak,
             "phases_ms": {k: statistics.median(getattr(i, k) for i in infos)
                           for k in ("bin_ms", "count_ms", "fill_ms", "rbf_ms")},
-            "launches": infos[-1].kernel_launches, "cell_list_structs": infos[-1].n_cell_structs,
+            "launches": infos[-1].kernel_launches, "onepass": infos[-1].onepass, "onepass_fallback_rows": infos[-1].onepass_fallback_rows, "hit_cap": infos[-1].hit_cap, "cell_list_structs": infos[-1].n_cell_structs,
             "max_degree": int(g.max_degree), "near_cutoff_pairs": int(g.n_near_cutoff), "tie_rows": int(g.n_tie_rows)}
     print(json.dumps(line), flush=True)
     del t
@@ -72,6 +72,30 @@ def main():
         b1 = syn.concat(parts)
         run(gb, torch, "C1 9 shipped POSCARs, reference defaults r_c=10 cap=20 dr=0.1", b1, 10.0, 20, 0.1, args.reps, peak)
         run(gb, torch, "C1 9 shipped POSCARs, topology caller r_c=10 uncapped dr=0.1", b1, 10.0, UNCAPPED, 0.1, args.reps, peak)
+        # the reference API's own shape: one structure per call (NeighborList + CrystalGraph constructors); wall clock
+        # per call through the C ABI with host inputs, H2D and all syncs included
+        import time
+        singles = [syn.concat([p]) for p in parts]
+        for onepass in (-1, 0):
+            gb.set_option("onepass", onepass)
+            for _ in range(3):
+                for b in singles:
+                    gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=10.0, max_neighbors=20, epsilon=1e-10,
+                             rbf_r_cutoff=10.0, dr=0.1)
+            t0 = time.perf_counter()
+            reps = 20
+            for _ in range(reps):
+                for b in singles:
+                    gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=10.0, max_neighbors=20, epsilon=1e-10,
+                             rbf_r_cutoff=10.0, dr=0.1)
+            dt = (time.perf_counter() - t0) / (reps * len(singles))
+            print(json.dumps({"config": "C1 one POSCAR per dgnn_build call (reference API shape), host inputs, wall clock",
+                              "onepass_option": onepass, "onepass": gb.info().onepass, "ms_per_call": dt * 1e3,
+                              "structures_per_sec": 1.0 / dt, "launches": gb.info().kernel_launches}), flush=True)
+        gb.set_option("onepass", -1)
+        for kv in args.opt:
+            k, v = kv.split("=")
+            gb.set_option(k, float(v))
         big = syn.concat(parts * 200)
         run(gb, torch, "C1 x200 (1800 POSCAR structures), reference defaults", big, 10.0, 20, 0.1, args.reps, peak)
     if on("C2cap"):
