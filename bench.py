@@ -70,7 +70,7 @@ class ClockSampler:
             fd, self.path = tempfile.mkstemp(prefix="clocks_", suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
@@ -171,6 +171,11 @@ def main():
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
         return run_reference(args, rank)
+
+    # stdout carries exactly one JSON line: anything libraries print there (NCCL's version banner ...) goes to stderr
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
 
     import torch
     import torch.distributed as dist
@@ -328,7 +333,8 @@ def main():
         line["cpu_baseline_1core"] = {"value": e1c / s1c, "unit": UNIT, "cores": 1, "kind": "port",
                                       "structures_per_sec": n1c / s1c, "sample": f"{n1c} C2 structures"}
     if rank == 0:
-        print(json.dumps(line))
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     gb.close()
     if multi:
         dist.destroy_process_group()
