@@ -23,6 +23,8 @@ EXPORTS = [
     "dgnn_abi_version", "dgnn_strerror", "dgnn_last_error", "dgnn_create", "dgnn_destroy", "dgnn_build",
     "dgnn_copy_to_host", "dgnn_copy_edges_to_host", "dgnn_rbf_expand", "dgnn_rbf_expand_f64",
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
+    "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
+    "dgnn_last_consumer_info",
 ]
 
 
@@ -72,6 +74,18 @@ class DgnnBuildInfo(C.Structure):
     ]
 
 
+class DgnnCollated(C.Structure):
+    _fields_ = [
+        ("n_nodes", C.c_int64), ("n_edges", C.c_int64), ("F", C.c_int32), ("K", C.c_int32),
+        ("x", C.c_void_p), ("edge_index", C.c_void_p), ("batch", C.c_void_p), ("edge_attr", C.c_void_p),
+    ]
+
+
+class DgnnConsumerInfo(C.Structure):
+    _fields_ = [("device_ms", C.c_float), ("kernel_launches", C.c_int32), ("bytes_read", C.c_int64),
+                ("bytes_written", C.c_int64)]
+
+
 class DgnnError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"dgnn error {code}: {msg}")
@@ -116,6 +130,18 @@ def load_library():
         L.dgnn_stream.restype = C.c_void_p
         L.dgnn_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
         L.dgnn_set_option.restype = C.c_int
+        L.dgnn_collate.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs), C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32,
+                                   C.c_int32, C.c_uint32, C.POINTER(DgnnCollated)]
+        L.dgnn_collate.restype = C.c_int
+        L.dgnn_copy_collated_to_host.argtypes = [C.c_void_p, C.POINTER(DgnnCollated)] + [C.c_void_p] * 3
+        L.dgnn_copy_collated_to_host.restype = C.c_int
+        L.dgnn_edge_views.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs)] + [C.c_void_p] * 4
+        L.dgnn_edge_views.restype = C.c_int
+        L.dgnn_neighborhood_clouds.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs), C.c_int64, C.c_int64, C.c_void_p,
+                                               C.c_void_p]
+        L.dgnn_neighborhood_clouds.restype = C.c_int
+        L.dgnn_last_consumer_info.argtypes = [C.c_void_p, C.POINTER(DgnnConsumerInfo)]
+        L.dgnn_last_consumer_info.restype = C.c_int
         _lib = L
     return _lib
 
@@ -249,3 +275,53 @@ class GraphBuilder:
         if f64_colmajor and isinstance(out, np.ndarray):
             return out.T  # column-major E x K viewed as E x K
         return out
+
+    # ---- consumers of the last build's CSR ----
+    def collate(self, node_keys=None, emb_keys=None, emb_table=None, g: DgnnGraphs | None = None,
+                device_keys: bool = False) -> DgnnCollated:
+        """dgnn_collate: PyG-style batch (x, edge_index, batch, edge_attr) left on the device."""
+        g = g or self.last
+        n_keys = F = 0
+        if emb_keys is not None:
+            emb_keys = np.ascontiguousarray(emb_keys, dtype=np.int32)
+            emb_table = np.ascontiguousarray(emb_table, dtype=np.float64)
+            n_keys, F = emb_table.shape
+            if isinstance(node_keys, np.ndarray):
+                node_keys = np.ascontiguousarray(node_keys, dtype=np.int32)
+        self._keep_c = (node_keys, emb_keys, emb_table)
+        out = DgnnCollated()
+        self._check(self.lib.dgnn_collate(self.h, C.byref(g), _ptr(node_keys), _ptr(emb_keys), _ptr(emb_table),
+                                          int(n_keys), int(F), INPUT_DEVICE if device_keys else 0, C.byref(out)))
+        return out
+
+    def collated_to_host(self, c: DgnnCollated):
+        x = np.empty((c.n_nodes, c.F), dtype=np.float32) if c.x else None
+        ei = np.empty((2, c.n_edges), dtype=np.int64)
+        batch = np.empty(c.n_nodes, dtype=np.int64)
+        self._check(self.lib.dgnn_copy_collated_to_host(self.h, C.byref(c), _ptr(x), _ptr(ei), _ptr(batch)))
+        return x, ei, batch
+
+    def edge_views(self, g: DgnnGraphs | None = None, displacements: bool = True):
+        """dgnn_edge_views: the viewer's flat arrays (sources, targets, distances, displacements)."""
+        g = g or self.last
+        e = int(g.n_edges)
+        src = np.empty(e, dtype=np.int32)
+        tgt = np.empty(e, dtype=np.int32)
+        dist = np.empty(e, dtype=np.float32)
+        disp = np.empty(3 * e, dtype=np.float32) if displacements else None
+        self._check(self.lib.dgnn_edge_views(self.h, C.byref(g), _ptr(src), _ptr(tgt), _ptr(dist), _ptr(disp)))
+        return src, tgt, dist, disp
+
+    def neighborhood_clouds(self, a0: int, a1: int, row_ptr: np.ndarray, g: DgnnGraphs | None = None):
+        """dgnn_neighborhood_clouds for the atoms [a0, a1); row_ptr (host) sizes the output."""
+        g = g or self.last
+        n_points = int(row_ptr[a1] - row_ptr[a0]) + (a1 - a0)
+        cloud = np.empty((n_points, 3), dtype=np.float64)
+        cptr = np.empty(a1 - a0 + 1, dtype=np.int64)
+        self._check(self.lib.dgnn_neighborhood_clouds(self.h, C.byref(g), int(a0), int(a1), _ptr(cloud), _ptr(cptr)))
+        return cloud, cptr
+
+    def consumer_info(self) -> DgnnConsumerInfo:
+        i = DgnnConsumerInfo()
+        self._check(self.lib.dgnn_last_consumer_info(self.h, C.byref(i)))
+        return i

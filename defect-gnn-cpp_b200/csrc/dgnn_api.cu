@@ -8,6 +8,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <vector>
 
 #include "../../include/dgnn_cabi.h"
 #include "dgnn_internal.h"
@@ -59,6 +60,17 @@ struct dgnn_ctx {
     double hits_max_bytes = 16e9;         // no hit lists beyond this much scratch
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
+    // the last successful build, for the CSR consumers (collation, viewer arrays, neighbourhood clouds)
+    struct {
+        bool valid = false;
+        long long S = 0, N = 0, E = 0;
+        const long long* off = nullptr;
+        const double *x = nullptr, *y = nullptr, *z = nullptr;
+    } last;
+    DevBuf col_x, col_ei, col_batch, col_keys, col_lut, col_table, col_err;  // dgnn_collate outputs / staging
+    DevBuf view_a, view_b;                                                    // edge views / clouds staging
+    dgnn_consumer_info cinfo{};
+    cudaEvent_t cev[2] = {nullptr, nullptr};
     int onepass_row_cap = 0;              // (testing) row buffer entries of the single-pass build, 0: density estimate
     double onepass_arena_scale = 1.06;    // (testing) edge arena = scale * density estimate of the edge total
 };
@@ -245,10 +257,13 @@ void dgnn_destroy(dgnn_ctx* ctx) {
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
                       &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
-                      &ctx->tmp_in, &ctx->tmp_out, &ctx->stats};
+                      &ctx->tmp_in, &ctx->tmp_out, &ctx->stats, &ctx->col_x, &ctx->col_ei, &ctx->col_batch, &ctx->col_keys,
+                      &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b};
     for (DevBuf* b : bufs) release(*b);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (auto& e : ctx->ev.e)
+        if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->cev)
         if (e) cudaEventDestroy(e);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -318,6 +333,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (!b || !out) return fail(ctx, DGNN_ERR_INVALID_ARG, "null batch / output");
     memset(out, 0, sizeof(*out));
     ctx->err.clear();
+    ctx->last.valid = false;
     const long long S = b->n_structs;
     if (S < 0) return fail(ctx, DGNN_ERR_INVALID_ARG, "n_structs < 0");
     if (!(b->r_cutoff > 0.0) || !std::isfinite(b->r_cutoff))
@@ -768,6 +784,11 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     out->n_near_cutoff = (int64_t)ctx->h_stats->n_near;
     out->n_tie_rows = ctx->h_stats->n_tie_rows;
 
+    ctx->last.valid = true;
+    ctx->last.S = S; ctx->last.N = N; ctx->last.E = E;
+    ctx->last.off = d_off;
+    ctx->last.x = d_x; ctx->last.y = d_y; ctx->last.z = d_z;
+
     dgnn_build_info& I = ctx->info;
     cudaEventElapsedTime(&I.h2d_ms, ctx->ev.e[0], ctx->ev.e[1]);
     cudaEventElapsedTime(&I.bin_ms, ctx->ev.e[1], ctx->ev.e[2]);
@@ -867,3 +888,193 @@ int dgnn_rbf_expand_f64(dgnn_ctx* ctx, const double* dist, int64_t n, double r_c
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------------
+// consumers of the last build's CSR (dgnn_collate.cu)
+// ---------------------------------------------------------------------------------------------------------------------
+namespace {
+int consumer_begin(dgnn_ctx* ctx, const dgnn_graphs* g, const char* who) {
+    if (!g) return fail(ctx, DGNN_ERR_INVALID_ARG, "%s: null graphs", who);
+    if (!ctx->last.valid || g->row_ptr != (const int64_t*)ctx->row_ptr.p || g->n_atoms != ctx->last.N ||
+        g->n_edges != ctx->last.E || g->n_structs != ctx->last.S)
+        return fail(ctx, DGNN_ERR_INVALID_ARG, "%s: graphs are not the result of the last dgnn_build on this context", who);
+    CU(cudaSetDevice(ctx->device));
+    for (auto& e : ctx->cev)
+        if (!e) CU(cudaEventCreate(&e));
+    memset(&ctx->cinfo, 0, sizeof(ctx->cinfo));
+    dg_collate_launch_count_reset();
+    return DGNN_OK;
+}
+int consumer_end(dgnn_ctx* ctx, long long bytes_read, long long bytes_written) {
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaEventElapsedTime(&ctx->cinfo.device_ms, ctx->cev[0], ctx->cev[1]);
+    ctx->cinfo.kernel_launches = dg_collate_launch_count_reset();
+    ctx->cinfo.bytes_read = bytes_read;
+    ctx->cinfo.bytes_written = bytes_written;
+    return DGNN_OK;
+}
+}  // namespace
+
+int dgnn_last_consumer_info(const dgnn_ctx* ctx, dgnn_consumer_info* out) {
+    if (!ctx || !out) return DGNN_ERR_INVALID_ARG;
+    *out = ctx->cinfo;
+    return DGNN_OK;
+}
+
+int dgnn_collate(dgnn_ctx* ctx, const dgnn_graphs* g, const int32_t* node_keys, const int32_t* emb_keys,
+                 const double* emb_table, int32_t n_keys, int32_t F, uint32_t flags, dgnn_collated* out) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    if (!out) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: null output");
+    memset(out, 0, sizeof(*out));
+    {
+        int r = consumer_begin(ctx, g, "dgnn_collate");
+        if (r != DGNN_OK) return r;
+    }
+    const long long N = ctx->last.N, E = ctx->last.E;
+    const bool want_x = node_keys != nullptr || emb_keys != nullptr || emb_table != nullptr || F > 0 || n_keys > 0;
+    if (want_x) {
+        if (!node_keys || !emb_keys || !emb_table) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: node_keys, emb_keys and emb_table go together");
+        if (F < 1 || F > 65536) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: feature width out of range");
+        if (n_keys < 1 || n_keys > 65536) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: n_keys out of range");
+    }
+    cudaStream_t st = ctx->stream;
+    int lut_size = 0;
+    if (want_x) {
+        // the std::map<int, VectorXd> as a dense key -> row table (keys are species indices / atomic numbers)
+        int max_key = 0;
+        for (int i = 0; i < n_keys; ++i) {
+            if (emb_keys[i] < 0 || emb_keys[i] >= 65536) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: embedding key %d out of range", emb_keys[i]);
+            if (emb_keys[i] > max_key) max_key = emb_keys[i];
+        }
+        lut_size = max_key + 1;
+        std::vector<int> lut((size_t)lut_size, -1);
+        for (int i = 0; i < n_keys; ++i) {
+            if (lut[emb_keys[i]] >= 0) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: duplicate embedding key %d", emb_keys[i]);
+            lut[emb_keys[i]] = i;
+        }
+        std::vector<float> tab((size_t)n_keys * F);
+        for (size_t i = 0; i < tab.size(); ++i) tab[i] = (float)emb_table[i];  // torch.tensor(..., dtype=torch.float)
+        ENSURE(ctx->col_lut, (size_t)lut_size * 4);
+        ENSURE(ctx->col_table, tab.size() * 4);
+        ENSURE(ctx->col_err, 16);
+        ENSURE(ctx->col_x, (size_t)(N > 0 ? N : 1) * F * 4);
+        CU(cudaMemcpyAsync(ctx->col_lut.p, lut.data(), (size_t)lut_size * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemcpyAsync(ctx->col_table.p, tab.data(), tab.size() * 4, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(ctx->col_err.p, 0xff, 4, st));  // -1: no missing key
+        if (!(flags & DGNN_INPUT_DEVICE) && N > 0) {
+            ENSURE(ctx->col_keys, (size_t)N * 4);
+            CU(cudaMemcpyAsync(ctx->col_keys.p, node_keys, (size_t)N * 4, cudaMemcpyHostToDevice, st));
+            node_keys = (const int32_t*)ctx->col_keys.p;
+        }
+        CU(cudaStreamSynchronize(st));  // lut / tab are stack-scoped host vectors
+    }
+    ENSURE(ctx->col_ei, (size_t)(E > 0 ? E : 1) * 16);
+    ENSURE(ctx->col_batch, (size_t)(N > 0 ? N : 1) * 8);
+    CU(cudaEventRecord(ctx->cev[0], st));
+    dg_launch_collate_nodes(st, N, want_x ? F : 0, node_keys, (const int*)ctx->col_lut.p, lut_size,
+                            (const float*)ctx->col_table.p, (const int*)ctx->astruct.p, want_x ? (float*)ctx->col_x.p : nullptr,
+                            (long long*)ctx->col_batch.p, (int*)ctx->col_err.p, ctx->sm_count);
+    dg_launch_collate_edges(st, N, E, (const long long*)ctx->row_ptr.p, (const int*)ctx->astruct.p, ctx->last.off,
+                            (const int*)ctx->dst.p, (long long*)ctx->col_ei.p, ctx->sm_count);
+    CU(cudaEventRecord(ctx->cev[1], st));
+    if (want_x && N > 0) {
+        int bad = -1;
+        CU(cudaMemcpyAsync(&bad, ctx->col_err.p, 4, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        if (bad >= 0) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: node %d: key not in the embedding table (std::map::at would throw)", bad);
+    }
+    {
+        int r = consumer_end(ctx, 8 * (N + 1) + 4 * N + 4 * E + (want_x ? 4 * N : 0),
+                             16 * E + 8 * N + (want_x ? 4LL * F * N : 0));
+        if (r != DGNN_OK) return r;
+    }
+    out->n_nodes = N;
+    out->n_edges = E;
+    out->F = want_x ? F : 0;
+    out->K = g->K;
+    out->x = want_x ? (const float*)ctx->col_x.p : nullptr;
+    out->edge_index = (const int64_t*)ctx->col_ei.p;
+    out->batch = (const int64_t*)ctx->col_batch.p;
+    out->edge_attr = g->rbf;
+    return DGNN_OK;
+}
+
+int dgnn_copy_collated_to_host(dgnn_ctx* ctx, const dgnn_collated* c, float* x, int64_t* edge_index, int64_t* batch) {
+    if (!ctx || !c) return DGNN_ERR_INVALID_ARG;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (x) {
+        if (!c->x) return fail(ctx, DGNN_ERR_INVALID_ARG, "no node features in this collation");
+        if (c->n_nodes > 0) CU(cudaMemcpyAsync(x, c->x, (size_t)c->n_nodes * c->F * 4, cudaMemcpyDeviceToHost, st));
+    }
+    if (edge_index && c->n_edges > 0) CU(cudaMemcpyAsync(edge_index, c->edge_index, (size_t)c->n_edges * 16, cudaMemcpyDeviceToHost, st));
+    if (batch && c->n_nodes > 0) CU(cudaMemcpyAsync(batch, c->batch, (size_t)c->n_nodes * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return DGNN_OK;
+}
+
+int dgnn_edge_views(dgnn_ctx* ctx, const dgnn_graphs* g, int32_t* sources, int32_t* targets, float* distances,
+                    float* displacements) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    {
+        int r = consumer_begin(ctx, g, "dgnn_edge_views");
+        if (r != DGNN_OK) return r;
+    }
+    const long long N = ctx->last.N, E = ctx->last.E;
+    cudaStream_t st = ctx->stream;
+    if (E == 0) return DGNN_OK;
+    // staging: [sources | targets | distances | displacements], only what was asked for
+    const size_t e4 = (size_t)E * 4;
+    ENSURE(ctx->view_a, e4 * ((sources ? 1 : 0) + (targets ? 1 : 0) + (distances ? 1 : 0) + (displacements ? 3 : 0)) + 16);
+    unsigned char* p = (unsigned char*)ctx->view_a.p;
+    int* d_src = nullptr; int* d_tgt = nullptr; float* d_dist = nullptr; float* d_disp = nullptr;
+    if (sources) { d_src = (int*)p; p += e4; }
+    if (targets) { d_tgt = (int*)p; p += e4; }
+    if (distances) { d_dist = (float*)p; p += e4; }
+    if (displacements) { d_disp = (float*)p; p += 3 * e4; }
+    CU(cudaEventRecord(ctx->cev[0], st));
+    dg_launch_edge_views(st, N, (const long long*)ctx->row_ptr.p, (const int*)ctx->astruct.p, (const DgSmall*)ctx->small.p,
+                         ctx->last.x, ctx->last.y, ctx->last.z, (const int*)ctx->dst.p, (const uint32_t*)ctx->image.p,
+                         (const double*)ctx->dist.p, d_src, d_tgt, d_dist, d_disp, ctx->sm_count);
+    CU(cudaEventRecord(ctx->cev[1], st));
+    if (sources) CU(cudaMemcpyAsync(sources, d_src, e4, cudaMemcpyDeviceToHost, st));
+    if (targets) CU(cudaMemcpyAsync(targets, d_tgt, e4, cudaMemcpyDeviceToHost, st));
+    if (distances) CU(cudaMemcpyAsync(distances, d_dist, e4, cudaMemcpyDeviceToHost, st));
+    if (displacements) CU(cudaMemcpyAsync(displacements, d_disp, 3 * e4, cudaMemcpyDeviceToHost, st));
+    return consumer_end(ctx, 8 * (N + 1) + E * ((targets || displacements ? 4 : 0) + (distances ? 8 : 0) + (displacements ? 4 : 0)),
+                        (long long)e4 * ((sources ? 1 : 0) + (targets ? 1 : 0) + (distances ? 1 : 0) + (displacements ? 3 : 0)));
+}
+
+int dgnn_neighborhood_clouds(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, int64_t a1, double* cloud,
+                             int64_t* cloud_ptr) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    {
+        int r = consumer_begin(ctx, g, "dgnn_neighborhood_clouds");
+        if (r != DGNN_OK) return r;
+    }
+    if (a0 < 0 || a1 < a0 || a1 > ctx->last.N) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_neighborhood_clouds: atom range out of bounds");
+    if (!cloud || !cloud_ptr) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_neighborhood_clouds: null output");
+    cudaStream_t st = ctx->stream;
+    const long long n = a1 - a0;
+    if (n == 0) {
+        cloud_ptr[0] = 0;
+        return DGNN_OK;
+    }
+    long long rp[2];
+    CU(cudaMemcpyAsync(&rp[0], (const long long*)ctx->row_ptr.p + a0, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&rp[1], (const long long*)ctx->row_ptr.p + a1, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const long long n_points = (rp[1] - rp[0]) + n;
+    ENSURE(ctx->view_a, (size_t)n_points * 24 + 16);
+    ENSURE(ctx->view_b, (size_t)(n + 1) * 8);
+    CU(cudaEventRecord(ctx->cev[0], st));
+    dg_launch_neighborhood_clouds(st, a0, a1, (const long long*)ctx->row_ptr.p, (const int*)ctx->astruct.p,
+                                  (const DgSmall*)ctx->small.p, ctx->last.x, ctx->last.y, ctx->last.z,
+                                  (const int*)ctx->dst.p, (const uint32_t*)ctx->image.p, (double*)ctx->view_a.p,
+                                  (long long*)ctx->view_b.p, ctx->sm_count);
+    CU(cudaEventRecord(ctx->cev[1], st));
+    CU(cudaMemcpyAsync(cloud, ctx->view_a.p, (size_t)n_points * 24, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(cloud_ptr, ctx->view_b.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, st));
+    return consumer_end(ctx, 8 * (n + 1) + 24 * n + 8 * (rp[1] - rp[0]), 24 * n_points + 8 * (n + 1));
+}

@@ -1,0 +1,217 @@
+// dgnn_collate.cu -- consumers of the CSR the build leaves in HBM (the callers on either side of the path):
+//
+//   f1  PyG-style batch collation, device-resident: node features gathered from the atom-embedding table
+//       (crystal_graph.cpp:15-21), edge_index [2, E] int64 with per-structure node offsets (crystal_graph.cpp:32-37 per
+//       structure + the planned train::BatchedGraph collation, PROJECT_ROADMAP.md:892-904), batch vector; dtypes of the
+//       Python consumer (.reference_code/Defect_GNN/utilities.py:69-71: x float, edge_index long, edge_attr float).
+//   f4  the viewer's flat getters (src/viz/wasm_bindings.cpp:206-294): edge sources / targets (int32), distances and
+//       displacements (float32) -- CSR expansions served by one kernel instead of four host walks.
+//   f2  the Betti caller's per-atom neighbourhood clouds (src/topology/betti_features.cpp:65-75):
+//       cloud[0] = position_i, cloud[1 + e] = position_i + displacement_e, fp64.
+//
+// All three are HBM-bound streaming kernels: one warp per CSR row, lanes over the row's edges, coalesced stores.
+// Compile with -fmad=false: displacements follow the reference's FMA-free operand order.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "dgnn_internal.h"
+
+static int g_collate_launches = 0;
+int dg_collate_launch_count_reset() {
+    int v = g_collate_launches;
+    g_collate_launches = 0;
+    return v;
+}
+
+#define DG_COLLATE_THREADS 256
+
+// ---- f1: edge_index [2, E] int64 (row 0 = global source node, row 1 = global target node) ---------------------------
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_edges(long long N, long long E,
+                                                                      const long long* __restrict__ row_ptr,
+                                                                      const int* __restrict__ astruct,
+                                                                      const long long* __restrict__ atom_offsets,
+                                                                      const int* __restrict__ dst,
+                                                                      long long* __restrict__ edge_index) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long a = warp0; a < N; a += nwarps) {
+        const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        const long long base = atom_offsets[astruct[a]];
+        for (long long e = e0 + lane; e < e1; e += 32) {
+            __stcs(edge_index + e, a);
+            __stcs(edge_index + E + e, base + (long long)dst[e]);
+        }
+    }
+}
+
+// ---- f1: x [N, F] fp32 gathered from the embedding table, batch [N] int64 -------------------------------------------
+// lut[key] = row of the table or -1 (key absent: std::map::at would throw, crystal_graph.cpp:20)
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_nodes(long long N, int F,
+                                                                      const int* __restrict__ node_keys,
+                                                                      const int* __restrict__ lut, int lut_size,
+                                                                      const float* __restrict__ table,
+                                                                      const int* __restrict__ astruct,
+                                                                      float* __restrict__ x,
+                                                                      long long* __restrict__ batch,
+                                                                      int* __restrict__ err) {
+    const long long total = N * (long long)F;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const long long a = i / F;
+        const int c = (int)(i - a * F);
+        const int key = node_keys[a];
+        const int row = (key >= 0 && key < lut_size) ? lut[key] : -1;
+        if (row < 0) {
+            if (c == 0) atomicCAS(err, -1, (int)(a < 0x7fffffffLL ? a : 0x7fffffffLL));
+            continue;
+        }
+        x[i] = table[(long long)row * F + c];
+        if (c == 0 && batch) batch[a] = (long long)astruct[a];
+    }
+}
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_batch(long long N, const int* __restrict__ astruct,
+                                                                      long long* __restrict__ batch) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x; a < N; a += stride)
+        batch[a] = (long long)astruct[a];
+}
+
+// ---- f4 / f2: per-edge expansion with the reference's displacement ---------------------------------------------------
+// displacement = cloud_pos - query_pos, cloud_pos = pos_j + ((n_a*row0 + n_b*row1) + n_c*row2)   neighbor_list.cpp:82-87,51
+__device__ __forceinline__ void dg_edge_displacement(const DgSmall* __restrict__ G, const double* __restrict__ x,
+                                                     const double* __restrict__ y, const double* __restrict__ z,
+                                                     long long ai, long long aj, uint32_t packed, double& dx,
+                                                     double& dy, double& dz) {
+    const int na = (int)(int8_t)(packed & 0xffu), nb = (int)(int8_t)((packed >> 8) & 0xffu),
+              nc = (int)(int8_t)((packed >> 16) & 0xffu);
+    dx = DG_SUB(DG_ADD(x[aj], dg_image_offset(G->L, 0, na, nb, nc)), x[ai]);
+    dy = DG_SUB(DG_ADD(y[aj], dg_image_offset(G->L, 1, na, nb, nc)), y[ai]);
+    dz = DG_SUB(DG_ADD(z[aj], dg_image_offset(G->L, 2, na, nb, nc)), z[ai]);
+}
+
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_edge_views(long long N, const long long* __restrict__ row_ptr,
+                                                                   const int* __restrict__ astruct,
+                                                                   const DgSmall* __restrict__ small,
+                                                                   const double* __restrict__ x,
+                                                                   const double* __restrict__ y,
+                                                                   const double* __restrict__ z,
+                                                                   const int* __restrict__ dst,
+                                                                   const uint32_t* __restrict__ image,
+                                                                   const double* __restrict__ dist,
+                                                                   int* __restrict__ sources, int* __restrict__ targets,
+                                                                   float* __restrict__ distances,
+                                                                   float* __restrict__ displacements) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    for (long long a = warp0; a < N; a += nwarps) {
+        const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        const DgSmall* __restrict__ G = small + astruct[a];
+        const long long base = G->atom_base;
+        const int iloc = (int)(a - base);
+        for (long long e = e0 + lane; e < e1; e += 32) {
+            const int j = dst[e];
+            if (sources) sources[e] = iloc;                    // static_cast<int>(i)
+            if (targets) targets[e] = j;                       // static_cast<int>(neighbor.idx)
+            if (distances) distances[e] = (float)dist[e];      // static_cast<float>(neighbor.distance)
+            if (displacements) {
+                double dx, dy, dz;
+                dg_edge_displacement(G, x, y, z, a, base + j, image[e], dx, dy, dz);
+                displacements[3 * e + 0] = (float)dx;
+                displacements[3 * e + 1] = (float)dy;
+                displacements[3 * e + 2] = (float)dz;
+            }
+        }
+    }
+}
+
+// f2: clouds of the atoms [a0, a1): atom a owns rows [cloud_ptr(a), cloud_ptr(a) + deg + 1) of the (x, y, z) fp64 array,
+// cloud_ptr(a) = (row_ptr[a] - row_ptr[a0]) + (a - a0)
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_neighborhood_clouds(long long a0, long long a1,
+                                                                            const long long* __restrict__ row_ptr,
+                                                                            const int* __restrict__ astruct,
+                                                                            const DgSmall* __restrict__ small,
+                                                                            const double* __restrict__ x,
+                                                                            const double* __restrict__ y,
+                                                                            const double* __restrict__ z,
+                                                                            const int* __restrict__ dst,
+                                                                            const uint32_t* __restrict__ image,
+                                                                            double* __restrict__ cloud,
+                                                                            long long* __restrict__ cloud_ptr) {
+    const int lane = threadIdx.x & 31;
+    const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    const long long ebase = row_ptr[a0];
+    for (long long a = a0 + warp0; a < a1; a += nwarps) {
+        const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        const DgSmall* __restrict__ G = small + astruct[a];
+        const long long base = G->atom_base;
+        const long long p0 = (e0 - ebase) + (a - a0);
+        const double xi = x[a], yi = y[a], zi = z[a];
+        if (lane == 0) {
+            cloud_ptr[a - a0] = p0;
+            if (a == a1 - 1) cloud_ptr[a1 - a0] = (e1 - ebase) + (a1 - a0);
+            cloud[3 * p0 + 0] = xi;  // point_cloud.row(0) = center.position
+            cloud[3 * p0 + 1] = yi;
+            cloud[3 * p0 + 2] = zi;
+        }
+        for (long long e = e0 + lane; e < e1; e += 32) {
+            double dx, dy, dz;
+            dg_edge_displacement(G, x, y, z, a, base + dst[e], image[e], dx, dy, dz);
+            const long long p = p0 + 1 + (e - e0);
+            cloud[3 * p + 0] = DG_ADD(xi, dx);  // center.position + neighbors[i].displacement
+            cloud[3 * p + 1] = DG_ADD(yi, dy);
+            cloud[3 * p + 2] = DG_ADD(zi, dz);
+        }
+    }
+}
+
+static unsigned grid_for(long long work_items, int sm_count, int per_block) {
+    long long g = (work_items + per_block - 1) / per_block;
+    const long long cap = (long long)sm_count * 16;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (unsigned)g;
+}
+
+void dg_launch_collate_edges(cudaStream_t st, long long N, long long E, const long long* row_ptr, const int* astruct,
+                             const long long* atom_offsets, const int* dst, long long* edge_index, int sm_count) {
+    if (N <= 0 || E <= 0) return;
+    k_collate_edges<<<grid_for(N, sm_count, DG_COLLATE_THREADS / 32), DG_COLLATE_THREADS, 0, st>>>(
+        N, E, row_ptr, astruct, atom_offsets, dst, edge_index);
+    ++g_collate_launches;
+}
+
+void dg_launch_collate_nodes(cudaStream_t st, long long N, int F, const int* node_keys, const int* lut, int lut_size,
+                             const float* table, const int* astruct, float* x, long long* batch, int* err,
+                             int sm_count) {
+    if (N <= 0) return;
+    if (F > 0 && x) {
+        k_collate_nodes<<<grid_for(N * (long long)F, sm_count, DG_COLLATE_THREADS), DG_COLLATE_THREADS, 0, st>>>(
+            N, F, node_keys, lut, lut_size, table, astruct, x, batch, err);
+    } else if (batch) {
+        k_collate_batch<<<grid_for(N, sm_count, DG_COLLATE_THREADS), DG_COLLATE_THREADS, 0, st>>>(N, astruct, batch);
+    }
+    ++g_collate_launches;
+}
+
+void dg_launch_edge_views(cudaStream_t st, long long N, const long long* row_ptr, const int* astruct,
+                          const DgSmall* small, const double* x, const double* y, const double* z, const int* dst,
+                          const uint32_t* image, const double* dist, int* sources, int* targets, float* distances,
+                          float* displacements, int sm_count) {
+    if (N <= 0) return;
+    k_edge_views<<<grid_for(N, sm_count, DG_COLLATE_THREADS / 32), DG_COLLATE_THREADS, 0, st>>>(
+        N, row_ptr, astruct, small, x, y, z, dst, image, dist, sources, targets, distances, displacements);
+    ++g_collate_launches;
+}
+
+void dg_launch_neighborhood_clouds(cudaStream_t st, long long a0, long long a1, const long long* row_ptr,
+                                   const int* astruct, const DgSmall* small, const double* x, const double* y,
+                                   const double* z, const int* dst, const uint32_t* image, double* cloud,
+                                   long long* cloud_ptr, int sm_count) {
+    if (a1 <= a0) return;
+    k_neighborhood_clouds<<<grid_for(a1 - a0, sm_count, DG_COLLATE_THREADS / 32), DG_COLLATE_THREADS, 0, st>>>(
+        a0, a1, row_ptr, astruct, small, x, y, z, dst, image, cloud, cloud_ptr);
+    ++g_collate_launches;
+}

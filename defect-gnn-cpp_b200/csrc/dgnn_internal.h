@@ -173,3 +173,19 @@ void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, i
 void dg_launch_rbf_f64_colmajor(cudaStream_t st, const double* dist, long long n_edges, int K, double r_cutoff,
                                 double dr, double* out);
 int dg_rbf_launch_count_reset();
+
+// ---- dgnn_collate.cu: consumers of the CSR (collation, viewer arrays, neighbourhood clouds) ----
+void dg_launch_collate_edges(cudaStream_t st, long long N, long long E, const long long* row_ptr, const int* astruct,
+                             const long long* atom_offsets, const int* dst, long long* edge_index, int sm_count);
+void dg_launch_collate_nodes(cudaStream_t st, long long N, int F, const int* node_keys, const int* lut, int lut_size,
+                             const float* table, const int* astruct, float* x, long long* batch, int* err,
+                             int sm_count);
+void dg_launch_edge_views(cudaStream_t st, long long N, const long long* row_ptr, const int* astruct,
+                          const DgSmall* small, const double* x, const double* y, const double* z, const int* dst,
+                          const uint32_t* image, const double* dist, int* sources, int* targets, float* distances,
+                          float* displacements, int sm_count);
+void dg_launch_neighborhood_clouds(cudaStream_t st, long long a0, long long a1, const long long* row_ptr,
+                                   const int* astruct, const DgSmall* small, const double* x, const double* y,
+                                   const double* z, const int* dst, const uint32_t* image, double* cloud,
+                                   long long* cloud_ptr, int sm_count);
+int dg_collate_launch_count_reset();

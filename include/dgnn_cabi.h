@@ -120,6 +120,59 @@ int dgnn_rbf_expand(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutof
 int dgnn_rbf_expand_f64(dgnn_ctx* ctx, const double* dist, int64_t n, double r_cutoff, double dr, double* out,
                         int32_t* K_out);
 
+/* ---- Consumers of the last build's device-resident CSR (the callers either side of the path) --------
+ * All of them take the dgnn_graphs of the LAST dgnn_build on this ctx; when that build read device inputs
+ * (DGNN_INPUT_DEVICE) the caller's coordinate buffers must still be alive. */
+
+/* f1: PyG-style batch collation, left in HBM for the training consumer.  Replaces CrystalGraph's node / edge-index
+ * assembly (crystal_graph.cpp:15-21, 32-37) plus the planned train::BatchedGraph collation (PROJECT_ROADMAP.md:
+ * 892-904) with the dtypes of the Python consumer (utilities.py:69-71: x float, edge_index long, edge_attr float). */
+typedef struct {
+    int64_t n_nodes;
+    int64_t n_edges;
+    int32_t F;                  /* node feature width (0: no embedding table given) */
+    int32_t K;                  /* edge feature width (= dgnn_graphs::K) */
+    const float* x;             /* [n_nodes, F] row-major fp32: x[i] = atom_embeddings.at(node_keys[i]) */
+    const int64_t* edge_index;  /* [2, n_edges] row-major int64: row 0 = source node, row 1 = target node, both GLOBAL
+                                 * (structure s's nodes start at atom_offsets[s]) */
+    const int64_t* batch;       /* [n_nodes] structure index of every node */
+    const float* edge_attr;     /* [n_edges, K] = dgnn_graphs::rbf */
+} dgnn_collated;
+/* node_keys: [n_atoms] int32, the key CrystalGraph passes to atom_embeddings.at() -- the reference passes
+ * Atom::element, the POSCAR species index (structure.cpp:15), against a table keyed by atomic number
+ * (json_parser.cpp:22-30); pass whichever the caller means, the lookup itself is the same.  Host pointer, or device
+ * when flags has DGNN_INPUT_DEVICE.  emb_keys [n_keys] (host, distinct, 0 <= key < 65536) and emb_table
+ * [n_keys, F] (host, row-major fp64, converted to fp32 once) are the std::map.  A node whose key is absent fails
+ * with DGNN_ERR_INVALID_ARG (std::map::at would throw std::out_of_range, crystal_graph.cpp:20).
+ * node_keys / emb_keys / emb_table may all be NULL (F = 0): only edge_index and batch are produced. */
+int dgnn_collate(dgnn_ctx* ctx, const dgnn_graphs* g, const int32_t* node_keys, const int32_t* emb_keys,
+                 const double* emb_table, int32_t n_keys, int32_t F, uint32_t flags, dgnn_collated* out);
+int dgnn_copy_collated_to_host(dgnn_ctx* ctx, const dgnn_collated* c, float* x, int64_t* edge_index, int64_t* batch);
+
+/* f4: the viewer's flat getters (wasm_bindings.cpp:206-294) in one kernel + one D2H per array: sources / targets
+ * [E] int32 (atom indices local to the structure), distances [E] float32, displacements [3E] float32
+ * (static_cast<float> of Neighbor::displacement = cloud_pos - query_pos, neighbor_list.cpp:51).  Host outputs,
+ * any may be NULL. */
+int dgnn_edge_views(dgnn_ctx* ctx, const dgnn_graphs* g, int32_t* sources, int32_t* targets, float* distances,
+                    float* displacements);
+
+/* f2: per-atom neighbourhood point clouds of the Betti caller (betti_features.cpp:65-75) for the atoms [a0, a1):
+ * atom a owns the points [cloud_ptr[a - a0], cloud_ptr[a - a0 + 1]) of `cloud` ([n_points, 3] fp64): first its own
+ * position, then position + displacement of every neighbour in row order.  n_points = (row_ptr[a1] - row_ptr[a0])
+ * + (a1 - a0).  Host outputs. */
+int dgnn_neighborhood_clouds(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, int64_t a1, double* cloud,
+                             int64_t* cloud_ptr);
+
+/* Device time (CUDA events on the ctx stream, kernels only -- no H2D / D2H) and algorithmic bytes of the last
+ * dgnn_collate / dgnn_edge_views / dgnn_neighborhood_clouds call. */
+typedef struct {
+    float device_ms;
+    int32_t kernel_launches;
+    int64_t bytes_read;    /* algorithmic bytes the kernels read ... */
+    int64_t bytes_written; /* ... and wrote */
+} dgnn_consumer_info;
+int dgnn_last_consumer_info(const dgnn_ctx* ctx, dgnn_consumer_info* out);
+
 /* Device timings of the phases of the last dgnn_build (CUDA events on the ctx stream), milliseconds:
  * bin = geometry + cell-list binning (K1), dist = count + scan + fill/sort (K2), rbf = K3, h2d = input upload,
  * total = first to last event. */

@@ -208,3 +208,73 @@ def rows_brute(x, y, z, lattice, r_cutoff, sources, row_cap, epsilon=1e-10):
     if rc != 0:
         raise RuntimeError(f"orc_rows_brute failed rc={rc}")
     return deg, dst, image, dist
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Consumers of the neighbour list -- numpy restatements, test infrastructure only.
+# ---------------------------------------------------------------------------------------------------------------------
+def crystal_graph_arrays(o: OracleGraph, node_keys, atom_embeddings: dict):
+    """CrystalGraph's node / edge-index assembly for ONE structure (src/graph/crystal_graph.cpp:15-40):
+    node_features.row(i) = atom_embeddings.at(element_i)  (KeyError where std::map::at throws);
+    edge_index(0, e) = i, edge_index(1, e) = neighbor.idx, edges by source atom then row order."""
+    n = o.row_ptr.shape[0] - 1
+    x = np.stack([np.asarray(atom_embeddings[int(k)], dtype=np.float64) for k in node_keys]) if n else np.zeros((0, 0))
+    src = np.repeat(np.arange(n, dtype=np.int64), np.diff(o.row_ptr))
+    edge_index = np.stack([src, o.dst.astype(np.int64)])
+    return x, edge_index
+
+
+def collate(graphs, node_keys_per_graph, atom_embeddings: dict):
+    """The batch collation the training consumer does (planned train::BatchedGraph, PROJECT_ROADMAP.md:892-904; PyG
+    Batch semantics of the Python ancestor): concatenate node features, offset edge indices by the node count of the
+    preceding graphs, batch[i] = graph of node i.  dtypes of utilities.py:69-71 (x float32, edge_index int64)."""
+    xs, eis, batch = [], [], []
+    base = 0
+    for gi, (o, keys) in enumerate(zip(graphs, node_keys_per_graph)):
+        x, ei = crystal_graph_arrays(o, keys, atom_embeddings)
+        n = o.row_ptr.shape[0] - 1
+        if n:
+            xs.append(x.astype(np.float32))
+        eis.append(ei + base)
+        batch.append(np.full(n, gi, dtype=np.int64))
+        base += n
+    F = len(next(iter(atom_embeddings.values()))) if atom_embeddings else 0
+    x = np.concatenate(xs) if xs else np.zeros((0, F), dtype=np.float32)
+    return x, np.concatenate(eis, axis=1) if eis else np.zeros((2, 0), np.int64), \
+        np.concatenate(batch) if batch else np.zeros(0, np.int64)
+
+
+def displacements(x, y, z, lattice, o: OracleGraph) -> np.ndarray:
+    """Neighbor::displacement re-derived from (dst, image): cloud_pos - query_pos with
+    cloud_pos = pos_j + ((n_a*row0 + n_b*row1) + n_c*row2)  (src/graph/neighbor_list.cpp:82-87, 51); numpy fp64
+    element-wise arithmetic rounds once per operation like the reference's FMA-free build.  The exhaustive and KD-tree
+    algorithms of the C++ oracle return the same quantity directly (OracleGraph.disp) -- tests pin one on the other."""
+    Lm = _f64(lattice).reshape(3, 3)
+    pos = np.stack([_f64(x), _f64(y), _f64(z)], axis=1)
+    n = o.row_ptr.shape[0] - 1
+    src = np.repeat(np.arange(n), np.diff(o.row_ptr))
+    na = o.image[:, 0].astype(np.float64)[:, None]
+    nb = o.image[:, 1].astype(np.float64)[:, None]
+    nc = o.image[:, 2].astype(np.float64)[:, None]
+    off = (na * Lm[0][None, :] + nb * Lm[1][None, :]) + nc * Lm[2][None, :]
+    return (pos[o.dst] + off) - pos[src]
+
+
+def viewer_arrays(o: OracleGraph, disp=None):
+    """WasmAPI::get_edge_sources / targets / distances / displacements (src/viz/wasm_bindings.cpp:206-294):
+    static_cast<int>(i), static_cast<int>(neighbor.idx), static_cast<float>(distance), static_cast<float>(disp.xyz)."""
+    n = o.row_ptr.shape[0] - 1
+    src = np.repeat(np.arange(n, dtype=np.int32), np.diff(o.row_ptr))
+    d = o.disp if disp is None else disp
+    return src, o.dst.astype(np.int32), o.dist.astype(np.float32), d.astype(np.float32).reshape(-1)
+
+
+def neighborhood_cloud(x, y, z, o: OracleGraph, atom: int, disp=None) -> np.ndarray:
+    """compute_atom_betti_features' point cloud (src/topology/betti_features.cpp:65-75): row 0 = the atom's position,
+    row 1 + e = position + neighbors[e].displacement (fp64, one rounding per component)."""
+    e0, e1 = int(o.row_ptr[atom]), int(o.row_ptr[atom + 1])
+    c = np.array([x[atom], y[atom], z[atom]], dtype=np.float64)
+    out = np.empty((e1 - e0 + 1, 3), dtype=np.float64)
+    out[0] = c
+    out[1:] = c[None, :] + (o.disp if disp is None else disp)[e0:e1]
+    return out

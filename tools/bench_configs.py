@@ -101,6 +101,42 @@ def main():
     if on("C2cap"):
         b2 = syn.c2_batch(10_000)
         run(gb, torch, "C2 10k perovskite supercells, cap=20 (secondary)", b2, 8.0, 20, 0.2, args.reps, peak)
+    if on("F1"):
+        # consumers of the CSR: device time of the kernels, algorithmic bytes / time against the copy peak
+        b2 = syn.c2_batch(10_000)
+        dev = torch.device("cuda:0")
+        t = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (b2.atom_offsets, b2.x, b2.y, b2.z, b2.lattices)]
+        g = gb.build(*t, r_cutoff=8.0, max_neighbors=UNCAPPED, epsilon=1e-10, rbf_r_cutoff=8.0, dr=0.2, device_inputs=True)
+        rng = np.random.default_rng(0)
+        keys = torch.from_numpy(rng.integers(1, 101, size=b2.n_atoms).astype(np.int32)).to(dev)
+        ek = np.arange(1, 101, dtype=np.int32)
+        et = rng.standard_normal((100, 92))
+        ms, info = [], None
+        for i in range(args.reps + 2):
+            c = gb.collate(keys, ek, et, device_keys=True)
+            info = gb.consumer_info()
+            if i >= 2:
+                ms.append(info.device_ms)
+        m = statistics.median(ms)
+        tot = info.bytes_read + info.bytes_written
+        print(json.dumps({"config": "F1 dgnn_collate on C2 10k uncapped (x [N,92] f32 gather, edge_index [2,E] i64, batch [N] i64)",
+                          "n_nodes": int(c.n_nodes), "n_edges": int(c.n_edges), "device_ms": m,
+                          "algorithmic_bytes": int(tot), "achieved_gbs": tot / (m * 1e-3) / 1e9,
+                          "frac_of_measured_peak": tot / (m * 1e-3) / 1e9 / peak, "launches": info.kernel_launches}), flush=True)
+        del t
+        b2c = syn.c2_batch(2_000)
+        g = gb.build(b2c.atom_offsets, b2c.x, b2c.y, b2c.z, b2c.lattices, r_cutoff=5.0, max_neighbors=12, skip_rbf=True)
+        ms = []
+        for i in range(args.reps + 2):
+            gb.edge_views()
+            info = gb.consumer_info()
+            if i >= 2:
+                ms.append(info.device_ms)
+        m = statistics.median(ms)
+        tot = info.bytes_read + info.bytes_written
+        print(json.dumps({"config": "F4 dgnn_edge_views on 2k C2 structures, viewer params r_c=5 cap=12 (kernel only; D2H outside)",
+                          "n_edges": int(g.n_edges), "device_ms": m, "algorithmic_bytes": int(tot),
+                          "achieved_gbs": tot / (m * 1e-3) / 1e9, "launches": info.kernel_launches}), flush=True)
     if on("C3"):
         b3 = syn.c3_batch(10_000)
         run(gb, torch, "C3 10k triclinic short-vector cells r_c=8 K=40 uncapped", b3, 8.0, UNCAPPED, 0.2, args.reps, peak)
