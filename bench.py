@@ -269,7 +269,7 @@ def main():
     e2e_steps = args.e2e_steps or args.steps
     for _ in range(2):
         step_e2e()
-    ms_e2e, _, edges_all_e2e, _ = timed(step_e2e, e2e_steps)
+    ms_e2e, _, edges_all_e2e, infos_e2e = timed(step_e2e, e2e_steps)
     h2d_bytes = sum(int(t.numel() * t.element_size()) for t in h_in)
     d2h_bytes = int(h_seo.numel() * 8 + h_rowptr.numel() * 8)
 
@@ -312,6 +312,8 @@ def main():
                       for k in ("bin_ms", "count_ms", "fill_ms", "rbf_ms", "total_ms")},
         "e2e": {"value": edges_all_e2e / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": d2h_bytes, "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
+                "phases_ms": {k: statistics.mean(getattr(i, k) for i in infos_e2e)
+                              for k in ("h2d_ms", "bin_ms", "count_ms", "fill_ms", "total_ms")},
                 "note": "dgnn_build on pinned host SoA buffers + D2H of row_ptr and per-structure edge offsets; "
                         "graphs stay in HBM for the consumer"},
         "gpu_launches": launches,

@@ -58,6 +58,11 @@ struct dgnn_ctx {
     int fuse_rbf = 1;
     int hit_cap_opt = -1;                 // -1: auto (density estimate), 0: off, > 0: fixed slots per row
     double hits_max_bytes = 16e9;         // no hit lists beyond this much scratch
+    cudaStream_t copy_stream = nullptr;   // host inputs: coordinates are uploaded in structure-aligned chunks on this
+    cudaEvent_t copy_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // stream ...
+    long long upload_min_atoms = 1 << 18; // smaller batches go up in one piece
+    int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
+    int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
     // the last successful build, for the CSR consumers (collation, viewer arrays, neighbourhood clouds)
@@ -234,6 +239,9 @@ int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out) {
     ctx->sm_count = prop.multiProcessorCount;
     ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    for (auto& e : ctx->copy_ev)
+        if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     for (auto& e : ctx->ev.e)
         if (cudaEventCreate(&e) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     if (cudaMallocHost(&ctx->h_stats, sizeof(DgStats)) != cudaSuccess) return bail(DGNN_ERR_CUDA);
@@ -265,6 +273,9 @@ void dgnn_destroy(dgnn_ctx* ctx) {
         if (e) cudaEventDestroy(e);
     for (auto& e : ctx->cev)
         if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->copy_ev)
+        if (e) cudaEventDestroy(e);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -304,6 +315,14 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "hits_max_bytes")) {
         if (!(value >= 0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "hits_max_bytes out of range");
         ctx->hits_max_bytes = value;
+    } else if (!strcmp(name, "upload_min_atoms")) {
+        if (!(value >= 0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "upload_min_atoms out of range");
+        ctx->upload_min_atoms = (long long)value;
+    } else if (!strcmp(name, "upload_chunks")) {
+        if (!(value >= 1 && value <= 8)) return fail(ctx, DGNN_ERR_INVALID_ARG, "upload_chunks must be in [1, 8]");
+        ctx->upload_chunks = (int)value;
+    } else if (!strcmp(name, "rbf_recur")) {
+        ctx->rbf_recur = value != 0.0;
     } else if (!strcmp(name, "onepass")) {
         if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass must be -1, 0 or 1");
         ctx->onepass_opt = (int)value;  // single-pass build (look-back row offsets) instead of count + fill
@@ -359,6 +378,17 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // ---- inputs ----------------------------------------------------------------------------------------------
     const bool dev_in = (b->flags & DGNN_INPUT_DEVICE) != 0;
     long long N = 0;
+    // chunked coordinate upload (host inputs): atoms [up_a[c], up_a[c+1]) arrive with copy_ev[c].  The guard keeps the
+    // caller's buffers from being released under an in-flight copy when the build returns early.
+    int n_up = 1;
+    long long up_a[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    struct UploadGuard {
+        cudaStream_t s;
+        bool armed;
+        ~UploadGuard() {
+            if (armed) cudaStreamSynchronize(s);
+        }
+    } upload{ctx->copy_stream, false};
     CU(cudaEventRecord(ctx->ev.e[0], st));
     const long long* d_off;
     const double *d_x, *d_y, *d_z, *d_lat;
@@ -375,6 +405,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         N = b->atom_offsets[S];
     }
     if (N < 0 || N >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "atom count %lld out of range", N);
+    up_a[1] = N;
     if (N > 0 && (!b->x || !b->y || !b->z)) return fail(ctx, DGNN_ERR_INVALID_ARG, "coordinate pointer is null");
     if (S > 0 && !b->lattice) return fail(ctx, DGNN_ERR_INVALID_ARG, "lattice pointer is null");
     if (!dev_in) {
@@ -384,12 +415,20 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         ENSURE(ctx->in_z, (size_t)N * 8 + 8);
         ENSURE(ctx->in_lat, (size_t)S * 72 + 8);
         CU(cudaMemcpyAsync(ctx->in_off.p, b->atom_offsets, (size_t)(S + 1) * 8, cudaMemcpyHostToDevice, st));
-        if (N > 0) {
-            CU(cudaMemcpyAsync(ctx->in_x.p, b->x, (size_t)N * 8, cudaMemcpyHostToDevice, st));
-            CU(cudaMemcpyAsync(ctx->in_y.p, b->y, (size_t)N * 8, cudaMemcpyHostToDevice, st));
-            CU(cudaMemcpyAsync(ctx->in_z.p, b->z, (size_t)N * 8, cudaMemcpyHostToDevice, st));
-        }
         if (S > 0) CU(cudaMemcpyAsync(ctx->in_lat.p, b->lattice, (size_t)S * 72, cudaMemcpyHostToDevice, st));
+        // coordinates: structure-aligned chunks on the copy stream; the consumers below wait chunk by chunk
+        if (N >= ctx->upload_min_atoms && S >= ctx->upload_chunks) n_up = ctx->upload_chunks;
+        for (int c = 0; c <= n_up; ++c) up_a[c] = b->atom_offsets[S * c / n_up];
+        for (int c = 0; c < n_up; ++c) {
+            const long long a0 = up_a[c], n = up_a[c + 1] - up_a[c];
+            if (n > 0) {
+                upload.armed = true;
+                CU(cudaMemcpyAsync((double*)ctx->in_x.p + a0, b->x + a0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->copy_stream));
+                CU(cudaMemcpyAsync((double*)ctx->in_y.p + a0, b->y + a0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->copy_stream));
+                CU(cudaMemcpyAsync((double*)ctx->in_z.p + a0, b->z + a0, (size_t)n * 8, cudaMemcpyHostToDevice, ctx->copy_stream));
+            }
+            CU(cudaEventRecord(ctx->copy_ev[c], ctx->copy_stream));
+        }
         d_off = (const long long*)ctx->in_off.p;
         d_x = (const double*)ctx->in_x.p; d_y = (const double*)ctx->in_y.p; d_z = (const double*)ctx->in_z.p;
         d_lat = (const double*)ctx->in_lat.p;
@@ -416,8 +455,6 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     const int eps_mode = !(b->epsilon > 0.0) ? 0 : (b->epsilon <= DG_EPS_FAST ? 1 : 2);
     dg_launch_small_geom(st, S, d_off, d_lat, b->r_cutoff, ctx->direct_max_atoms, eps_mode == 1 ? b->epsilon : 0.0,
                          small, d_stats);
-    dg_launch_direct_prep(st, N, S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p, (double*)ctx->fa.p,
-                          (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
     // hit lists: the count pass records every accepted (atom, image) pair so that the fill pass does not repeat the
     // traversal.  Slots per row come from the density estimate of the degree (rows that outgrow them, and structures
     // whose image range does not fit the 5-bit fields, are filled by the traversal pass instead).
@@ -542,15 +579,35 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             const int keep_max_1p = row_cap_1p < max_nb ? row_cap_1p : max_nb;
             onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 &&
                                 (long long)keep_max_1p * (K / 4) < (1LL << 22);
-            if (onepass_fused_rbf) O.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+            if (onepass_fused_rbf) {
+                O.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+                O.rbf.recur = ctx->rbf_recur;
+            }
             CU(cudaMemsetAsync(ctx->lb_status.p, 0, (size_t)(N + 1) * 8, st));
+            for (int c = 0; c < n_up; ++c) {
+                if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
+                dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
+                                      (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+            }
             CU(cudaEventRecord(ctx->ev.e[3], st));
             CU(dg_launch_direct_onepass(st, O, ctx->sm_count, ctx->direct_min_blocks));
             onepass = true;
         }
     }
     if (!onepass) {
-        CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+        // per upload chunk (structure-aligned): fractional coordinates, then the count pass of its rows -- the next
+        // chunk's coordinates cross PCIe meanwhile
+        for (int c = 0; c < n_up; ++c) {
+            if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
+            dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
+                                  (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+            if (up_a[c + 1] > up_a[c]) {
+                D.row_begin = up_a[c];
+                D.row_end = up_a[c + 1];
+                CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+            }
+        }
+        D.row_begin = D.row_end = 0;
         dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
     }
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
@@ -708,7 +765,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
                                   : (want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
                                      (long long)keep_max * (K / 4) < (1LL << 22));
     if (want_rbf && E > 0) ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
-    if (fuse_rbf) D.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+    if (fuse_rbf) {
+        D.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+        D.rbf.recur = ctx->rbf_recur;
+    }
     while (D.n_warps > 1 && (int)dg_direct_smem_bytes(D, true) > ctx->smem_optin) D.n_warps >>= 1;
     if ((int)dg_direct_smem_bytes(D, true) > ctx->smem_optin)
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);

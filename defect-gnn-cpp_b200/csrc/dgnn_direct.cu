@@ -73,14 +73,14 @@ void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_of
 }
 
 // per-atom: owning structure and fractional coordinates
-__global__ void __launch_bounds__(256) k_direct_prep(long long N, long long S,
+__global__ void __launch_bounds__(256) k_direct_prep(long long a_begin, long long N, long long S,
                                                      const long long* __restrict__ atom_offsets,
                                                      const double* __restrict__ x, const double* __restrict__ y,
                                                      const double* __restrict__ z,
                                                      const DgSmall* __restrict__ small, int* __restrict__ astruct,
                                                      double* __restrict__ fa, double* __restrict__ fb,
                                                      double* __restrict__ fc, DgStats* __restrict__ stats) {
-    const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const long long a = a_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= N) return;
     long long lo = 0, hi = S;  // last s with atom_offsets[s] <= a
     while (hi - lo > 1) {
@@ -103,12 +103,13 @@ __global__ void __launch_bounds__(256) k_direct_prep(long long N, long long S,
     }
 }
 
-void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
-                           const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
-                           double* fa, double* fb, double* fc, DgStats* stats) {
-    if (N <= 0) return;
-    k_direct_prep<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, S, atom_offsets, x, y, z, small, astruct, fa, fb,
-                                                                fc, stats);
+// atoms [a_begin, a_end)
+void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, long long S,
+                           const long long* atom_offsets, const double* x, const double* y, const double* z,
+                           const DgSmall* small, int* astruct, double* fa, double* fb, double* fc, DgStats* stats) {
+    if (a_end <= a_begin) return;
+    k_direct_prep<<<(unsigned)((a_end - a_begin + 255) / 256), 256, 0, st>>>(a_begin, a_end, S, atom_offsets, x, y, z,
+                                                                              small, astruct, fa, fb, fc, stats);
     ++g_direct_launches;
 }
 
@@ -374,11 +375,13 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     if (FILL) rb = dg_rowbuf_carve(smem_raw + (size_t)warp * dg_rowbuf_bytes(A.row_cap, A.n_buckets), A.row_cap);
     unsigned near = 0;
     int maxdeg = 0;
-    const long long n_chunks = (A.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    // rows [row_begin, row_end) (row_end = 0: all rows); the count pass runs range by range behind the chunked upload
+    const long long r0 = A.row_begin, r1 = A.row_end > 0 ? A.row_end : A.n_atoms;
+    const long long n_chunks = (r1 - r0 + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
 
     for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-        const long long a_end = (chunk + 1) * DG_ROW_CHUNK < A.n_atoms ? (chunk + 1) * DG_ROW_CHUNK : A.n_atoms;
-        for (long long a = chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
+        const long long a_end = r0 + (chunk + 1) * DG_ROW_CHUNK < r1 ? r0 + (chunk + 1) * DG_ROW_CHUNK : r1;
+        for (long long a = r0 + chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
             const DgSmall* __restrict__ G = A.small + A.astruct[a];
             const int mode = G->mode;
             if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;  // the cell-list path owns this structure
@@ -611,9 +614,11 @@ static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int s
     if (occ < 1) occ = 1;
     // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin (the single-pass
     // look-back relies on the grid being fully resident: never more CTAs than the occupancy query allows)
-    const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    const long long rows = (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
+    const long long want = (rows + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
     long long grid = (long long)sm_count * occ;
     if (grid > want) grid = want;
+    if (grid < 1) return cudaSuccess;
     k_direct<FILL, MINB, EPS, HITS><<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
 }

@@ -36,6 +36,12 @@ struct DgRbfEpi {
     float inv_k4;  // 1 / (K/4)
     int K4;        // K / 4
     float4* out;   // E x K fp32 row-major
+    // Gaussian recurrence across the 4 bins of a float4 (row_sort.cuh): g(k+1)/g(k) = r * q^(2i+1) with
+    // r = 2^(c2dr * x0), q = 2^(coef * dr^2): two ex2 instead of four per float4
+    float c2dr;    // 2 * coef * dr
+    float q;       // 2^(coef * dr^2)
+    float q2;      // q * q
+    int recur;     // 1: use the recurrence in the fused epilogue
 };
 DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out);  // dgnn_rbf.cu
 
@@ -147,6 +153,7 @@ struct DgDirectArgs {
     long long* row_ptr_out;         // [N+1]
     long long edge_cap;             // edges the output arrays can hold
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
+    long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -155,9 +162,9 @@ struct DgDirectArgs {
 // eps_fast > 0: the traversal will use the fast self-exclusion (eps_mode 1); cells thinner than 2 eps are rejected
 void dg_launch_small_geom(cudaStream_t st, long long S, const long long* atom_offsets, const double* lattice,
                           double r_cutoff, int direct_max_atoms, double eps_fast, DgSmall* small, DgStats* stats);
-void dg_launch_direct_prep(cudaStream_t st, long long N, long long S, const long long* atom_offsets,
-                           const double* x, const double* y, const double* z, const DgSmall* small, int* astruct,
-                           double* fa, double* fb, double* fc, DgStats* stats);
+void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, long long S,
+                           const long long* atom_offsets, const double* x, const double* y, const double* z,
+                           const DgSmall* small, int* astruct, double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);

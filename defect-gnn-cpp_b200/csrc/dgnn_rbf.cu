@@ -72,6 +72,13 @@ DgRbfEpi dg_make_rbf_epi(int K, double r_cutoff, double dr, float* out) {
     P.dr = (float)dr;
     P.coef = (float)(-0.5 / (sigma * sigma) * 1.4426950408889634074);
     P.lognorm = (float)std::log2(1.0 / (sigma * 2.5066282746310005024));
+    {
+        const double coef = -0.5 / (sigma * sigma) * 1.4426950408889634074;
+        P.c2dr = (float)(2.0 * coef * dr);
+        P.q = (float)std::exp2(coef * dr * dr);
+        P.q2 = (float)std::exp2(2.0 * coef * dr * dr);
+        P.recur = 0;
+    }
     P.K4 = K / 4;
     P.inv_k4 = P.K4 > 0 ? 1.0f / (float)P.K4 : 0.0f;
     P.out = reinterpret_cast<float4*>(out);

@@ -6,8 +6,11 @@
 
 #include "crystal/structure.hpp"
 
+#include <Eigen/Dense>
+
 #include <cstddef>
 #include <cstdint>
+#include <map>
 #include <memory>
 #include <vector>
 
@@ -28,6 +31,7 @@ struct SoABatch {
     std::vector<int64_t> atom_offsets;  // [S+1]
     std::vector<double> x, y, z;        // [N]
     std::vector<double> lattice;        // [9 S] row-major
+    std::vector<int> element;           // [N] Atom::element (the key CrystalGraph looks the embedding up with)
     void add(const crystal::Structure& s);
     [[nodiscard]] int64_t n_structs() const { return (int64_t)atom_offsets.size() - 1; }
     [[nodiscard]] int64_t n_atoms() const { return atom_offsets.empty() ? 0 : atom_offsets.back(); }
@@ -49,6 +53,26 @@ struct BatchedGraphs {
     std::vector<int64_t> host_struct_edge_offsets;  // copied back: the only D2H of the hot path
 };
 
+// The training consumer's batch (the planned train::BatchedGraph, PROJECT_ROADMAP.md:892-904) left on the device with
+// the dtypes of the Python consumer (utilities.py:69-71).  DEVICE pointers owned by the builder, valid until its next
+// build() / collate().
+struct CollatedBatch {
+    int64_t num_nodes = 0, num_edges = 0;
+    int num_graphs = 0;
+    int32_t F = 0, K = 0;
+    const float* x = nullptr;             // [num_nodes, F]   node_features rows (crystal_graph.cpp:19-21), fp32
+    const int64_t* edge_index = nullptr;  // [2, num_edges]   global node ids (per-structure offsets applied)
+    const float* edge_attr = nullptr;     // [num_edges, K]   = BatchedGraphs::rbf
+    const int64_t* batch = nullptr;       // [num_nodes]      graph membership
+};
+
+// The viewer's flat getters (src/viz/wasm_bindings.cpp:206-294) for every edge of the batch, host vectors.
+struct EdgeViews {
+    std::vector<int> sources, targets;        // atom indices local to the structure
+    std::vector<float> distances;             // static_cast<float>(Neighbor::distance)
+    std::vector<float> displacements;         // 3 per edge, static_cast<float>(Neighbor::displacement)
+};
+
 class BatchBuilder {
 public:
     explicit BatchBuilder(int device = 0);
@@ -59,6 +83,13 @@ public:
     // Throws std::runtime_error with the C-ABI error text on failure; there is no CPU fallback.
     BatchedGraphs build(const SoABatch& batch, const BatchParams& params);
     BatchedGraphs build(const std::vector<const crystal::Structure*>& structures, const BatchParams& params);
+
+    // Node features gathered on the device: x[i] = atom_embeddings.at(node_keys[i]); throws std::out_of_range where
+    // std::map::at would (crystal_graph.cpp:20).  node_keys: one per atom of the batch (SoABatch::element).
+    CollatedBatch collate(const BatchedGraphs& g, const std::vector<int>& node_keys,
+                          const std::map<int, Eigen::VectorXd>& atom_embeddings);
+    void copy_collated_to_host(const CollatedBatch& c, float* x, int64_t* edge_index, int64_t* batch) const;
+    EdgeViews edge_views(const BatchedGraphs& g, bool with_displacements = true);
 
     // Host copies of the last result (any pointer may be null).
     void copy_edges_to_host(const BatchedGraphs& g, int64_t* row_ptr, int32_t* dst, int32_t* image, double* dist,

@@ -13,6 +13,7 @@ void SoABatch::add(const crystal::Structure& s) {
         x.push_back(a.position[0]);
         y.push_back(a.position[1]);
         z.push_back(a.position[2]);
+        element.push_back(a.element);
     }
     for (int r = 0; r < 3; ++r)
         for (int c = 0; c < 3; ++c) lattice.push_back(s.lattice()(r, c));
@@ -80,6 +81,89 @@ BatchedGraphs BatchBuilder::build(const std::vector<const crystal::Structure*>& 
         b.add(*s);
     }
     return build(b, p);
+}
+
+namespace {
+dgnn_graphs as_cabi(const BatchedGraphs& g) {
+    dgnn_graphs v{};
+    v.n_structs = g.n_structs;
+    v.n_atoms = g.n_atoms;
+    v.n_edges = g.n_edges;
+    v.K = g.K;
+    v.max_degree = g.max_degree;
+    v.row_ptr = g.row_ptr;
+    v.dst = g.dst;
+    v.image = g.image;
+    v.dist = g.dist;
+    v.rbf = g.rbf;
+    v.struct_edge_offsets = g.struct_edge_offsets;
+    return v;
+}
+}  // namespace
+
+CollatedBatch BatchBuilder::collate(const BatchedGraphs& g, const std::vector<int>& node_keys,
+                                    const std::map<int, Eigen::VectorXd>& atom_embeddings) {
+    if (static_cast<int64_t>(node_keys.size()) != g.n_atoms)
+        throw std::invalid_argument("BatchBuilder::collate: one key per atom expected");
+    std::vector<int32_t> keys;
+    std::vector<double> table;
+    int F = 0;
+    for (const auto& kv : atom_embeddings) {
+        if (keys.empty()) F = static_cast<int>(kv.second.size());
+        if (static_cast<int>(kv.second.size()) != F)
+            throw std::invalid_argument("BatchBuilder::collate: embeddings of different widths");
+        keys.push_back(kv.first);
+        for (int d = 0; d < F; ++d) table.push_back(kv.second[d]);
+    }
+    // map::at semantics up front: the exception type the reference's constructor lets escape
+    for (int k : node_keys)
+        if (atom_embeddings.find(k) == atom_embeddings.end()) throw std::out_of_range("map::at");
+    const dgnn_graphs v = as_cabi(g);
+    dgnn_collated c{};
+    std::vector<int32_t> nk(node_keys.begin(), node_keys.end());
+    const bool with_x = !keys.empty();
+    const int rc = dgnn_collate(impl_->ctx, &v, with_x ? nk.data() : nullptr, with_x ? keys.data() : nullptr,
+                                with_x ? table.data() : nullptr, static_cast<int32_t>(keys.size()), F, 0u, &c);
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::collate");
+    CollatedBatch out;
+    out.num_nodes = c.n_nodes;
+    out.num_edges = c.n_edges;
+    out.num_graphs = static_cast<int>(g.n_structs);
+    out.F = c.F;
+    out.K = c.K;
+    out.x = c.x;
+    out.edge_index = c.edge_index;
+    out.edge_attr = c.edge_attr;
+    out.batch = c.batch;
+    return out;
+}
+
+void BatchBuilder::copy_collated_to_host(const CollatedBatch& c, float* x, int64_t* edge_index, int64_t* batch) const {
+    dgnn_collated v{};
+    v.n_nodes = c.num_nodes;
+    v.n_edges = c.num_edges;
+    v.F = c.F;
+    v.K = c.K;
+    v.x = c.x;
+    v.edge_index = c.edge_index;
+    v.batch = c.batch;
+    v.edge_attr = c.edge_attr;
+    const int rc = dgnn_copy_collated_to_host(impl_->ctx, &v, x, edge_index, batch);
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::copy_collated_to_host");
+}
+
+EdgeViews BatchBuilder::edge_views(const BatchedGraphs& g, bool with_displacements) {
+    EdgeViews out;
+    const auto e = static_cast<size_t>(g.n_edges);
+    out.sources.resize(e);
+    out.targets.resize(e);
+    out.distances.resize(e);
+    if (with_displacements) out.displacements.resize(3 * e);
+    const dgnn_graphs v = as_cabi(g);
+    const int rc = dgnn_edge_views(impl_->ctx, &v, out.sources.data(), out.targets.data(), out.distances.data(),
+                                   with_displacements ? out.displacements.data() : nullptr);
+    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::edge_views");
+    return out;
 }
 
 void BatchBuilder::copy_edges_to_host(const BatchedGraphs& g, int64_t* row_ptr, int32_t* dst, int32_t* image,

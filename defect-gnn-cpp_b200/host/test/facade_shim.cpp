@@ -169,4 +169,53 @@ int facade_build_batch(int64_t n_structs, const int64_t* atom_offsets, const dou
     });
 }
 
+// Batched collation + viewer arrays through the facade: embeddings value = key + 0.25 * dim (as above).
+// missing_is_out_of_range: returns 2 when std::out_of_range escaped (the reference's map::at behaviour).
+int facade_collate_batch(int64_t n_structs, const int64_t* atom_offsets, const double* frac, const double* lattices,
+                         const int* types, double r_cutoff, uint64_t max_neighbors, double dr, int emb_dims,
+                         int n_emb_keys, const int* emb_keys, int64_t edge_cap, float* x, int64_t* edge_index,
+                         int64_t* batch, int* sources, int* targets, float* distances, float* displacements,
+                         int64_t* n_edges, int32_t* num_graphs) {
+    try {
+        std::vector<crystal::Structure> structs;
+        for (int64_t s = 0; s < n_structs; ++s)
+            structs.emplace_back(make_vasp(atom_offsets[s + 1] - atom_offsets[s], frac + 3 * atom_offsets[s],
+                                           lattices + 9 * s, types ? types + atom_offsets[s] : nullptr));
+        graph::SoABatch soa;
+        for (const auto& st : structs) soa.add(st);
+        graph::BatchParams p;
+        p.r_cutoff = r_cutoff;
+        p.max_neighbors = max_neighbors == std::numeric_limits<uint64_t>::max() ? std::numeric_limits<size_t>::max()
+                                                                                 : static_cast<size_t>(max_neighbors);
+        p.rbf_r_cutoff = r_cutoff;
+        p.dr = dr;
+        graph::BatchBuilder bb(0);
+        graph::BatchedGraphs g = bb.build(soa, p);
+        if (g.n_edges > edge_cap) throw std::runtime_error("edge_cap too small");
+        std::map<int, Eigen::VectorXd> emb;
+        for (int q = 0; q < n_emb_keys; ++q) {
+            Eigen::VectorXd v;
+            v.resize(emb_dims);
+            for (int d = 0; d < emb_dims; ++d) v[d] = emb_keys[q] + 0.25 * d;
+            emb[emb_keys[q]] = v;
+        }
+        graph::CollatedBatch c = bb.collate(g, soa.element, emb);
+        bb.copy_collated_to_host(c, x, edge_index, batch);
+        graph::EdgeViews v = bb.edge_views(g);
+        std::memcpy(sources, v.sources.data(), sizeof(int) * v.sources.size());
+        std::memcpy(targets, v.targets.data(), sizeof(int) * v.targets.size());
+        std::memcpy(distances, v.distances.data(), sizeof(float) * v.distances.size());
+        std::memcpy(displacements, v.displacements.data(), sizeof(float) * v.displacements.size());
+        *n_edges = g.n_edges;
+        *num_graphs = c.num_graphs;
+        return 0;
+    } catch (const std::out_of_range& e) {
+        g_err = e.what();
+        return 2;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
 }  // extern "C"

@@ -202,3 +202,53 @@ def test_batch_builder_facade(facade, oracle, c1_structures):
         assert np.max(np.abs(rbf[e0:e1] - ref) / ref) <= 1e-5
         e0 = e1
     assert seo[-1] == e0 == ne.value
+
+
+@pytest.mark.gpu
+def test_batch_builder_collate_and_edge_views(facade, oracle, c1_structures):
+    """BatchBuilder::collate (the planned train::BatchedGraph, device-resident) and ::edge_views (the viewer's flat
+    getters) against the numpy restatements of crystal_graph.cpp:15-40 / wasm_bindings.cpp:206-294."""
+    i32p, i64p, fp, dp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_float), C.POINTER(C.c_double)
+    facade.facade_collate_batch.argtypes = [C.c_int64, i64p, dp, dp, i32p, C.c_double, C.c_uint64, C.c_double, C.c_int,
+                                            C.c_int, i32p, C.c_int64, fp, i64p, i64p, i32p, i32p, fp, fp, i64p, i32p]
+    items = list(c1_structures.values())[:3]
+    fr = np.ascontiguousarray(np.concatenate([it[5] for it in items]))
+    Ls = np.ascontiguousarray(np.stack([it[3] for it in items]))
+    types = np.ascontiguousarray(np.concatenate([it[4] for it in items]).astype(np.int32))
+    offs = np.zeros(len(items) + 1, np.int64)
+    offs[1:] = np.cumsum([len(it[5]) for it in items])
+    n = int(offs[-1])
+    ecap, F = 20 * n, 8
+    keys = np.array(sorted(set(types.tolist())), np.int32)
+
+    def run(emb_keys):
+        x = np.zeros((n, F), np.float32)
+        ei = np.zeros((2, ecap), np.int64)
+        batch = np.zeros(n, np.int64)
+        src, tgt = np.zeros(ecap, np.int32), np.zeros(ecap, np.int32)
+        dist, disp = np.zeros(ecap, np.float32), np.zeros(3 * ecap, np.float32)
+        ne, ng = C.c_int64(), C.c_int32()
+        rc_ = facade.facade_collate_batch(len(items), _p(offs, C.c_int64), _p(fr, C.c_double), _p(Ls, C.c_double),
+                                          _p(types, C.c_int32), 10.0, C.c_uint64(20), 0.1, F, len(emb_keys),
+                                          _p(emb_keys, C.c_int32), ecap, _p(x, C.c_float), _p(ei, C.c_int64),
+                                          _p(batch, C.c_int64), _p(src, C.c_int32), _p(tgt, C.c_int32),
+                                          _p(dist, C.c_float), _p(disp, C.c_float), C.byref(ne), C.byref(ng))
+        return rc_, x, ei, batch, src, tgt, dist, disp, ne.value, ng.value
+
+    rc_, x, ei, batch, src, tgt, dist, disp, ne, ng = run(keys)
+    assert rc_ == 0, facade.facade_last_error()
+    assert ne == ecap and ng == len(items)      # capped at 20 neighbours: E = 20 N, and edge_index is [2, E] exactly
+    emb = {int(k): k + 0.25 * np.arange(F) for k in keys}
+    og = [oracle.neighbor_list(it[0], it[1], it[2], it[3], 10.0, 20, 1e-10, oracle.ALGO_CELLLIST) for it in items]
+    Xo, eio, bo = oracle.collate(og, [it[4] for it in items], emb)
+    assert np.array_equal(x, Xo) and np.array_equal(ei, eio) and np.array_equal(batch, bo)
+    e0 = 0
+    for it, o in zip(items, og):
+        so, to, do, po = oracle.viewer_arrays(o, oracle.displacements(it[0], it[1], it[2], it[3], o))
+        e1 = e0 + o.n_edges
+        assert np.array_equal(src[e0:e1], so) and np.array_equal(tgt[e0:e1], to)
+        assert np.array_equal(dist[e0:e1], do) and np.array_equal(disp[3 * e0:3 * e1], po)
+        e0 = e1
+    # a species without an embedding: std::out_of_range, like CrystalGraph's map::at (crystal_graph.cpp:20)
+    rc_ = run(keys[:-1])[0]
+    assert rc_ == 2

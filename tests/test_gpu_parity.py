@@ -325,3 +325,32 @@ def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
     big = syn.c2_batch(96, seed0=31000)
     check_batch(gb, oracle, big, 8.0, None, dr=0.2)
     gb.close()
+
+
+@pytest.mark.parametrize("opts", [{"upload_chunks": 3}, {"upload_chunks": 8, "onepass": 0}, {"upload_chunks": 5, "onepass": 0, "hit_cap": 0},
+                                  {"upload_chunks": 2, "direct_max_atoms": 150}])
+def test_chunked_upload_overlaps_count_pass(pkg, oracle, syn, opts):
+    """Host inputs travel in structure-aligned chunks on a copy stream while the prep + count pass of earlier chunks
+    run (dgnn_build, host-input path); chunk boundaries fall on empty structures, tiny and large ones."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("upload_min_atoms", 0)
+    for k, v in opts.items():
+        gb.set_option(k, v)
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    parts = [none, syn.triclinic_cell(31)[:4], syn.perovskite_supercell(4, 4, 2, seed=51)[:4], none, none,
+             syn.perovskite_supercell(3, 3, 3, seed=52)[:4], syn.triclinic_cell(33)[:4],
+             syn.perovskite_supercell(2, 2, 2, seed=53)[:4], syn.perovskite_supercell(4, 4, 2, seed=54)[:4], none]
+    b = syn.concat(parts)
+    check_batch(gb, oracle, b, 8.0, None, dr=0.2)
+    check_batch(gb, oracle, b, 10.0, 20, dr=0.1)
+    # pinned host tensors (the bench's e2e leg) and plain numpy give the same graphs
+    t = [torch.from_numpy(np.ascontiguousarray(a)).pin_memory() for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+    g = gb.build(*t, r_cutoff=8.0, max_neighbors=oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
+    h1 = gb.to_host(g)
+    h2 = build_and_fetch(gb, b, 8.0, oracle.UNCAPPED, 8.0, 0.2)
+    for f in ("row_ptr", "dst", "image", "dist", "rbf"):
+        assert np.array_equal(getattr(h1, f), getattr(h2, f)), f
+    gb.close()
