@@ -63,6 +63,7 @@ struct dgnn_ctx {
     long long upload_min_atoms = 1 << 18; // smaller batches go up in one piece
     cudaEvent_t copy_meta_ev = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
+    int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
@@ -324,6 +325,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "upload_chunks")) {
         if (!(value >= 1 && value <= 8)) return fail(ctx, DGNN_ERR_INVALID_ARG, "upload_chunks must be in [1, 8]");
         ctx->upload_chunks = (int)value;
+    } else if (!strcmp(name, "sym_count")) {
+        ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
     } else if (!strcmp(name, "onepass")) {
@@ -606,6 +609,12 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (!onepass) {
         // per upload chunk (structure-aligned): fractional coordinates, then the count pass of its rows -- the next
         // chunk's coordinates cross PCIe meanwhile
+        // without hit lists the count pass is symmetric: one sweep decides i -> j and j -> i (dgnn_direct.cu)
+        const bool sym = ctx->sym_count && D.hit_cap == 0 && eps_mode <= 1;
+        if (sym) {
+            D.sym_band = (D.near_d2_hi - D.near_d2_lo) + 1.0e-9 * r2;
+            CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
+        }
         for (int c = 0; c < n_up; ++c) {
             if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
             dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
@@ -613,7 +622,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             if (up_a[c + 1] > up_a[c]) {
                 D.row_begin = up_a[c];
                 D.row_end = up_a[c + 1];
-                CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+                if (sym) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
+                else CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
             }
         }
         D.row_begin = D.row_end = 0;

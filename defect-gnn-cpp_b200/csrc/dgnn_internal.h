@@ -154,6 +154,7 @@ struct DgDirectArgs {
     long long edge_cap;             // edges the output arrays can hold
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
     long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
+    double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -167,6 +168,7 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
                            const DgSmall* small, int* astruct, double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
+cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
 cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 // fill pass from the count pass's hit lists (rows with degree <= hit_cap and image range <= DG_HIT_NMAX)

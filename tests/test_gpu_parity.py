@@ -354,3 +354,30 @@ def test_chunked_upload_overlaps_count_pass(pkg, oracle, syn, opts):
     for f in ("row_ptr", "dst", "image", "dist", "rbf"):
         assert np.array_equal(getattr(h1, f), getattr(h2, f)), f
     gb.close()
+
+
+@pytest.mark.parametrize("sym", [0, 1])
+def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
+    """The symmetric count pass (one sweep decides i -> j and j -> i, the near-cutoff band recomputes the mirror) must
+    give the degrees and the near-cutoff statistic of the two-sided sweep: lattice sites exactly at r_c, skewed cells,
+    tiny cells with many images, coincident atoms, far-from-origin (unwrapped) coordinates."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    for k, v in (("onepass", 0), ("hit_cap", 0), ("sym_count", sym)):
+        gb.set_option(k, v)
+    sc3 = syn.simple_cubic(2.0, 3)
+    for rc in (4.0, 2.0, 2.0 * np.sqrt(2.0), 6.0):           # shells exactly at the cutoff: strict '<' on rounded d2
+        check_batch(gb, oracle, sc3, rc, None, algo=oracle.ALGO_BRUTE)
+    check_batch(gb, oracle, syn.adversarial_cells(), 8.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+    check_batch(gb, oracle, syn.c3_batch(80, seed0=7), 8.0, None, dr=0.2)
+    check_batch(gb, oracle, syn.c2_batch(6, seed0=123), 8.0, None, dr=0.2)
+    check_batch(gb, oracle, syn.c2_batch(4, seed0=321), 10.0, 20, dr=0.1)
+    # coincident atoms and an unwrapped, far-away copy of a structure (positions are never wrapped, rule R2)
+    x, y, z, L = syn.perovskite_supercell(2, 2, 2, seed=3)[:4]
+    x2, y2, z2 = np.append(x, x[5]), np.append(y, y[5]), np.append(z, z[5])
+    shift = 7.0 * L[0] - 5.0 * L[1] + 1000.0 * L[2]
+    far = (x + shift[0], y + shift[1], z + shift[2], L)
+    check_batch(gb, oracle, syn.concat([(x2, y2, z2, L), far]), 6.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+    gb.close()
