@@ -290,6 +290,15 @@ def main():
         top_bytes = E * (4 * K_BINS + 8)  # algorithmic: fp64 distance in, K fp32 out per edge
         top_name = "k_rbf_f32_vec4 (Gaussian RBF expansion, write phase)"
     achieved = top_bytes / (top_ms * 1e-3) / 1e9
+    # DRAM traffic of that kernel per launch from the committed `ncu --set full` capture of this workload
+    # (profiles/ncu_traffic.json, written by tools/ncu_traffic.py); null when the capture is of another size / kernel
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if int(tj["n_edges"]) == E and fused and ("k_direct_one" in tj["kernel"]) == bool(infos[-1].onepass):
+            traffic = float(tj["traffic"])
+    except Exception:
+        traffic = None
     launches = sum(i.kernel_launches for i in infos)
     all_bytes = (sum(int(t.numel() * t.element_size()) for t in d_in) + 8 * (b.n_atoms + 1) + E * (4 + 4 + 8)
                  + 4 * K_BINS * E)
@@ -305,7 +314,9 @@ def main():
         "roofline": {"bound": "hbm", "kernel": top_name,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "frac_of_8TBs_nominal": achieved / 8000.0, "peak_source": peak_src,
-                     "algorithmic_bytes_per_launch": top_bytes, "avg_launch_ms": top_ms, "traffic": None},
+                     "algorithmic_bytes_per_launch": top_bytes, "avg_launch_ms": top_ms, "traffic": traffic,
+                     "traffic_source": "profiles/ncu_traffic.json (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum)"
+                                       if traffic else None},
         "whole_path": {"algorithmic_bytes_per_step": all_bytes, "achieved_gbs": all_bytes / (ms / args.steps * 1e-3) / 1e9,
                        "frac_of_peak": all_bytes / (ms / args.steps * 1e-3) / 1e9 / peak},
         "phases_ms": {k: statistics.mean(getattr(i, k) for i in infos)

@@ -20,7 +20,7 @@ ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-fil
     > $out/${tag}_ncu_launches.log 2>&1
 echo "ncu launches exit $?"
 $CMD > $out/${tag}_plain2.log 2>&1 &&
-ncu --set full --clock-control none --import-source on -k "regex:^k_direct$|^k_fill_hits$" -s 6 -c 2 -f -o $out/${tag}_prof $CMD \
+ncu --set full --clock-control none --import-source on -k "regex:^k_direct$|^k_direct_count_sym$|^k_fill_hits$" -s 6 -c 2 -f -o $out/${tag}_prof $CMD \
     > $out/${tag}_ncu_full.log 2>&1
 echo "ncu full exit $?"
 ls -la $out
