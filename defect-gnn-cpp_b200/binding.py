@@ -14,6 +14,8 @@ import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(HERE, "libdgnn_b200.so")
+# (A/B experiments only: DGNN_LIB points at an alternative build of the same sources)
+LIB_PATH = os.environ.get("DGNN_LIB", LIB_PATH)
 
 UNCAPPED = 2**64 - 1
 INPUT_DEVICE = 0x1

@@ -901,8 +901,10 @@ __device__ __forceinline__ RowHead row_head_load(const DgDirectArgs& A, long lon
 
 // shared memory of one warp of k_fill_hits: d2 / hit words double buffered (the next row streams in with cp.async while
 // this one is sorted and emitted), sorted words, fp32 distances in row order, tie scratch
+__host__ __device__ inline size_t dg_fill_hits_sk_words(int W) { return ((size_t)DG_SK_WORDS(W) + 3) & ~(size_t)3; }
 __host__ __device__ inline size_t dg_fill_hits_warp_bytes(int W) {
-    return (size_t)2 * W * 8 + (size_t)2 * W * 4 + (size_t)W * 4 + (size_t)W * 4 + 16 + (size_t)2 * DG_STAGE_Q * 16;
+    return (size_t)2 * W * 8 + (size_t)2 * W * 4 + dg_fill_hits_sk_words(W) * 4 + (size_t)W * 4 + 16 +
+           (size_t)2 * DG_STAGE_Q * 16;
 }
 
 __global__ void __launch_bounds__(256, 3) k_fill_hits(const DgDirectArgs A) {
@@ -914,10 +916,10 @@ __global__ void __launch_bounds__(256, 3) k_fill_hits(const DgDirectArgs A) {
     unsigned char* base = smem_raw + (size_t)warp * dg_fill_hits_warp_bytes(W);
     double* rd = reinterpret_cast<double*>(base);                      // [2][W]
     uint32_t* hw = reinterpret_cast<uint32_t*>(base + (size_t)2 * W * 8);  // [2][W]
-    uint32_t* sk = hw + 2 * W;
-    float* fd = reinterpret_cast<float*>(sk + W);
+    uint32_t* sk = hw + 2 * W;  // padded (DG_SKI)
+    float* fd = reinterpret_cast<float*>(sk + dg_fill_hits_sk_words(W));
     int* tie = reinterpret_cast<int*>(fd + W);
-    float4* stage = reinterpret_cast<float4*>(base + (size_t)32 * W + 16);  // 2 x DG_STAGE_Q float4 (TMA source)
+    float4* stage = reinterpret_cast<float4*>(reinterpret_cast<unsigned char*>(tie) + 16);  // 2 x DG_STAGE_Q float4 (TMA source)
     unsigned seq = 0;
     const long long n_chunks = (A.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
 

@@ -319,6 +319,20 @@ struct DgFixedOffset {
     __device__ __forceinline__ long long get(int) { return o; }
 };
 
+// The sorted words leave the registers lane-major (position p = lane * EPL + r): with EPL = 4 / 8 / 16 a plain sk[p]
+// store puts the 32 lanes on 8 / 4 / 2 banks.  One pad word per 32 positions (DG_SK_PAD = 1) makes the store and the
+// later p = lane + 32 k reads conflict-free -- and the fill kernel 4 % SLOWER (same-box A/B: 8.69 vs 8.35 ms): the
+// kernel is bound by instruction issue, the extra index arithmetic costs more than the conflicts.  Kept off.
+#ifndef DG_SK_PAD
+#define DG_SK_PAD 0
+#endif
+#if DG_SK_PAD
+#define DG_SKI(p) ((p) + ((p) >> 5))
+#else
+#define DG_SKI(p) (p)
+#endif
+#define DG_SK_WORDS(n) ((n) + (((n) >> 5) + 4))
+
 template <int EPL, class Payload, class OP>
 __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
                                                          float* __restrict__ fd, int* __restrict__ tie,
@@ -398,13 +412,13 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
     // transpose through shared memory: coalesced CSR stores, and the run scan below needs random access
 #pragma unroll
     for (int r = 0; r < EPL; ++r)
-        if (lane * EPL + r < m) sk[lane * EPL + r] = v[r];
+        if (lane * EPL + r < m) sk[DG_SKI(lane * EPL + r)] = v[r];
     __syncwarp();
     const long long o = op.get(keep);
     if (o < 0) return o;
     if (!clash) {
         for (int p = lane; p < keep; p += 32) {
-            const int e = (int)(sk[p] & IDMASK);
+            const int e = (int)(sk[DG_SKI(p)] & IDMASK);
             const double d = rd[e];
             int j;
             uint32_t img;
@@ -416,20 +430,20 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
         }
     } else {
         for (int p = lane; p < m; p += 32) {
-            const uint32_t w = sk[p];
+            const uint32_t w = sk[DG_SKI(p)];
             const uint32_t tk = w & ~IDMASK;
             const int e = (int)(w & IDMASK);
             const double de = rd[e];
             int s = p, t = p + 1;
-            while (s > 0 && (sk[s - 1] & ~IDMASK) == tk) --s;
-            while (t < m && (sk[t] & ~IDMASK) == tk) ++t;
+            while (s > 0 && (sk[DG_SKI(s - 1)] & ~IDMASK) == tk) --s;
+            while (t < m && (sk[DG_SKI(t)] & ~IDMASK) == tk) ++t;
             int rank = p;
             if (t - s > 1) {  // run of equal truncated keys: exact canonical rank inside it
                 const unsigned long long ke = dg_payload_tie_key(P, e);
                 rank = s;
                 for (int q = s; q < t; ++q) {
                     if (q == p) continue;
-                    const int f = (int)(sk[q] & IDMASK);
+                    const int f = (int)(sk[DG_SKI(q)] & IDMASK);
                     const double df = rd[f];
                     if (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ++rank;
                 }
@@ -481,7 +495,8 @@ __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int
                                                     DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     if (m <= DG_BITONIC_MAX) {
         const RowBufPayload P{sm.rj, sm.rn};
-        const long long o = dg_row_sort_bitonic_any_op(sm.rd, sm.sk, sm.fd, sm.cnt, P, m, keep, key_scale, op, dst,
+        // padded sorted words: bs (unused by this path) and sk are adjacent, 2 * row_cap words
+        const long long o = dg_row_sort_bitonic_any_op(sm.rd, sm.bs, sm.fd, sm.cnt, P, m, keep, key_scale, op, dst,
                                                        image, dist, stats, lane);
         if (o >= 0 && rbf.K4 > 0) {
             dg_rbf_row(sm.fd, keep, o, lane, rbf);
