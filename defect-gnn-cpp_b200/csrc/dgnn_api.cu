@@ -63,6 +63,10 @@ struct dgnn_ctx {
     long long upload_min_atoms = 1 << 18; // smaller batches go up in one piece
     cudaEvent_t copy_meta_ev = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
+    int fill_hits_bulk = 1;               // k_fill_hits feature stores: bulk-copy engine (1) or st.global.cs (0)
+    int pipeline = 0;                     // fill of part k and count of part k+1 in one kernel.  Evaluated and kept OFF:
+                                          // the fill kernel is bound by instruction issue, the interleaved count does not
+                                          // hide (C2, same box: 11.12 ms against 10.37 ms with the passes back to back)
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
@@ -325,6 +329,10 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "upload_chunks")) {
         if (!(value >= 1 && value <= 8)) return fail(ctx, DGNN_ERR_INVALID_ARG, "upload_chunks must be in [1, 8]");
         ctx->upload_chunks = (int)value;
+    } else if (!strcmp(name, "fill_hits_bulk")) {
+        ctx->fill_hits_bulk = value != 0.0;
+    } else if (!strcmp(name, "pipeline")) {
+        ctx->pipeline = value != 0.0;
     } else if (!strcmp(name, "sym_count")) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
@@ -399,8 +407,18 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     const long long* d_off;
     const double *d_x, *d_y, *d_z, *d_lat;
     if (dev_in) {
-        CU(cudaMemcpyAsync(&N, b->atom_offsets + S, sizeof(long long), cudaMemcpyDeviceToHost, st));
+        // N and the structure-aligned part boundaries of the pipelined plan
+        const int np = S >= ctx->upload_chunks ? ctx->upload_chunks : 1;
+        for (int c = 0; c <= np; ++c)
+            CU(cudaMemcpyAsync(&up_a[c], b->atom_offsets + S * c / np, sizeof(long long), cudaMemcpyDeviceToHost, st));
         CU(cudaStreamSynchronize(st));
+        N = up_a[np];
+        if (N >= ctx->upload_min_atoms && np > 1) {
+            n_up = np;
+        } else {
+            up_a[0] = 0;
+            up_a[1] = N;
+        }
         d_off = (const long long*)b->atom_offsets;
         d_x = b->x; d_y = b->y; d_z = b->z; d_lat = b->lattice;
     } else {
@@ -411,7 +429,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         N = b->atom_offsets[S];
     }
     if (N < 0 || N >= 0x7fffffffLL) return fail(ctx, DGNN_ERR_TOO_LARGE, "atom count %lld out of range", N);
-    up_a[1] = N;
+    if (n_up == 1) up_a[1] = N;
+    for (int c = 0; c < n_up; ++c)
+        if (up_a[c + 1] < up_a[c] || up_a[c] < 0 || up_a[c + 1] > N)
+            return fail(ctx, DGNN_ERR_INVALID_ARG, "atom_offsets not monotone");
     if (N > 0 && (!b->x || !b->y || !b->z)) return fail(ctx, DGNN_ERR_INVALID_ARG, "coordinate pointer is null");
     if (S > 0 && !b->lattice) return fail(ctx, DGNN_ERR_INVALID_ARG, "lattice pointer is null");
     if (!dev_in) {
@@ -543,7 +564,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // ---- single-pass build (direct-path batches): traversal + look-back row offsets + sort + emit in one kernel --
     // The edge arena and the row buffers are sized from the density estimate; rows that outgrow the buffer, or an
     // arena that turns out too small, are completed by the regular fill pass afterwards (row_ptr is final either way).
-    bool onepass = false, onepass_fused_rbf = false;
+    bool onepass = false, onepass_fused_rbf = false, pipelined = false;
     int row_cap_1p = 0;
     // Auto policy: the look-back couples every CTA to its predecessors with one step of slack, which costs large batches
     // more than the count pass saves (C2 10 k structures: 11.8 ms vs 10.9 ms count + fill), but a batch of a few steps
@@ -615,19 +636,94 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             D.sym_band = (D.near_d2_hi - D.near_d2_lo) + 1.0e-9 * r2;
             CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
         }
-        for (int c = 0; c < n_up; ++c) {
-            if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
-            dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
-                                  (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
-            if (up_a[c + 1] > up_a[c]) {
-                D.row_begin = up_a[c];
-                D.row_end = up_a[c + 1];
-                if (sym) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
-                else CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+        // Pipelined plan (large direct-path batches, symmetric count): the fill of part k and the count of part k+1
+        // share one kernel, so the issue-bound count hides under the store-bound fill.  Row offsets chain from part to
+        // part on the device; arena and row buffer come from the density estimate like the single-pass plan's.
+        DgDirectArgs F = D;
+        if (sym && ctx->pipeline && n_up >= 2 && have_est && ctx->h_stats->err_status == 0 &&
+            ctx->h_stats->n_cell_structs == 0 && ctx->direct_min_blocks <= 2) {
+            const long long est = ctx->h_stats->est_deg;
+            long long rc = est + est / 8 + 8;
+            if (rc > DGNN_MAX_DEGREE) rc = DGNN_MAX_DEGREE;
+            if (ctx->onepass_row_cap > 0) rc = ctx->onepass_row_cap;
+            row_cap_1p = round_up((int)(rc > 32 ? rc : 32), 32);
+            double est_e = (double)ctx->h_stats->est_edges;
+            if (est_e > (double)N * (double)max_nb) est_e = (double)N * (double)max_nb;
+            est_e = est_e * ctx->onepass_arena_scale + (ctx->onepass_arena_scale >= 1.0 ? 64.0 * 1024.0 : 0.0);
+            F.row_cap = row_cap_1p;
+            F.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap_1p <= 256 ? 256 : (row_cap_1p <= 1024 ? 512 : 1024));
+            F.n_warps = 8;
+            if ((int)dg_direct_smem_bytes(F, true) <= ctx->smem_optin && est_e < 9.0e18) {
+                const size_t e_est = (size_t)est_e;
+                ENSURE(ctx->dst, (e_est + 1) * 4);
+                ENSURE(ctx->image, (e_est + 1) * 4);
+                ENSURE(ctx->dist, (e_est + 1) * 8);
+                if (want_rbf) ENSURE(ctx->rbf, e_est * (size_t)K * 4 + 16);
+                size_t cap_e = ctx->dst.cap / 4;
+                if (ctx->image.cap / 4 < cap_e) cap_e = ctx->image.cap / 4;
+                if (ctx->dist.cap / 8 < cap_e) cap_e = ctx->dist.cap / 8;
+                if (want_rbf && (ctx->rbf.cap - 16) / ((size_t)K * 4) < cap_e) cap_e = (ctx->rbf.cap - 16) / ((size_t)K * 4);
+                F.edge_cap = (long long)cap_e - 1;
+                F.row_ptr = (const long long*)ctx->row_ptr.p;
+                F.dst = (int*)ctx->dst.p;
+                F.image = (uint32_t*)ctx->image.p;
+                F.dist = (double*)ctx->dist.p;
+                const int keep_max_1p = row_cap_1p < max_nb ? row_cap_1p : max_nb;
+                onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 &&
+                                    (long long)keep_max_1p * (K / 4) < (1LL << 22);
+                if (onepass_fused_rbf) {
+                    F.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+                    F.rbf.recur = ctx->rbf_recur;
+                }
+                pipelined = true;
             }
         }
-        D.row_begin = D.row_end = 0;
-        dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+        if (pipelined) {
+            if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[0], 0));
+            dg_launch_direct_prep(st, up_a[0], up_a[1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
+                                  (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+            D.row_begin = up_a[0];
+            D.row_end = up_a[1];
+            if (up_a[1] > up_a[0]) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
+            CU(cudaEventRecord(ctx->ev.e[3], st));
+            for (int c = 0; c < n_up; ++c) {
+                const long long p0 = up_a[c], p1 = up_a[c + 1];
+                dg_scan_i32_i64_based(st, (const int*)ctx->deg.p + p0, (long long*)ctx->row_ptr.p + p0, p1 - p0,
+                                      (long long*)ctx->scratch.p, c > 0 ? (const long long*)ctx->row_ptr.p + p0 : nullptr);
+                F.row_begin = p0;
+                F.row_end = p1;
+                F.cnt_begin = F.cnt_end = 0;
+                if (c + 1 < n_up) {
+                    if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c + 1], 0));
+                    dg_launch_direct_prep(st, up_a[c + 1], up_a[c + 2], S, d_off, d_x, d_y, d_z, small,
+                                          (int*)ctx->astruct.p, (double*)ctx->fa.p, (double*)ctx->fb.p,
+                                          (double*)ctx->fc.p, d_stats);
+                    F.cnt_begin = up_a[c + 1];
+                    F.cnt_end = up_a[c + 2];
+                }
+                if (p1 > p0 || F.cnt_end > F.cnt_begin) CU(dg_launch_direct_fill_cnt(st, F, ctx->sm_count));
+                if (c + 1 < n_up && up_a[c + 2] > up_a[c + 1]) {
+                    D.row_begin = up_a[c + 1];
+                    D.row_end = up_a[c + 2];
+                    dg_launch_cap_degrees(st, D, ctx->sm_count);
+                }
+            }
+            D.row_begin = D.row_end = 0;
+        } else {
+            for (int c = 0; c < n_up; ++c) {
+                if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
+                dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
+                                      (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+                if (up_a[c + 1] > up_a[c]) {
+                    D.row_begin = up_a[c];
+                    D.row_end = up_a[c + 1];
+                    if (sym) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
+                    else CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+                }
+            }
+            D.row_begin = D.row_end = 0;
+            dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+        }
     }
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
     CU(cudaGetLastError());
@@ -641,7 +737,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (ctx->h_stats->lb_timeout) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
     int n_fallback_rows = ctx->h_stats->n_fallback_rows;
-    const bool onepass_redo_all = onepass && ctx->h_stats->cap_overflow != 0;
+    const bool onepass_redo_all = (onepass || pipelined) && ctx->h_stats->cap_overflow != 0;
 
     // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
     DgTraverseArgs A;
@@ -759,7 +855,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         n_fallback_rows = ctx->h_stats->n_fallback_rows;
     }
-    if (!onepass) CU(cudaEventRecord(ctx->ev.e[3], st));
+    if (!onepass && !pipelined) CU(cudaEventRecord(ctx->ev.e[3], st));
     const long long E = ctx->h_stats->n_edges;
     const int max_deg = ctx->h_stats->max_deg;
     if (max_deg > DGNN_MAX_DEGREE)
@@ -780,7 +876,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.n_warps = 8;
     // fused RBF epilogue: rows stream their K features right after the sort (needs K % 4 == 0 for the float4 stores)
     const int keep_max = max_deg < max_nb ? max_deg : max_nb;
-    const bool fuse_rbf = onepass ? (onepass_fused_rbf && E > 0)
+    const bool fuse_rbf = (onepass || pipelined) ? (onepass_fused_rbf && E > 0)
                                   : (want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
                                      (long long)keep_max * (K / 4) < (1LL << 22));
     if (want_rbf && E > 0) ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
@@ -793,18 +889,31 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
     // rows with a stored hit list are filled from it; the traversal fill pass takes whatever is left
     DgDirectArgs H = D;
+    H.fill_hits_bulk = ctx->fill_hits_bulk;
     if (n_cell_structs > 0) {
         H.cloud_j = (const int*)ctx->cj.p;
         H.cloud_n = (const uint32_t*)ctx->cn.p;
     }
-    bool use_hits = hit_cap > 0 && !onepass;
+    bool use_hits = hit_cap > 0 && !onepass && !pipelined;
+    if (pipelined) {
+        // rows within the estimated row buffer are written; longer ones (and everything, if the estimated arena was
+        // too small and has just been regrown) go through the regular fill pass
+        D.hit_cap = 0;
+        D.skip_deg_le = onepass_redo_all ? 0 : row_cap_1p;
+        if (E > 0 && (onepass_redo_all || max_deg > row_cap_1p)) {
+            if (onepass_redo_all) CU(cudaMemsetAsync(&((DgStats*)ctx->stats.p)->n_tie_rows, 0, sizeof(int), st));
+            CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+        }
+    }
     if (onepass) {
         // everything is already written, except rows that outgrew the estimated row buffer (or all rows, when the
         // estimated arena was too small and has just been regrown by the ENSUREs above)
         D.hit_cap = 0;
         D.skip_deg_le = onepass_redo_all ? 0 : row_cap_1p;
-        if (E > 0 && (onepass_redo_all || n_fallback_rows > 0))
+        if (E > 0 && (onepass_redo_all || n_fallback_rows > 0)) {
+            if (onepass_redo_all) CU(cudaMemsetAsync(&((DgStats*)ctx->stats.p)->n_tie_rows, 0, sizeof(int), st));
             CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+        }
     }
     if (use_hits) {
         H.n_warps = 8;
@@ -813,7 +922,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     if (!use_hits) D.hit_cap = 0;
     if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
-    if (E > 0 && !onepass && (!use_hits || n_fallback_rows > 0))
+    if (E > 0 && !onepass && !pipelined && (!use_hits || n_fallback_rows > 0))
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
     if (n_cell_structs > 0 && E > 0 && (!use_hits || n_fallback_rows > 0)) {
         A.hit_cap = use_hits ? hit_cap : 0;
@@ -885,6 +994,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.rbf_fused = fuse_rbf ? 1 : 0;
     I.hit_cap = use_hits ? hit_cap : 0;
     I.onepass = onepass ? (onepass_redo_all ? 2 : 1) : 0;
+    I.pipeline_parts = pipelined ? n_up : 0;
+    I.pipeline_refill = pipelined ? (onepass_redo_all ? 2 : (max_deg > row_cap_1p ? 1 : 0)) : 0;
     I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
     return DGNN_OK;
 }

@@ -723,6 +723,97 @@ __global__ void __launch_bounds__(256, MINB) k_direct_count_sym(const DgDirectAr
     if (lane == 0 && near) atomicAdd(&A.stats->n_near, (unsigned long long)near);
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Pipelined plan: the batch is cut into structure-aligned parts; this kernel FILLS part k (rows [row_begin, row_end),
+// offsets from the scan of the part's degrees) and runs the symmetric COUNT of part k+1 (rows [cnt_begin, cnt_end)) in
+// the same warps, row by row.  The fill is bound by its stores, the count by instruction issue: interleaved they share
+// the SM instead of running back to back.  Arena and row buffer come from the density estimate: rows that would not
+// fit the arena raise cap_overflow (the host regrows and refills), rows longer than the row buffer are left to a
+// regular fill pass (skip_deg_le).
+// ---------------------------------------------------------------------------------------------------------------------
+template <int EPS>
+__global__ void __launch_bounds__(256, 2) k_direct_fill_cnt(const DgDirectArgs A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const RowBuf rb = dg_rowbuf_carve(smem_raw + (size_t)warp * dg_rowbuf_bytes(A.row_cap, A.n_buckets), A.row_cap);
+    const RowBuf none = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned near = 0, dummy = 0;
+    const long long r0 = A.row_begin, r1 = A.row_end, c0 = A.cnt_begin, c1 = A.cnt_end;
+    const long long nrows = (r1 - r0) > (c1 - c0) ? (r1 - r0) : (c1 - c0);
+    const long long n_chunks = (nrows + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const long long k_end = (chunk + 1) * DG_ROW_CHUNK < nrows ? (chunk + 1) * DG_ROW_CHUNK : nrows;
+        for (long long k = chunk * DG_ROW_CHUNK + warp; k < k_end; k += nwarps) {
+            const long long a = r0 + k;
+            if (a < r1) {  // ---- fill one row of part k ----
+                const DgSmall* __restrict__ G = A.small + A.astruct[a];
+                const int mode = G->mode;
+                const int deg = A.deg_raw[a];
+                if (mode != DG_MODE_CELL && G->status == DG_ST_OK && deg <= A.row_cap) {
+                    const long long o = A.row_ptr[a];
+                    const int keep = deg < A.max_neighbors ? deg : A.max_neighbors;
+                    if (o + keep > A.edge_cap) {
+                        if (lane == 0) atomicExch(&A.stats->cap_overflow, 1);
+                    } else {
+                        const int m = traverse_row<true, EPS, false, false>(A, G, a, mode, rb, nullptr, nullptr, lane,
+                                                                            lt_mask, dummy);
+                        if (m != deg) {  // cannot happen: both passes evaluate the same predicate
+                            if (lane == 0) atomicExch(&A.stats->overflow, 1);
+                        } else {
+                            dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, o, A.dst, A.image, A.dist,
+                                             A.stats, lane, A.rbf);
+                        }
+                    }
+                }
+            }
+            const long long a2 = c0 + k;
+            if (a2 < c1) {  // ---- count one row of part k+1 ----
+                const DgSmall* __restrict__ G = A.small + A.astruct[a2];
+                const int mode = G->mode;
+                if (mode != DG_MODE_CELL && G->status == DG_ST_OK) {
+                    if (mode == DG_MODE_ATOMPAR) {
+                        sweep_row_sym<EPS>(A, G, a2, lane, near);
+                    } else {
+                        int m = traverse_row<false, EPS, false, false>(A, G, a2, mode, none, nullptr, nullptr, lane,
+                                                                       lt_mask, near);
+                        m = __reduce_add_sync(FULL_MASK, m);
+                        if (lane == 0 && m) atomicAdd(A.deg_raw + a2, m);
+                    }
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) near += __shfl_xor_sync(FULL_MASK, near, o);
+    if (lane == 0 && near) atomicAdd(&A.stats->n_near, (unsigned long long)near);
+}
+
+template <int EPS>
+static cudaError_t launch_fill_cnt_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(k_direct_fill_cnt<EPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct_fill_cnt<EPS>, a.n_warps * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) occ = 1;
+    const long long fr = a.row_end - a.row_begin, cr = a.cnt_end - a.cnt_begin;
+    const long long want = ((fr > cr ? fr : cr) + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    long long grid = (long long)sm_count * occ;
+    if (grid > want) grid = want;
+    if (grid < 1) return cudaSuccess;
+    k_direct_fill_cnt<EPS><<<(unsigned)grid, a.n_warps * 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
+// fill rows [row_begin, row_end) + symmetric count of rows [cnt_begin, cnt_end) (may be empty); eps_mode 0 or 1
+cudaError_t dg_launch_direct_fill_cnt(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
+    if (a.eps_mode > 1) return cudaErrorInvalidValue;
+    const size_t smem = dg_direct_smem_bytes(a, true);
+    ++g_direct_launches;
+    return a.eps_mode == 0 ? launch_fill_cnt_t<0>(st, a, sm_count, smem) : launch_fill_cnt_t<1>(st, a, sm_count, smem);
+}
+void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count);
+
 // deg_capped = min(deg_raw, max_neighbors) and the largest row, after the symmetric count pass (direct-path rows only)
 __global__ void __launch_bounds__(256) k_cap_degrees(const DgDirectArgs A) {
     const long long r0 = A.row_begin, r1 = A.row_end > 0 ? A.row_end : A.n_atoms;
@@ -761,6 +852,14 @@ static cudaError_t launch_count_sym_m(cudaStream_t st, const DgDirectArgs& a, in
     k_cap_degrees<<<(unsigned)g2, 256, 0, st>>>(a);
     g_direct_launches += 2;
     return cudaGetLastError();
+}
+void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
+    const long long rows = (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
+    if (rows <= 0) return;
+    long long g2 = (rows + 255) / 256;
+    if (g2 > (long long)sm_count * 8) g2 = (long long)sm_count * 8;
+    k_cap_degrees<<<(unsigned)g2, 256, 0, st>>>(a);
+    ++g_direct_launches;
 }
 // symmetric count pass of rows [row_begin, row_end): deg_raw must be zero there; eps_mode 0 or 1 only
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks) {
@@ -969,7 +1068,8 @@ __global__ void __launch_bounds__(256, 3) k_fill_hits(const DgDirectArgs A) {
                                         A.dist, A.stats, lane);
             }
             if (A.rbf.K4 > 0) {
-                dg_rbf_row_bulk(fd, keep, cur.o, lane, A.rbf, stage, seq);
+                if (A.fill_hits_bulk) dg_rbf_row_bulk(fd, keep, cur.o, lane, A.rbf, stage, seq);
+                else dg_rbf_row(fd, keep, cur.o, lane, A.rbf);
                 __syncwarp();
             }
         }

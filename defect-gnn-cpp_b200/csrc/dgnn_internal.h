@@ -110,6 +110,9 @@ void dg_launch_finish_rows(cudaStream_t st, long long N, long long S, const long
                            const long long* row_ptr, long long* struct_edge_offsets, DgStats* stats);
 // exclusive scan int32 -> int64, out has n+1 entries (out[n] = total); scratch >= n/2048 + 2 entries
 void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch);
+// same, offsets start at *base (device pointer, may be null = 0): chains the scans of consecutive parts
+void dg_scan_i32_i64_based(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch,
+                           const long long* base);
 int dg_num_kernel_launches_reset();  // returns launches since last reset
 
 // ---- dgnn_direct.cu: direct (small-structure) path ----
@@ -154,6 +157,8 @@ struct DgDirectArgs {
     long long edge_cap;             // edges the output arrays can hold
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
     long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
+    long long cnt_begin, cnt_end;   // k_direct_fill_cnt: rows whose symmetric count runs next to the fill of [row_begin, row_end)
+    int fill_hits_bulk;             // k_fill_hits: features through the bulk-copy engine (1) or st.global.cs (0)
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
 };
 #define DG_EPS_FAST 1.0e-3
@@ -168,6 +173,8 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
                            const DgSmall* small, int* astruct, double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
+cudaError_t dg_launch_direct_fill_cnt(cudaStream_t st, const DgDirectArgs& a, int sm_count);
+void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count);
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
 cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);

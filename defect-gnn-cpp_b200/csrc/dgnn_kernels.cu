@@ -78,10 +78,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_reduce(const int* __restr
 }
 
 // single block: exclusive scan of bsum[0..nb) in place, bsum[nb] = grand total
-__global__ void __launch_bounds__(1024) k_scan_bsums(long long* bsum, long long nb) {
+__global__ void __launch_bounds__(1024) k_scan_bsums(long long* bsum, long long nb, const long long* base) {
     __shared__ long long s_warp[33];
     __shared__ long long s_carry;
-    if (threadIdx.x == 0) s_carry = 0;
+    if (threadIdx.x == 0) s_carry = base ? *base : 0;
     __syncthreads();
     for (long long base = 0; base < nb; base += blockDim.x) {
         const long long idx = base + threadIdx.x;
@@ -123,19 +123,23 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_apply(const int* __restri
     if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = bsum[nb];
 }
 
-__global__ void k_scan_empty(long long* out) { out[0] = 0; }
+__global__ void k_scan_empty(long long* out, const long long* base) { out[0] = base ? *base : 0; }
 
-void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch) {
+void dg_scan_i32_i64_based(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch,
+                           const long long* base) {
     if (n <= 0) {
-        k_scan_empty<<<1, 1, 0, st>>>(out);
+        k_scan_empty<<<1, 1, 0, st>>>(out, base);
         DG_COUNT_LAUNCH();
         return;
     }
     const long long nb = (n + SCAN_TILE - 1) / SCAN_TILE;
     k_scan_reduce<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n, scratch);
-    k_scan_bsums<<<1, 1024, 0, st>>>(scratch, nb);
+    k_scan_bsums<<<1, 1024, 0, st>>>(scratch, nb, base);
     k_scan_apply<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n, scratch, out, nb);
     g_launches += 3;
+}
+void dg_scan_i32_i64(cudaStream_t st, const int* in, long long* out, long long n, long long* scratch) {
+    dg_scan_i32_i64_based(st, in, out, n, scratch, nullptr);
 }
 
 // =====================================================================================================================

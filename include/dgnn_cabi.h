@@ -190,6 +190,9 @@ typedef struct {
     int32_t onepass;         /* 1: single-pass build (no count pass; row offsets by look-back), 2: its estimated edge
                               * arena was too small and the fill pass rewrote every row, 0: count + fill */
     int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
+    int32_t pipeline_parts;  /* > 0: pipelined plan, fill of part k + count of part k+1 per kernel, this many parts */
+    int32_t pipeline_refill; /* pipelined plan: 1 = a fill pass completed rows beyond the estimated row buffer,
+                              * 2 = the estimated arena was too small and the fill pass rewrote every row */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 

@@ -381,3 +381,53 @@ def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
     far = (x + shift[0], y + shift[1], z + shift[2], L)
     check_batch(gb, oracle, syn.concat([(x2, y2, z2, L), far]), 6.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
     gb.close()
+
+
+@pytest.mark.parametrize("opts,refill", [
+    ({"upload_chunks": 2}, 0),
+    ({"upload_chunks": 5}, 0),
+    ({"upload_chunks": 4, "onepass_row_cap": 64}, 1),          # rows beyond the estimated row buffer -> fill pass
+    ({"upload_chunks": 3, "onepass_arena_scale": 0.25}, 2),    # estimated arena too small -> everything refilled
+    ({"upload_chunks": 4, "rbf_recur": 0}, 0),
+])
+@pytest.mark.parametrize("device_inputs", [False, True])
+def test_pipelined_plan_fill_and_count_share_a_kernel(pkg, oracle, syn, opts, refill, device_inputs):
+    """Large direct-path batches: fill of part k + symmetric count of part k+1 in one kernel, offsets chained on the
+    device, arena / row buffer from the density estimate with both recovery routes."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("upload_min_atoms", 0)
+    gb.set_option("onepass", 0)
+    gb.set_option("pipeline", 1)          # off by default (measured slower than the passes back to back)
+    for k, v in opts.items():
+        gb.set_option(k, v)
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    parts = [syn.perovskite_supercell(4, 4, 2, seed=61)[:4], none, syn.triclinic_cell(41)[:4],
+             syn.perovskite_supercell(3, 3, 3, seed=62)[:4], syn.perovskite_supercell(4, 4, 2, seed=63)[:4],
+             syn.triclinic_cell(43)[:4], none, syn.perovskite_supercell(4, 4, 4, seed=64)[:4],
+             syn.perovskite_supercell(2, 2, 2, seed=65)[:4], syn.perovskite_supercell(4, 4, 2, seed=66)[:4]]
+    b = syn.concat(parts)
+    if device_inputs:
+        dev = torch.device("cuda:0")
+        t = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+        torch.cuda.synchronize()
+        g = gb.build(*t, r_cutoff=8.0, max_neighbors=oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2, device_inputs=True)
+        h = gb.to_host(g)
+        info = gb.info()
+        e0 = 0
+        for s in range(b.n_structs):
+            o = oracle.neighbor_list(*b.structure(s), 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
+            e0 = assert_graph_equal(h, e0, int(b.atom_offsets[s]), int(b.atom_offsets[s + 1]), o, what=f"structure {s}")
+        assert e0 == h.n_edges
+    else:
+        check_batch(gb, oracle, b, 8.0, None, dr=0.2)
+        info = gb.info()
+    assert info.pipeline_parts == opts["upload_chunks"] and info.onepass == 0
+    assert info.pipeline_refill == refill
+    if not device_inputs:
+        check_batch(gb, oracle, b, 10.0, None, dr=0.1)        # K = 100, longer rows
+        check_batch(gb, oracle, b, 8.0, None, dr=0.3)         # K = 26: separate RBF launch
+        check_batch(gb, oracle, b, 8.0, None)                 # no features (still no hit lists: bytes/pair < 64 -> hits)
+    gb.close()
