@@ -1,0 +1,195 @@
+// io::load_vasp_batch -- multi-threaded POSCAR -> SoA ingest (see io/vasp_batch.hpp).
+#include "io/vasp_batch.hpp"
+
+#include <atomic>
+#include <cctype>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <stdexcept>
+#include <thread>
+
+namespace defect_gnn::io {
+
+namespace {
+
+struct Cursor {
+    const char* p;
+    const char* end;
+    // [b, e) of the next line (without the terminator); false at end of input
+    bool line(const char*& b, const char*& e) {
+        if (p >= end) return false;
+        b = p;
+        const char* nl = static_cast<const char*>(memchr(p, '\n', static_cast<size_t>(end - p)));
+        e = nl ? nl : end;
+        p = nl ? nl + 1 : end;
+        if (e > b && e[-1] == '\r') --e;
+        return true;
+    }
+};
+
+// up to `want` doubles from [b, e); returns how many were read (operator>> stops at the first non-number, too)
+int read_doubles(const char* b, const char* e, double* out, int want) {
+    char buf[512];
+    const size_t n = static_cast<size_t>(e - b) < sizeof(buf) - 1 ? static_cast<size_t>(e - b) : sizeof(buf) - 1;
+    memcpy(buf, b, n);
+    buf[n] = '\0';
+    char* q = buf;
+    int got = 0;
+    while (got < want) {
+        char* r = nullptr;
+        const double v = strtod(q, &r);
+        if (r == q) break;
+        out[got++] = v;
+        q = r;
+    }
+    return got;
+}
+
+struct Parsed {
+    double lattice[9];
+    std::vector<double> x, y, z;
+    std::vector<int> element;
+};
+
+void parse_text(const char* text, size_t len, Parsed& out, const std::string& what) {
+    Cursor c{text, text + len};
+    const char *b, *e;
+    auto need = [&](const char* which) {
+        if (!c.line(b, e)) throw std::runtime_error("parse_vasp: unexpected end of input (" + std::string(which) + ") in " + what);
+    };
+    need("comment");
+    need("scale");
+    double scale = 1.0;
+    if (read_doubles(b, e, &scale, 1) != 1) throw std::runtime_error("parse_vasp: bad scale in " + what);
+    for (int i = 0; i < 3; ++i) {
+        need("lattice");
+        if (read_doubles(b, e, out.lattice + 3 * i, 3) != 3) throw std::runtime_error("parse_vasp: bad lattice row in " + what);
+    }
+    for (double& v : out.lattice) v *= scale;  // vasp.lattice *= scale_factor
+    need("elements");
+    int n_sym = 0;
+    for (const char* q = b; q < e;) {
+        while (q < e && isspace(static_cast<unsigned char>(*q))) ++q;
+        if (q < e) ++n_sym;
+        while (q < e && !isspace(static_cast<unsigned char>(*q))) ++q;
+    }
+    need("counts");
+    std::vector<int> counts;
+    {
+        double tmp[64];
+        const int n = read_doubles(b, e, tmp, 64);
+        for (int i = 0; i < n; ++i) counts.push_back(static_cast<int>(tmp[i]));
+    }
+    if (counts.empty() || static_cast<int>(counts.size()) != n_sym)
+        throw std::runtime_error("parse_vasp: element / count lines do not match in " + what);
+    need("mode");
+    auto first = [&]() {
+        for (const char* q = b; q < e; ++q)
+            if (!isspace(static_cast<unsigned char>(*q))) return static_cast<char>(tolower(static_cast<unsigned char>(*q)));
+        return '\0';
+    };
+    if (first() == 's') need("mode");  // Selective dynamics
+    const char m = first();
+    const bool cartesian = m == 'c' || m == 'k';
+    const double* L = out.lattice;
+    // inverse lattice (for Cartesian input): frac = cart * L^-1  <=>  frac_k = sum_r cart_r * inv[r][k]
+    double inv[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (cartesian) {
+        const double c00 = L[4] * L[8] - L[5] * L[7], c01 = L[5] * L[6] - L[3] * L[8], c02 = L[3] * L[7] - L[4] * L[6];
+        const double det = L[0] * c00 + L[1] * c01 + L[2] * c02;
+        if (det == 0.0) throw std::runtime_error("parse_vasp: singular lattice in " + what);
+        const double id = 1.0 / det;
+        inv[0] = c00 * id; inv[1] = (L[2] * L[7] - L[1] * L[8]) * id; inv[2] = (L[1] * L[5] - L[2] * L[4]) * id;
+        inv[3] = c01 * id; inv[4] = (L[0] * L[8] - L[2] * L[6]) * id; inv[5] = (L[2] * L[3] - L[0] * L[5]) * id;
+        inv[6] = c02 * id; inv[7] = (L[1] * L[6] - L[0] * L[7]) * id; inv[8] = (L[0] * L[4] - L[1] * L[3]) * id;
+    }
+    long total = 0;
+    for (int n : counts) total += n;
+    out.x.reserve(static_cast<size_t>(total));
+    out.y.reserve(static_cast<size_t>(total));
+    out.z.reserve(static_cast<size_t>(total));
+    out.element.reserve(static_cast<size_t>(total));
+    for (size_t el = 0; el < counts.size(); ++el) {
+        for (int k = 0; k < counts[el]; ++k) {
+            need("coordinates");
+            double f[3];
+            if (read_doubles(b, e, f, 3) != 3) throw std::runtime_error("parse_vasp: bad coordinate line in " + what);
+            if (cartesian) {
+                const double cx = f[0] * scale, cy = f[1] * scale, cz = f[2] * scale;
+                f[0] = cx * inv[0] + cy * inv[3] + cz * inv[6];
+                f[1] = cx * inv[1] + cy * inv[4] + cz * inv[7];
+                f[2] = cx * inv[2] + cy * inv[5] + cz * inv[8];
+            }
+            // position = lattice^T * frac (structure.cpp:17): component k = e0 + (e1 + e2), e_r = L(r,k) f_r -- the
+            // order of Eigen's unrolled 3-term reduction (same as the facade's Structure)
+            out.x.push_back(L[0] * f[0] + (L[3] * f[1] + L[6] * f[2]));
+            out.y.push_back(L[1] * f[0] + (L[4] * f[1] + L[7] * f[2]));
+            out.z.push_back(L[2] * f[0] + (L[5] * f[1] + L[8] * f[2]));
+            out.element.push_back(static_cast<int>(el));
+        }
+    }
+}
+
+void append(const Parsed& p, graph::SoABatch& batch) {
+    batch.x.insert(batch.x.end(), p.x.begin(), p.x.end());
+    batch.y.insert(batch.y.end(), p.y.begin(), p.y.end());
+    batch.z.insert(batch.z.end(), p.z.begin(), p.z.end());
+    batch.element.insert(batch.element.end(), p.element.begin(), p.element.end());
+    batch.lattice.insert(batch.lattice.end(), p.lattice, p.lattice + 9);
+    batch.atom_offsets.push_back(batch.atom_offsets.back() + static_cast<int64_t>(p.x.size()));
+}
+
+}  // namespace
+
+void append_vasp_text(const char* text, size_t len, graph::SoABatch& batch) {
+    Parsed p;
+    parse_text(text, len, p, "<text>");
+    append(p, batch);
+}
+
+graph::SoABatch load_vasp_batch(const std::vector<std::string>& paths, unsigned n_threads) {
+    const size_t n = paths.size();
+    std::vector<Parsed> parsed(n);
+    std::vector<std::string> errors(n);
+    if (n_threads == 0) n_threads = std::thread::hardware_concurrency();
+    if (n_threads == 0) n_threads = 1;
+    if (n_threads > n) n_threads = static_cast<unsigned>(n > 0 ? n : 1);
+    std::atomic<size_t> next{0};
+    auto work = [&]() {
+        std::string buf;
+        for (size_t i = next.fetch_add(1); i < n; i = next.fetch_add(1)) {
+            try {
+                FILE* f = fopen(paths[i].c_str(), "rb");
+                if (!f) throw std::runtime_error("parse_vasp: cannot open " + paths[i]);
+                buf.clear();
+                char chunk[1 << 16];
+                size_t got;
+                while ((got = fread(chunk, 1, sizeof(chunk), f)) > 0) buf.append(chunk, got);
+                fclose(f);
+                parse_text(buf.data(), buf.size(), parsed[i], paths[i]);
+            } catch (const std::exception& ex) {
+                errors[i] = ex.what();
+            }
+        }
+    };
+    std::vector<std::thread> pool;
+    for (unsigned t = 1; t < n_threads; ++t) pool.emplace_back(work);
+    work();
+    for (auto& t : pool) t.join();
+    for (size_t i = 0; i < n; ++i)
+        if (!errors[i].empty()) throw std::runtime_error(errors[i]);
+    graph::SoABatch batch;
+    size_t total = 0;
+    for (const Parsed& p : parsed) total += p.x.size();
+    batch.x.reserve(total);
+    batch.y.reserve(total);
+    batch.z.reserve(total);
+    batch.element.reserve(total);
+    batch.lattice.reserve(9 * n);
+    batch.atom_offsets.reserve(n + 1);
+    for (const Parsed& p : parsed) append(p, batch);
+    return batch;
+}
+
+}  // namespace defect_gnn::io

@@ -4,6 +4,7 @@
 // (VASPStructure -> crystal::Structure -> NeighborList -> CrystalGraph, ETL_PIPELINE_PLAN.md MAIN-PIPELINE).
 #include "crystal/structure.hpp"
 #include "graph/batch.hpp"
+#include "io/vasp_batch.hpp"
 #include "graph/crystal_graph.hpp"
 #include "graph/edge_features.hpp"
 #include "graph/neighbor_list.hpp"
@@ -216,6 +217,34 @@ int facade_collate_batch(int64_t n_structs, const int64_t* atom_offsets, const d
         g_err = e.what();
         return 1;
     }
+}
+
+// Bulk ingest: newline-separated file paths -> SoA arrays (io::load_vasp_batch).
+int facade_load_batch(const char* paths_nl, unsigned n_threads, int64_t atom_cap, int64_t struct_cap,
+                      int64_t* atom_offsets, double* x, double* y, double* z, double* lattices, int* element,
+                      int64_t* n_structs) {
+    return guarded([&] {
+        std::vector<std::string> paths;
+        std::string cur;
+        for (const char* q = paths_nl; *q; ++q) {
+            if (*q == '\n') {
+                if (!cur.empty()) paths.push_back(cur);
+                cur.clear();
+            } else {
+                cur.push_back(*q);
+            }
+        }
+        if (!cur.empty()) paths.push_back(cur);
+        graph::SoABatch b = io::load_vasp_batch(paths, n_threads);
+        if (b.n_structs() > struct_cap || b.n_atoms() > atom_cap) throw std::runtime_error("caps too small");
+        *n_structs = b.n_structs();
+        std::memcpy(atom_offsets, b.atom_offsets.data(), sizeof(int64_t) * b.atom_offsets.size());
+        std::memcpy(x, b.x.data(), sizeof(double) * b.x.size());
+        std::memcpy(y, b.y.data(), sizeof(double) * b.y.size());
+        std::memcpy(z, b.z.data(), sizeof(double) * b.z.size());
+        std::memcpy(lattices, b.lattice.data(), sizeof(double) * b.lattice.size());
+        std::memcpy(element, b.element.data(), sizeof(int) * b.element.size());
+    });
 }
 
 }  // extern "C"

@@ -111,6 +111,66 @@ def test_poscar_parser_roundtrip(tmp_path, facade, c1_structures):
         assert r.returncode == 1 and "no CPU fallback" in r.stderr
 
 
+def test_bulk_poscar_ingest_matches_per_file_parser(tmp_path, facade, c1_structures):
+    """io::load_vasp_batch (SURVEY 8f f3: multi-threaded POSCAR -> SoA) gives the positions crystal::Structure computes
+    from io::parse_vasp's output, file by file: Direct input bit-exact, scaled / Cartesian input to rounding."""
+    i32p, i64p, dp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+    facade.facade_load_batch.argtypes = [C.c_char_p, C.c_uint, C.c_int64, C.c_int64, i64p, dp, dp, dp, dp, i32p, i64p]
+    items = list(c1_structures.items())
+    paths, expect = [], []
+    for k, (nm, (x, y, z, L, species, frac)) in enumerate(items):
+        counts = np.bincount(species)
+        scale = 1.0 if k % 3 else 1.5
+        cart = k % 4 == 3
+        path = tmp_path / f"{nm}.vasp"
+        with open(path, "w") as f:
+            f.write(f"fixture {nm}\n{scale!r}\n")
+            for r in L / scale:
+                f.write("  ".join(repr(float(v)) for v in r) + "\n")
+            f.write(" ".join(f"E{i}" for i in range(len(counts))) + "\n" + "  ".join(str(int(c)) for c in counts) + "\n")
+            if k % 2:
+                f.write("Selective dynamics\n")
+            f.write("Cartesian\n" if cart else "Direct\n")
+            pts = (np.stack([x, y, z], axis=1) / scale) if cart else frac
+            for p_ in pts:
+                f.write(" ".join(repr(float(v)) for v in p_) + (" T T T" if k % 2 else "") + "\n")
+        paths.append(str(path))
+        expect.append((scale, cart))
+    n_atoms = sum(len(it[1][0]) for it in items)
+    for threads in (1, 4):
+        offs = np.zeros(len(items) + 1, np.int64)
+        X, Y, Z = np.zeros(n_atoms), np.zeros(n_atoms), np.zeros(n_atoms)
+        Ls = np.zeros((len(items), 9))
+        el = np.zeros(n_atoms, np.int32)
+        ns = C.c_int64()
+        rc_ = facade.facade_load_batch("\n".join(paths).encode(), threads, n_atoms, len(items), _p(offs, C.c_int64),
+                                       _p(X, C.c_double), _p(Y, C.c_double), _p(Z, C.c_double), _p(Ls, C.c_double),
+                                       _p(el, C.c_int32), C.byref(ns))
+        assert rc_ == 0, facade.facade_last_error()
+        assert ns.value == len(items) and offs[-1] == n_atoms
+        for k, (nm, (x, y, z, L, species, frac)) in enumerate(items):
+            a0, a1 = int(offs[k]), int(offs[k + 1])
+            assert a1 - a0 == len(x)
+            scale, cart = expect[k]
+            assert np.array_equal(el[a0:a1], species)
+            got = np.stack([X[a0:a1], Y[a0:a1], Z[a0:a1]], axis=1)
+            if scale == 1.0 and not cart:
+                assert np.array_equal(Ls[k].reshape(3, 3), L)
+                assert np.array_equal(got, positions(facade, np.ascontiguousarray(frac), np.ascontiguousarray(L)))
+            else:
+                assert np.allclose(Ls[k].reshape(3, 3), L, rtol=1e-15, atol=0)
+                assert np.allclose(got, np.stack([x, y, z], axis=1), rtol=0, atol=1e-11)
+    # a missing file and a truncated file fail with the parser's error text
+    ns = C.c_int64()
+    bad = tmp_path / "bad.vasp"
+    bad.write_text("x\n1.0\n1 0 0\n")
+    for pth in (str(tmp_path / "nope.vasp"), str(bad)):
+        rc_ = facade.facade_load_batch(pth.encode(), 2, n_atoms, 1, _p(offs, C.c_int64), _p(X, C.c_double),
+                                       _p(Y, C.c_double), _p(Z, C.c_double), _p(Ls, C.c_double), _p(el, C.c_int32),
+                                       C.byref(ns))
+        assert rc_ != 0 and b"parse_vasp" in facade.facade_last_error()
+
+
 # ---- GPU: reference-shaped API against the oracle -------------------------------------------------------------------
 @pytest.mark.gpu
 def test_neighbor_list_facade_vs_oracle(facade, oracle, c1_structures):
