@@ -22,16 +22,28 @@ ti = sum(a[0] for a in agg.values()); ts = sum(a[1] for a in agg.values())
 print(f"{filt}: {ti} warp-instr, {ts} samples")
 for k, a in sorted(agg.items(), key=lambda kv: -kv[1][1])[:topn]:
     print(f"{k[0]:16s}:{k[1]:4d} instr {100*a[0]/ti:5.1f}% samp {100*a[1]/ts:5.1f}%  {a[2]}")
-# phase summary for the fill kernel (line ranges of row_sort.cuh / rbf_math.cuh / dgnn_direct.cu)
-PH = [("row_sort.cuh", 73, 112, "rbf epilogue"), ("row_sort.cuh", 113, 150, "bitonic: sqrt+key"),
-      ("row_sort.cuh", 151, 195, "bitonic: network"), ("row_sort.cuh", 196, 205, "bitonic: clash check"),
-      ("row_sort.cuh", 206, 222, "bitonic: emit"), ("row_sort.cuh", 223, 250, "sort dispatch/init"),
-      ("row_sort.cuh", 251, 999, "counting sort (fallback)"),
-      ("rbf_math.cuh", 0, 999, "rbf epilogue"), ("dgnn_direct.cu", 0, 9999, "traversal"), ("geom.h", 0, 9999, "traversal")]
+# per-function summary: every source line is attributed to the nearest preceding function definition in its file
+import os, re, bisect
+CS = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "defect-gnn-cpp_b200", "csrc")
+DEF = re.compile(r"^(?:template.*>\s*)?(?:static\s+)?(?:__global__|__device__|__host__|DG_HD|inline).*?\b([A-Za-z_][A-Za-z0-9_]*)\s*\(")
+fmap = {}
+for fn_ in os.listdir(CS):
+    if not fn_.endswith((".cu", ".cuh", ".h")):
+        continue
+    starts, names = [], []
+    for ln, text in enumerate(open(os.path.join(CS, fn_), errors="ignore"), 1):
+        m = DEF.match(text)
+        if m and not text.rstrip().endswith(";"):
+            starts.append(ln); names.append(m.group(1))
+    fmap[fn_] = (starts, names)
 ph = collections.OrderedDict()
 for (f, l), a in agg.items():
-    name = next((p[3] for p in PH if p[0] == f and p[1] <= l <= p[2]), "other:" + f)
+    name = "other:" + f
+    if f in fmap and fmap[f][0]:
+        k = bisect.bisect_right(fmap[f][0], l) - 1
+        if k >= 0:
+            name = f"{f}:{fmap[f][1][k]}"
     v = ph.setdefault(name, [0, 0]); v[0] += a[0]; v[1] += a[1]
-print("-- phases")
-for n, v in sorted(ph.items(), key=lambda kv: -kv[1][1]):
-    print(f"{n:28s} instr {100*v[0]/ti:5.1f}%  samples {100*v[1]/ts:5.1f}%")
+print("-- by function (source line -> nearest preceding definition)")
+for n, v in sorted(ph.items(), key=lambda kv: -kv[1][1])[:24]:
+    print(f"{n:48s} instr {100*v[0]/ti:5.1f}%  samples {100*v[1]/ts:5.1f}%")
