@@ -429,9 +429,14 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
             fd[p] = (float)d;
         }
     } else {
+        // truncated rows: a position beyond `keep` whose key differs from the key AT position keep belongs to a run that
+        // starts after it -- its rank can neither be emitted (rank < keep) nor enter the tie statistic (rank <= keep),
+        // so only the runs that reach into [0, keep] are resolved (capped rows of ideal lattices: 20 of ~300 entries)
+        const uint32_t tk_edge = keep < m ? (sk[DG_SKI(keep)] & ~IDMASK) : 0u;
         for (int p = lane; p < m; p += 32) {
             const uint32_t w = sk[DG_SKI(p)];
             const uint32_t tk = w & ~IDMASK;
+            if (p > keep && tk != tk_edge) continue;
             const int e = (int)(w & IDMASK);
             const double de = rd[e];
             int s = p, t = p + 1;
