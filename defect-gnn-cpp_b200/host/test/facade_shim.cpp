@@ -8,6 +8,7 @@
 #include "graph/crystal_graph.hpp"
 #include "graph/edge_features.hpp"
 #include "graph/neighbor_list.hpp"
+#include "graph/sharded.hpp"
 
 #include <cstring>
 #include <exception>
@@ -244,6 +245,51 @@ int facade_load_batch(const char* paths_nl, unsigned n_threads, int64_t atom_cap
         std::memcpy(z, b.z.data(), sizeof(double) * b.z.size());
         std::memcpy(lattices, b.lattice.data(), sizeof(double) * b.lattice.size());
         std::memcpy(element, b.element.data(), sizeof(int) * b.element.size());
+    });
+}
+
+// host logic of the sharded builder (no GPU): contiguous structure ranges balanced by predicted edges
+int facade_partition(int64_t n_structs, const int64_t* atom_offsets, const double* lattices, double r_cutoff,
+                     int n_shards, int64_t* bounds, double* weights) {
+    return guarded([&] {
+        graph::SoABatch b;
+        b.atom_offsets.assign(atom_offsets, atom_offsets + n_structs + 1);
+        b.lattice.assign(lattices, lattices + 9 * n_structs);
+        const std::vector<double> w = graph::predicted_edges(b, r_cutoff);
+        const std::vector<int64_t> bd = graph::partition_structures(w, n_shards);
+        std::memcpy(weights, w.data(), sizeof(double) * w.size());
+        std::memcpy(bounds, bd.data(), sizeof(int64_t) * bd.size());
+    });
+}
+
+// sharded build over `n_shards` contexts (device ids given; the same device may repeat), host copies concatenated
+int facade_build_sharded(int64_t n_structs, const int64_t* atom_offsets, const double* frac, const double* lattices,
+                         double r_cutoff, uint64_t max_neighbors, double dr, int n_shards, const int* devices,
+                         int64_t edge_cap, int64_t* bounds, int64_t* global_edge_offsets, int32_t* dst, double* dist,
+                         int64_t* n_edges) {
+    return guarded([&] {
+        graph::SoABatch soa;
+        for (int64_t s = 0; s < n_structs; ++s)
+            soa.add(crystal::Structure(make_vasp(atom_offsets[s + 1] - atom_offsets[s], frac + 3 * atom_offsets[s],
+                                                 lattices + 9 * s, nullptr)));
+        graph::BatchParams p;
+        p.r_cutoff = r_cutoff;
+        p.max_neighbors = max_neighbors == std::numeric_limits<uint64_t>::max() ? std::numeric_limits<size_t>::max()
+                                                                                 : static_cast<size_t>(max_neighbors);
+        p.rbf_r_cutoff = r_cutoff;
+        p.dr = dr;
+        graph::ShardedBuilder sb(std::vector<int>(devices, devices + n_shards));
+        graph::ShardedGraphs g = sb.build(soa, p);
+        if (g.n_edges() > edge_cap) throw std::runtime_error("edge_cap too small");
+        *n_edges = g.n_edges();
+        std::memcpy(bounds, g.struct_bounds.data(), sizeof(int64_t) * g.struct_bounds.size());
+        std::memcpy(global_edge_offsets, g.global_edge_offsets.data(), sizeof(int64_t) * g.global_edge_offsets.size());
+        int64_t e0 = 0;
+        for (int r = 0; r < n_shards; ++r) {
+            const graph::BatchedGraphs& sh = g.shards[static_cast<size_t>(r)];
+            sb.builder(r).copy_edges_to_host(sh, nullptr, dst + e0, nullptr, dist + e0, nullptr);
+            e0 += sh.n_edges;
+        }
     });
 }
 

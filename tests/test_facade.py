@@ -312,3 +312,70 @@ def test_batch_builder_collate_and_edge_views(facade, oracle, c1_structures):
     # a species without an embedding: std::out_of_range, like CrystalGraph's map::at (crystal_graph.cpp:20)
     rc_ = run(keys[:-1])[0]
     assert rc_ == 2
+
+
+def test_sharded_partition_matches_python_helper(facade, pkg, syn):
+    """graph::predicted_edges / partition_structures (C++ host logic of the in-process sharded builder) against the
+    Python helpers bench.py's ranks use (defect-gnn-cpp_b200/sharding.py): every structure assigned exactly once,
+    contiguous, balanced by predicted edges."""
+    i64p, dp = C.POINTER(C.c_int64), C.POINTER(C.c_double)
+    facade.facade_partition.argtypes = [C.c_int64, i64p, dp, C.c_double, C.c_int, i64p, dp]
+    sh = pkg.sharding
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    parts = [syn.perovskite_supercell(4, 4, 2, seed=s)[:4] for s in range(5)] + [none, syn.triclinic_cell(3)[:4]] + \
+            [syn.perovskite_supercell(2, 2, 2, seed=9)[:4], syn.perovskite_supercell(4, 4, 4, seed=10)[:4]]
+    b = syn.concat(parts)
+    S = b.n_structs
+    offs = np.ascontiguousarray(b.atom_offsets, np.int64)
+    L = np.ascontiguousarray(b.lattices.reshape(S, 9))
+    w_ref = sh.predicted_edges(offs, b.lattices, 8.0)
+    for n in (1, 2, 3, 8, 16):
+        bounds = np.zeros(n + 1, np.int64)
+        w = np.zeros(S)
+        assert facade.facade_partition(S, _p(offs, C.c_int64), _p(L, C.c_double), 8.0, n, _p(bounds, C.c_int64),
+                                       _p(w, C.c_double)) == 0, facade.facade_last_error()
+        assert np.allclose(w, w_ref, rtol=1e-12)
+        assert bounds[0] == 0 and bounds[-1] == S and np.all(np.diff(bounds) >= 0)
+        ref = sh.partition_structures(w_ref, n)
+        loads = [w_ref[a:c].sum() for a, c in zip(bounds[:-1], bounds[1:])]
+        loads_ref = [w_ref[a:c].sum() for a, c in ref]
+        assert max(loads) <= max(loads_ref) * (1 + 1e-9) + 1e-9   # never worse balanced than the Python partition
+
+
+@pytest.mark.gpu
+def test_sharded_builder_concatenation_equals_single_build(facade, oracle, c1_structures):
+    """graph::ShardedBuilder over two contexts (here: the same device twice; on a multi-GPU box one per device):
+    the shards' edge lists concatenated equal the oracle's, global edge offsets are the scan of per-shard counts."""
+    i32p, i64p, dp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+    facade.facade_build_sharded.argtypes = [C.c_int64, i64p, dp, dp, C.c_double, C.c_uint64, C.c_double, C.c_int, i32p,
+                                            C.c_int64, i64p, i64p, i32p, dp, i64p]
+    import torch
+    items = list(c1_structures.values())[:5]
+    fr = np.ascontiguousarray(np.concatenate([it[5] for it in items]))
+    Ls = np.ascontiguousarray(np.stack([it[3] for it in items]))
+    offs = np.zeros(len(items) + 1, np.int64)
+    offs[1:] = np.cumsum([len(it[5]) for it in items])
+    ndev = torch.cuda.device_count()
+    for n_shards in (1, 2, 3):
+        devices = np.array([r % max(ndev, 1) for r in range(n_shards)], np.int32)
+        ecap = 20 * int(offs[-1])
+        bounds = np.zeros(n_shards + 1, np.int64)
+        geo = np.zeros(len(items) + 1, np.int64)
+        dst = np.zeros(ecap, np.int32)
+        dist = np.zeros(ecap)
+        ne = C.c_int64()
+        rc_ = facade.facade_build_sharded(len(items), _p(offs, C.c_int64), _p(fr, C.c_double), _p(Ls, C.c_double), 10.0,
+                                          C.c_uint64(20), 0.1, n_shards, _p(devices, C.c_int32), ecap,
+                                          _p(bounds, C.c_int64), _p(geo, C.c_int64), _p(dst, C.c_int32),
+                                          _p(dist, C.c_double), C.byref(ne))
+        assert rc_ == 0, facade.facade_last_error()
+        assert bounds[0] == 0 and bounds[-1] == len(items) and ne.value == ecap
+        e0 = 0
+        for s, (x, y, z, L, _, frac) in enumerate(items):
+            o = oracle.neighbor_list(x, y, z, L, 10.0, 20, 1e-10, oracle.ALGO_CELLLIST)
+            assert geo[s] == e0
+            e1 = e0 + o.n_edges
+            assert np.array_equal(dst[e0:e1], o.dst)
+            assert np.array_equal(dist[e0:e1].view(np.int64), o.dist.view(np.int64))
+            e0 = e1
+        assert geo[-1] == e0
