@@ -213,10 +213,14 @@ def main():
     h_rowptr = torch.empty(b.n_atoms + 1, dtype=torch.int64).pin_memory()
 
     def step_e2e():
-        g = gb.build(*h_in, r_cutoff=R_CUTOFF, max_neighbors=UNCAPPED, epsilon=1e-10, rbf_r_cutoff=R_CUTOFF, dr=DR,
-                     device_inputs=False)
-        gb._check(gb.lib.dgnn_copy_to_host(gb.h, g, h_rowptr.data_ptr(), None, None, None, None, h_seo.data_ptr()))
-        return g
+        # the result read of the step (row_ptr + per-structure offsets, what a host-side consumer needs while the graphs
+        # stay in HBM) goes through dgnn_set_offset_sinks: copied back while the fill pass runs, arrived at return
+        gb.set_offset_sinks(h_rowptr, h_seo)
+        try:
+            return gb.build(*h_in, r_cutoff=R_CUTOFF, max_neighbors=UNCAPPED, epsilon=1e-10, rbf_r_cutoff=R_CUTOFF,
+                            dr=DR, device_inputs=False)
+        finally:
+            gb.set_offset_sinks(None, None)
 
     def barrier():
         if multi:

@@ -26,7 +26,7 @@ EXPORTS = [
     "dgnn_copy_to_host", "dgnn_copy_edges_to_host", "dgnn_rbf_expand", "dgnn_rbf_expand_f64",
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
-    "dgnn_last_consumer_info",
+    "dgnn_last_consumer_info", "dgnn_set_offset_sinks",
 ]
 
 
@@ -143,6 +143,8 @@ def load_library():
         L.dgnn_neighborhood_clouds.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs), C.c_int64, C.c_int64, C.c_void_p,
                                                C.c_void_p]
         L.dgnn_neighborhood_clouds.restype = C.c_int
+        L.dgnn_set_offset_sinks.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.dgnn_set_offset_sinks.restype = C.c_int
         L.dgnn_last_consumer_info.argtypes = [C.c_void_p, C.POINTER(DgnnConsumerInfo)]
         L.dgnn_last_consumer_info.restype = C.c_int
         _lib = L
@@ -231,6 +233,12 @@ class GraphBuilder:
         self._check(self.lib.dgnn_build(self.h, C.byref(b), C.byref(g)))
         self.last = g
         return g
+
+    def set_offset_sinks(self, row_ptr=None, struct_edge_offsets=None):
+        """dgnn_set_offset_sinks: host (pinned) int64 buffers that receive row_ptr / struct_edge_offsets of every
+        following build, copied back while the fill pass runs."""
+        self._sinks = (row_ptr, struct_edge_offsets)
+        self._check(self.lib.dgnn_set_offset_sinks(self.h, _ptr(row_ptr), _ptr(struct_edge_offsets)))
 
     def info(self) -> DgnnBuildInfo:
         i = DgnnBuildInfo()

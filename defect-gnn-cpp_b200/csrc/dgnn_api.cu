@@ -62,6 +62,8 @@ struct dgnn_ctx {
     cudaEvent_t copy_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // stream ...
     long long upload_min_atoms = 1 << 18; // smaller batches go up in one piece
     cudaEvent_t copy_meta_ev = nullptr;
+    int64_t* sink_row_ptr = nullptr;      // dgnn_set_offset_sinks
+    int64_t* sink_seo = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
     int fill_hits_bulk = 1;               // k_fill_hits feature stores: bulk-copy engine (1) or st.global.cs (0)
     int pipeline = 0;                     // fill of part k and count of part k+1 in one kernel.  Evaluated and kept OFF:
@@ -352,6 +354,13 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else {
         return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s'", name);
     }
+    return DGNN_OK;
+}
+
+int dgnn_set_offset_sinks(dgnn_ctx* ctx, int64_t* host_row_ptr, int64_t* host_struct_edge_offsets) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    ctx->sink_row_ptr = host_row_ptr;
+    ctx->sink_seo = host_struct_edge_offsets;
     return DGNN_OK;
 }
 
@@ -856,6 +865,17 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         n_fallback_rows = ctx->h_stats->n_fallback_rows;
     }
     if (!onepass && !pipelined) CU(cudaEventRecord(ctx->ev.e[3], st));
+    // offset sinks: row_ptr and the per-structure offsets are final here for the two-pass plans (the stream has just
+    // been synchronised), so they travel back on the copy stream while the fill pass runs
+    const bool sinks = ctx->sink_row_ptr != nullptr || ctx->sink_seo != nullptr;
+    const bool sinks_early = sinks && !onepass && !pipelined;
+    if (sinks_early) {
+        upload.armed = true;  // (the guard also keeps these copies from outliving an early return)
+        if (ctx->sink_row_ptr)
+            CU(cudaMemcpyAsync(ctx->sink_row_ptr, ctx->row_ptr.p, (size_t)(N + 1) * 8, cudaMemcpyDeviceToHost, ctx->copy_stream));
+        if (ctx->sink_seo)
+            CU(cudaMemcpyAsync(ctx->sink_seo, ctx->seo.p, (size_t)(S + 1) * 8, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    }
     const long long E = ctx->h_stats->n_edges;
     const int max_deg = ctx->h_stats->max_deg;
     if (max_deg > DGNN_MAX_DEGREE)
@@ -952,6 +972,13 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     CU(cudaEventRecord(ctx->ev.e[5], st));
     CU(cudaGetLastError());
+    if (sinks && !sinks_early) {
+        if (ctx->sink_row_ptr)
+            CU(cudaMemcpyAsync(ctx->sink_row_ptr, ctx->row_ptr.p, (size_t)(N + 1) * 8, cudaMemcpyDeviceToHost, st));
+        if (ctx->sink_seo)
+            CU(cudaMemcpyAsync(ctx->sink_seo, ctx->seo.p, (size_t)(S + 1) * 8, cudaMemcpyDeviceToHost, st));
+    }
+    if (sinks_early) CU(cudaStreamSynchronize(ctx->copy_stream));
     {
         int r = fetch_stats(ctx);  // final sync: completion + tie statistics
         if (r != DGNN_OK) return r;

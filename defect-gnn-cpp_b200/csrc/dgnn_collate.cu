@@ -26,6 +26,11 @@ int dg_collate_launch_count_reset() {
 #define DG_COLLATE_THREADS 256
 
 // ---- f1: edge_index [2, E] int64 (row 0 = global source node, row 1 = global target node) ---------------------------
+// One warp per row; each lane stores two edges as one 16-byte streaming store (512 B per warp instruction), pairs
+// aligned separately for the two output rows (row 1 starts at element E, whose parity shifts the 16-byte grid).
+__device__ __forceinline__ void dg_stcs_ll2(long long* p, long long v0, long long v1) {
+    asm volatile("st.global.cs.v2.s64 [%0], {%1, %2};" ::"l"(p), "l"(v0), "l"(v1) : "memory");
+}
 __global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_edges(long long N, long long E,
                                                                       const long long* __restrict__ row_ptr,
                                                                       const int* __restrict__ astruct,
@@ -35,12 +40,27 @@ __global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_edges(long long 
     const int lane = threadIdx.x & 31;
     const long long warp0 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+    long long* __restrict__ out_src = edge_index;
+    long long* __restrict__ out_dst = edge_index + E;
+    const long long par = E & 1;  // out_dst + e is 16-byte aligned when (e + E) is even (the allocation is)
     for (long long a = warp0; a < N; a += nwarps) {
         const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        if (e1 <= e0) continue;
         const long long base = atom_offsets[astruct[a]];
-        for (long long e = e0 + lane; e < e1; e += 32) {
-            __stcs(edge_index + e, a);
-            __stcs(edge_index + E + e, base + (long long)dst[e]);
+        // sources: head / aligned pairs / tail
+        {
+            const long long b0 = e0 + (e0 & 1), b1 = e1 & ~1LL;
+            if (lane == 0 && b0 != e0) __stcs(out_src + e0, a);
+            if (lane == 1 && b1 != e1 && b1 >= b0) __stcs(out_src + b1, a);
+            for (long long e = b0 + 2 * lane; e < b1; e += 64) dg_stcs_ll2(out_src + e, a, a);
+        }
+        // targets
+        {
+            const long long b0 = e0 + ((e0 + par) & 1), b1 = e1 - ((e1 + par) & 1);
+            if (lane == 0 && b0 != e0) __stcs(out_dst + e0, base + (long long)dst[e0]);
+            if (lane == 1 && b1 != e1 && b1 >= b0) __stcs(out_dst + b1, base + (long long)dst[b1]);
+            for (long long e = b0 + 2 * lane; e < b1; e += 64)
+                dg_stcs_ll2(out_dst + e, base + (long long)__ldcs(dst + e), base + (long long)__ldcs(dst + e + 1));
         }
     }
 }

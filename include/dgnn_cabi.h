@@ -103,6 +103,13 @@ typedef struct {
 
 int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* batch, dgnn_graphs* out);
 
+/* Host sinks for the offsets of every following dgnn_build on this ctx (NULL, NULL switches them off): row_ptr
+ * [n_atoms+1] and struct_edge_offsets [n_structs+1] -- the counts / offsets a host-side consumer needs while the graphs
+ * stay on the device -- are copied back on the ctx's copy stream as soon as the scan has produced them, i.e. WHILE the
+ * fill pass runs, and have arrived when dgnn_build returns.  The buffers must hold the next build's sizes (pinned
+ * memory for a true overlap). */
+int dgnn_set_offset_sinks(dgnn_ctx* ctx, int64_t* host_row_ptr, int64_t* host_struct_edge_offsets);
+
 /* Copy results of the last build to host buffers (any pointer may be NULL to skip it).  Sizes as in dgnn_graphs. */
 int dgnn_copy_to_host(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t* row_ptr, int32_t* dst, int32_t* image,
                       double* dist, float* rbf, int64_t* struct_edge_offsets);

@@ -356,6 +356,43 @@ def test_chunked_upload_overlaps_count_pass(pkg, oracle, syn, opts):
     gb.close()
 
 
+@pytest.mark.parametrize("onepass", [0, 1])
+def test_offset_sinks_receive_row_ptr_during_the_build(pkg, oracle, syn, onepass):
+    """dgnn_set_offset_sinks: row_ptr / struct_edge_offsets are in the host sinks when dgnn_build returns (copied on the
+    copy stream while the fill runs for the two-pass plans, at the end for the single-pass plan), for host and device
+    inputs, direct and cell-list structures, and stop being written once the sinks are cleared."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("onepass", onepass)
+    gb.set_option("upload_min_atoms", 0)
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    parts = [syn.perovskite_supercell(4, 4, 2, seed=61)[:4], none, syn.triclinic_cell(62)[:4],
+             syn.perovskite_supercell(3, 3, 3, seed=63)[:4], syn.perovskite_supercell(2, 2, 2, seed=64)[:4]]
+    b = syn.concat(parts)
+    S, N = len(parts), b.n_atoms
+    for rc, cap in ((8.0, oracle.UNCAPPED), (10.0, 20)):
+        ref = build_and_fetch(gb, b, rc, cap, rc, 0.2)
+        h_rp = torch.full((N + 1,), -1, dtype=torch.int64).pin_memory()
+        h_so = torch.full((S + 1,), -1, dtype=torch.int64).pin_memory()
+        gb.set_offset_sinks(h_rp, h_so)
+        for dev_in in (False, True):
+            h_rp.fill_(-1), h_so.fill_(-1)
+            arrs = [np.ascontiguousarray(a) for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+            if dev_in:
+                arrs = [torch.from_numpy(a).cuda() for a in arrs]
+            g = gb.build(*arrs, r_cutoff=rc, max_neighbors=cap, rbf_r_cutoff=rc, dr=0.2, device_inputs=dev_in)
+            assert np.array_equal(h_rp.numpy(), ref.row_ptr), (rc, cap, dev_in)   # no sync, no copy_to_host needed
+            assert np.array_equal(h_so.numpy(), ref.struct_edge_offsets)
+            assert int(h_rp[-1]) == int(g.n_edges)
+        gb.set_offset_sinks(None, None)
+        h_rp.fill_(-7)
+        build_and_fetch(gb, b, rc, cap, rc, 0.2)
+        assert int(h_rp[0]) == -7 and int(h_rp[-1]) == -7
+    gb.close()
+
+
 @pytest.mark.parametrize("sym", [0, 1])
 def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
     """The symmetric count pass (one sweep decides i -> j and j -> i, the near-cutoff band recomputes the mirror) must
