@@ -11,6 +11,7 @@
 //
 // All three are HBM-bound streaming kernels: one warp per CSR row, lanes over the row's edges, coalesced stores.
 // Compile with -fmad=false: displacements follow the reference's FMA-free operand order.
+#include <cstdint>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -43,10 +44,21 @@ __global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_edges(long long 
     long long* __restrict__ out_src = edge_index;
     long long* __restrict__ out_dst = edge_index + E;
     const long long par = E & 1;  // out_dst + e is 16-byte aligned when (e + E) is even (the allocation is)
+    // the row header (row_ptr pair, structure base: three dependent loads) of the NEXT row is fetched before this row's
+    // stores are issued, so the latency chain overlaps the store stream
+    long long n0 = 0, n1 = 0, nbase = 0;
+    if (warp0 < N) {
+        n0 = row_ptr[warp0], n1 = row_ptr[warp0 + 1];
+        nbase = atom_offsets[astruct[warp0]];
+    }
     for (long long a = warp0; a < N; a += nwarps) {
-        const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        const long long e0 = n0, e1 = n1, base = nbase;
+        const long long an = a + nwarps;
+        if (an < N) {
+            n0 = row_ptr[an], n1 = row_ptr[an + 1];
+            nbase = atom_offsets[astruct[an]];
+        }
         if (e1 <= e0) continue;
-        const long long base = atom_offsets[astruct[a]];
         // sources: head / aligned pairs / tail
         {
             const long long b0 = e0 + (e0 & 1), b1 = e1 & ~1LL;
@@ -87,6 +99,31 @@ __global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_nodes(long long 
             continue;
         }
         x[i] = table[(long long)row * F + c];
+        if (c == 0 && batch) batch[a] = (long long)astruct[a];
+    }
+}
+// F % 4 == 0 and N * F / 4 < 2^31: one float4 per thread, 32-bit index arithmetic (the scalar kernel pays a 64-bit
+// division per element)
+__global__ void __launch_bounds__(DG_COLLATE_THREADS) k_collate_nodes_v4(unsigned N, unsigned F4,
+                                                                         const int* __restrict__ node_keys,
+                                                                         const int* __restrict__ lut, int lut_size,
+                                                                         const float4* __restrict__ table,
+                                                                         const int* __restrict__ astruct,
+                                                                         float4* __restrict__ x,
+                                                                         long long* __restrict__ batch,
+                                                                         int* __restrict__ err) {
+    const unsigned total = N * F4;
+    const unsigned stride = gridDim.x * blockDim.x;
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+        const unsigned a = i / F4;
+        const unsigned c = i - a * F4;
+        const int key = __ldg(node_keys + a);
+        const int row = (key >= 0 && key < lut_size) ? __ldg(lut + key) : -1;
+        if (row < 0) {
+            if (c == 0) atomicCAS(err, -1, (int)(a < 0x7fffffffu ? a : 0x7fffffffu));
+            continue;
+        }
+        __stcs(x + i, __ldg(table + (size_t)row * F4 + c));
         if (c == 0 && batch) batch[a] = (long long)astruct[a];
     }
 }
@@ -207,7 +244,12 @@ void dg_launch_collate_nodes(cudaStream_t st, long long N, int F, const int* nod
                              const float* table, const int* astruct, float* x, long long* batch, int* err,
                              int sm_count) {
     if (N <= 0) return;
-    if (F > 0 && x) {
+    if (F > 0 && x && F % 4 == 0 && N * (long long)(F / 4) < 0x7fffffffLL && ((uintptr_t)table & 15) == 0 &&
+        ((uintptr_t)x & 15) == 0) {
+        k_collate_nodes_v4<<<grid_for(N * (long long)(F / 4), sm_count, DG_COLLATE_THREADS), DG_COLLATE_THREADS, 0, st>>>(
+            (unsigned)N, (unsigned)(F / 4), node_keys, lut, lut_size, (const float4*)table, astruct, (float4*)x, batch,
+            err);
+    } else if (F > 0 && x) {
         k_collate_nodes<<<grid_for(N * (long long)F, sm_count, DG_COLLATE_THREADS), DG_COLLATE_THREADS, 0, st>>>(
             N, F, node_keys, lut, lut_size, table, astruct, x, batch, err);
     } else if (batch) {

@@ -54,7 +54,39 @@ __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_vec4(const double* __re
     }
 }
 
-// general K (not a multiple of 4): scalar stores, still flat-indexed and coalesced
+// K not a multiple of 4: rows are not 16-byte aligned, but a tile of RBF_TILE_EDGES (a multiple of 4) edges is -- the
+// tile's K * RBF_TILE_EDGES floats are written as float4s that may straddle two edges (one 32-bit division per float4)
+__global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_flat4(const double* __restrict__ dist, long long n_edges,
+                                                               unsigned K, float* __restrict__ out, DgRbfEpi P) {
+    __shared__ float s_d[RBF_TILE_EDGES];
+    const long long n_tiles = (n_edges + RBF_TILE_EDGES - 1) / RBF_TILE_EDGES;
+    for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const long long e0 = tile * RBF_TILE_EDGES;
+        const unsigned ne = (unsigned)((n_edges - e0) < RBF_TILE_EDGES ? (n_edges - e0) : RBF_TILE_EDGES);
+        __syncthreads();
+        for (unsigned i = threadIdx.x; i < ne; i += RBF_THREADS) s_d[i] = (float)__ldcs(dist + e0 + i);
+        __syncthreads();
+        const unsigned nf = ne * K;  // floats of this tile
+        float* __restrict__ o = out + e0 * K;
+#pragma unroll 2
+        for (unsigned f = threadIdx.x * 4u; f < nf; f += RBF_THREADS * 4u) {
+            unsigned e = f / K, k = f - e * K;
+            float g[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                g[i] = e < ne ? dg_rbf1(s_d[e], (int)k, P) : 0.0f;
+                if (++k == K) k = 0, ++e;
+            }
+            if (f + 4u <= nf) {
+                __stcs(reinterpret_cast<float4*>(o + f), make_float4(g[0], g[1], g[2], g[3]));
+            } else {  // last, partial float4 of the last tile
+                for (unsigned i = 0; f + i < nf; ++i) o[f + i] = g[i];
+            }
+        }
+    }
+}
+
+// fallback (unaligned output pointer, K beyond the 32-bit tile index): scalar stores, flat-indexed and coalesced
 __global__ void __launch_bounds__(RBF_THREADS) k_rbf_f32_scalar(const double* __restrict__ dist, long long n_edges,
                                                                 int K, float* __restrict__ out, DgRbfEpi P) {
     const long long total = n_edges * K;
@@ -95,6 +127,11 @@ void dg_launch_rbf_f32(cudaStream_t st, const double* dist, long long n_edges, i
         long long grid = (long long)sm_count * RBF_CTAS_PER_SM;  // resident CTAs per SM
         if (grid > n_tiles) grid = n_tiles;
         k_rbf_f32_vec4<<<(unsigned)grid, RBF_THREADS, 0, st>>>(dist, n_edges, reinterpret_cast<float4*>(out), P);
+    } else if (((uintptr_t)out & 15) == 0 && (long long)RBF_TILE_EDGES * K < (1LL << 31) && (RBF_TILE_EDGES & 3) == 0) {
+        const long long n_tiles = (n_edges + RBF_TILE_EDGES - 1) / RBF_TILE_EDGES;
+        long long grid = (long long)sm_count * RBF_CTAS_PER_SM;
+        if (grid > n_tiles) grid = n_tiles;
+        k_rbf_f32_flat4<<<(unsigned)grid, RBF_THREADS, 0, st>>>(dist, n_edges, (unsigned)K, out, P);
     } else {
         const long long total = n_edges * K;
         long long grid = (total + RBF_THREADS - 1) / RBF_THREADS;

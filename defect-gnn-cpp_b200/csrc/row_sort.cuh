@@ -429,40 +429,95 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
             fd[p] = (float)d;
         }
     } else {
-        // truncated rows: a position beyond `keep` whose key differs from the key AT position keep belongs to a run that
-        // starts after it -- its rank can neither be emitted (rank < keep) nor enter the tie statistic (rank <= keep),
-        // so only the runs that reach into [0, keep] are resolved (capped rows of ideal lattices: 20 of ~300 entries)
-        const uint32_t tk_edge = keep < m ? (sk[DG_SKI(keep)] & ~IDMASK) : 0u;
-        for (int p = lane; p < m; p += 32) {
-            const uint32_t w = sk[DG_SKI(p)];
-            const uint32_t tk = w & ~IDMASK;
-            if (p > keep && tk != tk_edge) continue;
-            const int e = (int)(w & IDMASK);
-            const double de = rd[e];
-            int s = p, t = p + 1;
-            while (s > 0 && (sk[DG_SKI(s - 1)] & ~IDMASK) == tk) --s;
-            while (t < m && (sk[DG_SKI(t)] & ~IDMASK) == tk) ++t;
-            int rank = p;
-            if (t - s > 1) {  // run of equal truncated keys: exact canonical rank inside it
-                const unsigned long long ke = dg_payload_tie_key(P, e);
-                rank = s;
-                for (int q = s; q < t; ++q) {
-                    if (q == p) continue;
-                    const int f = (int)(sk[DG_SKI(q)] & IDMASK);
-                    const double df = rd[f];
-                    if (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ++rank;
+        // Runs of equal truncated keys (coordination shells of an ideal lattice: every shell is one run) get their
+        // exact canonical order (distance, dst, image).  Truncated rows: a position beyond `keep` whose key differs
+        // from the key AT position keep belongs to a run that starts after it -- its rank can neither be emitted
+        // (rank < keep) nor enter the tie statistic (rank <= keep), so only positions up to the end of the run that
+        // holds position keep are resolved (capped rows of ideal lattices: 20 of ~300 entries).
+        int lim = m;
+        if (keep < m) {
+            const uint32_t tk_edge = sk[DG_SKI(keep)] & ~IDMASK;
+            lim = m;
+            for (int c0 = keep + 1; c0 < m; c0 += 32) {
+                const int q = c0 + lane;
+                const unsigned diff = __ballot_sync(FULL_MASK, q < m && (sk[DG_SKI(q)] & ~IDMASK) != tk_edge);
+                if (diff) {
+                    lim = c0 + __ffs(diff) - 1;
+                    break;
                 }
             }
-            if (rank < keep) {
-                int j;
-                uint32_t img;
-                P.get(e, j, img);
-                dst[o + rank] = j;
-                image[o + rank] = img;
-                dist[o + rank] = de;
-                fd[rank] = (float)de;
+        }
+        // 32 positions at a time: the entries that sit in a run are broadcast one by one from registers and every lane
+        // of the same run counts the ones ordered before it (no divergent per-entry loops, no shared-memory chase);
+        // only runs that cross the 32-position window finish with a scalar walk over the part outside it
+        // The window is cut back to the start of its last run when that run continues past it (and does not fill the
+        // whole window), so runs of up to 32 entries are always ranked inside one window.
+        for (int c0 = 0, adv = 32; c0 < lim; c0 += adv) {
+            const int p = c0 + lane;
+            adv = 32;
+            uint32_t w = p < lim ? sk[DG_SKI(p)] : 0u;
+            uint32_t tk = w & ~IDMASK;
+            if (c0 + 32 < lim) {
+                const uint32_t tk_next = sk[DG_SKI(c0 + 32)] & ~IDMASK;
+                const unsigned same = __ballot_sync(FULL_MASK, tk == tk_next);  // a suffix of the lanes (sorted keys)
+                if (same != 0u && same != FULL_MASK) adv = __ffs(same) - 1;
             }
-            if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+            const bool valid = p < lim && lane < adv;
+            if (!valid) w = 0u, tk = 0u;
+            const int e = (int)(w & IDMASK);
+            const double de = valid ? rd[e] : 0.0;
+            const bool nb_l = valid && p > 0 && (sk[DG_SKI(p - 1)] & ~IDMASK) == tk;
+            const bool nb_r = valid && p + 1 < m && (sk[DG_SKI(p + 1)] & ~IDMASK) == tk;
+            const unsigned inrun = __ballot_sync(FULL_MASK, nb_l || nb_r);
+            int rank = p;
+            if (inrun) {
+                const unsigned long long ke = (nb_l || nb_r) ? dg_payload_tie_key(P, e) : 0ull;
+                int cnt = 0, first = lane;
+                for (unsigned mask = inrun; mask; mask &= mask - 1) {
+                    const int r = __ffs(mask) - 1;
+                    const uint32_t tk_r = __shfl_sync(FULL_MASK, tk, r);
+                    const double de_r = __shfl_sync(FULL_MASK, de, r);
+                    const unsigned long long ke_r = __shfl_sync(FULL_MASK, ke, r);
+                    if (tk_r == tk) {
+                        first = min(first, r);
+                        cnt += (de_r < de || (de_r == de && ke_r < ke)) ? 1 : 0;
+                    }
+                }
+                if (nb_l || nb_r) {
+                    int s0 = c0 + first;
+                    if (first == 0) {  // the run may begin in an earlier window
+                        for (int q = c0 - 1; q >= 0; --q) {
+                            const uint32_t wq = sk[DG_SKI(q)];
+                            if ((wq & ~IDMASK) != tk) break;
+                            const int f = (int)(wq & IDMASK);
+                            const double df = rd[f];
+                            cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                            s0 = q;
+                        }
+                    }
+                    // ... and may run on past this window (positions beyond lim share no key with positions before it)
+                    for (int q = c0 + adv; q < lim; ++q) {
+                        const uint32_t wq = sk[DG_SKI(q)];
+                        if ((wq & ~IDMASK) != tk) break;
+                        const int f = (int)(wq & IDMASK);
+                        const double df = rd[f];
+                        cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                    }
+                    rank = s0 + cnt;
+                }
+            }
+            if (valid) {
+                if (rank < keep) {
+                    int j;
+                    uint32_t img;
+                    P.get(e, j, img);
+                    dst[o + rank] = j;
+                    image[o + rank] = img;
+                    dist[o + rank] = de;
+                    fd[rank] = (float)de;
+                }
+                if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+            }
         }
         if (m > keep && keep > 0) {  // truncated through a distance tie?  (statistic of rule R8)
             __syncwarp();

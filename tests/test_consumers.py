@@ -102,6 +102,32 @@ def test_gpu_collate_matches_restatement(gpu_builder, gpu_builder_cell, oracle, 
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("F", [1, 7, 8, 92])
+def test_gpu_collate_feature_widths(gpu_builder, oracle, syn, F):
+    """x gather: widths that are not a multiple of four take the scalar kernel, the others the float4 one; odd edge
+    totals shift the 16-byte grid of edge_index row 1 (paired stores peel head and tail per row)."""
+    gb = gpu_builder
+    b = _mixed_batch(syn)
+    rng = np.random.default_rng(F)
+    keys = rng.integers(0, 5, size=b.n_atoms).astype(np.int32)
+    emb = _emb(F=F, keys=range(0, 5))
+    ek = np.array(sorted(emb), dtype=np.int32)
+    et = np.stack([emb[int(k)] for k in ek])
+    per = [keys[b.atom_offsets[s]:b.atom_offsets[s + 1]] for s in range(b.n_structs)]
+    parities = set()
+    for rc, cap in ((8.0, oracle.UNCAPPED), (5.0, 11), (6.1, 13), (7.3, oracle.UNCAPPED)):
+        gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=rc, max_neighbors=cap, rbf_r_cutoff=rc, dr=0.2)
+        og = _oracle_graphs(oracle, b, rc, cap)
+        c = gb.collate(keys, ek, et)
+        X, ei, batch = gb.collated_to_host(c)
+        Xo, eio, bo = oracle.collate(og, per, emb)
+        assert c.F == F and np.array_equal(X, Xo) and np.array_equal(ei, eio) and np.array_equal(batch, bo)
+        parities.add(c.n_edges & 1)
+    if F == 92:
+        assert parities == {0, 1}, "the cases are meant to cover even and odd edge totals"
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("which", ["direct", "cell"])
 def test_gpu_edge_views_and_clouds_match_restatement(gpu_builder, gpu_builder_cell, oracle, syn, which):
     gb = gpu_builder if which == "direct" else gpu_builder_cell

@@ -223,7 +223,8 @@ def test_device_resident_inputs_and_rbf_standalone(gpu_builder, oracle, syn):
         assert np.array_equal(getattr(h_dev, f), getattr(h_host, f)), f
     # stand-alone gaussian_rbf replacement, host and device pointers, fp32 row-major and fp64 column-major
     d = np.concatenate([[0.0, 4.0, 8.0 - 1e-9], np.random.default_rng(0).uniform(0.0, 8.0, 5000)])
-    for rc, dr in ((8.0, 0.2), (10.0, 0.1), (8.0, 0.3)):   # K = 40, 100, 26 (scalar-store path)
+    # K = 40, 100 (float4 rows); 26, 50, 11, 7, 1 (rows not 16-byte aligned: float4s straddle edges, partial tail)
+    for rc, dr in ((8.0, 0.2), (10.0, 0.1), (8.0, 0.3), (10.0, 0.2), (8.0, 0.7), (7.0, 1.0), (8.0, 5.0)):
         ref = oracle.edge_attr(d, rc, dr)
         out = gb.rbf_expand(d, rc, dr)
         assert out.shape == ref.shape
