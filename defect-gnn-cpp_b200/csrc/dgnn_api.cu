@@ -71,6 +71,13 @@ struct dgnn_ctx {
                                           // hide (C2, same box: 11.12 ms against 10.37 ms with the passes back to back)
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
+    // speculative capped build: 0 off, -1 auto (large capped batches whose density estimate allows it), 1 wherever legal.
+    // Off by default: measured SLOWER than count-with-hit-lists + hit-list fill (2 k C2 structures, r_c = 10, cap 20:
+    // 3.23 vs 2.97 ms) -- the sweep into the shared-memory row buffer runs at 2 CTAs per SM, the hit-list count at full
+    // occupancy.  What it saves is memory: no hit lists (12 B x hit_cap per atom).
+    int spec_opt = 0;
+    bool spec_skip = false;               // (set while a failed speculation is being rebuilt)
+    int spec_failed = 0;                  // the rebuild reports it in dgnn_build_info
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
     // the last successful build, for the CSR consumers (collation, viewer arrays, neighbourhood clouds)
@@ -333,6 +340,9 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->upload_chunks = (int)value;
     } else if (!strcmp(name, "fill_hits_bulk")) {
         ctx->fill_hits_bulk = value != 0.0;
+    } else if (!strcmp(name, "speculative")) {
+        if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "speculative must be -1, 0 or 1");
+        ctx->spec_opt = (int)value;
     } else if (!strcmp(name, "pipeline")) {
         ctx->pipeline = value != 0.0;
     } else if (!strcmp(name, "sym_count")) {
@@ -507,7 +517,18 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         if (r != DGNN_OK) return r;
         have_est = true;
     }
-    if (ctx->hit_cap_opt < 0 && N > 0) {
+    // Speculative capped build: when even the sparsest structure's density promises several times max_neighbors
+    // candidates per atom (surface atoms of a slab still see half of it), every row will be truncated to the cap and row a starts at a * cap -- no count pass, no hit lists.
+    const long long onepass_small_rows = (long long)ctx->sm_count * 2 * 8 * 2;
+    const int est_min_deg = have_est && ctx->h_stats->est_sparse > 0 ? 1000000 - ctx->h_stats->est_sparse : 0;
+    const bool spec_try = have_est && ctx->spec_opt != 0 && !ctx->spec_skip && N > 0 && ctx->h_stats->err_status == 0 &&
+                          ctx->h_stats->n_cell_structs == 0 && b->max_neighbors >= 1 && b->max_neighbors <= 4096 &&
+                          (long long)b->max_neighbors * N < (1LL << 40) &&
+                          (!want_rbf || (ctx->fuse_rbf && (K & 3) == 0 &&
+                                         (long long)b->max_neighbors * (K / 4) < (1LL << 22))) &&
+                          (ctx->spec_opt > 0 || ((long long)est_min_deg >= 4 * (long long)b->max_neighbors + 32 &&
+                                                 !(ctx->onepass_opt != 0 && N <= onepass_small_rows)));
+    if (ctx->hit_cap_opt < 0 && N > 0 && !spec_try) {
         const long long est = ctx->h_stats->est_deg;
         // Worth it only where the fill pass is bound by the traversal, not by the bytes it writes: the lists cost the
         // count pass ~35 % more time and the fill pass 12 B of extra reads per accepted pair.  Measured on C2: uncapped
@@ -579,8 +600,51 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // more than the count pass saves (C2 10 k structures: 11.8 ms vs 10.9 ms count + fill), but a batch of a few steps
     // per CTA -- the reference's one-structure-per-call API above all -- finishes in one kernel and one sync less
     // (9 shipped POSCARs: 0.31 ms vs 1.37 ms).
+    bool spec = false;
+    if (spec_try) {
+        const long long est = ctx->h_stats->est_deg;
+        long long rc = est + est / 8 + 8;
+        if (rc < max_nb) rc = max_nb;
+        if (rc > DGNN_MAX_DEGREE) rc = DGNN_MAX_DEGREE;
+        if (ctx->onepass_row_cap > 0) rc = ctx->onepass_row_cap;
+        row_cap_1p = round_up((int)(rc > 32 ? rc : 32), 32);
+        DgDirectArgs O = D;
+        O.hit_cap = 0;
+        O.hits = nullptr;
+        O.hits_d2 = nullptr;
+        O.row_cap = row_cap_1p;
+        O.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap_1p <= 256 ? 256 : (row_cap_1p <= 1024 ? 512 : 1024));
+        O.n_warps = 8;
+        while (O.n_warps > 1 && (int)dg_direct_smem_bytes(O, true) > ctx->smem_optin) O.n_warps >>= 1;
+        onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 && (long long)max_nb * (K / 4) < (1LL << 22);
+        if ((int)dg_direct_smem_bytes(O, true) <= ctx->smem_optin && row_cap_1p >= max_nb &&
+            (!want_rbf || onepass_fused_rbf)) {
+            const size_t e_spec = (size_t)N * (size_t)max_nb;
+            ENSURE(ctx->dst, (e_spec + 1) * 4);
+            ENSURE(ctx->image, (e_spec + 1) * 4);
+            ENSURE(ctx->dist, (e_spec + 1) * 8);
+            if (want_rbf) ENSURE(ctx->rbf, e_spec * (size_t)K * 4 + 16);
+            O.dst = (int*)ctx->dst.p;
+            O.image = (uint32_t*)ctx->image.p;
+            O.dist = (double*)ctx->dist.p;
+            O.row_ptr_out = (long long*)ctx->row_ptr.p;
+            if (onepass_fused_rbf) {
+                O.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
+                O.rbf.recur = ctx->rbf_recur;
+            }
+            for (int c = 0; c < n_up; ++c) {
+                if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
+                dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
+                                      (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+            }
+            CU(cudaEventRecord(ctx->ev.e[3], st));
+            CU(dg_launch_direct_spec(st, O, ctx->sm_count));
+            onepass = true;
+            spec = true;
+        }
+    }
     const long long onepass_auto_rows = (long long)ctx->sm_count * 2 * 8 * 2;  // two steps of a full grid
-    if (have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
+    if (!spec && have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
         ctx->h_stats->n_cell_structs == 0 &&
         (ctx->onepass_opt > 0 || (N <= onepass_auto_rows && (hit_cap == 0 || ctx->hit_cap_opt < 0)))) {
         const long long est = ctx->h_stats->est_deg;
@@ -744,6 +808,17 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
     if (ctx->h_stats->lb_timeout) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
+    if (spec && ctx->h_stats->spec_fail) {
+        // a row came up short of max_neighbors (vacuum, a sparse corner of a cell): the offsets were wrong -- rebuild
+        // the batch with counted offsets (inputs are re-read from the caller's buffers)
+        if (upload.armed) CU(cudaStreamSynchronize(ctx->copy_stream));
+        ctx->spec_skip = true;
+        ctx->spec_failed = 1;
+        const int r = dgnn_build(ctx, b, out);
+        ctx->spec_skip = false;
+        ctx->spec_failed = 0;
+        return r;
+    }
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
     int n_fallback_rows = ctx->h_stats->n_fallback_rows;
     const bool onepass_redo_all = (onepass || pipelined) && ctx->h_stats->cap_overflow != 0;
@@ -1020,10 +1095,12 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.direct_warps = D.n_warps;
     I.rbf_fused = fuse_rbf ? 1 : 0;
     I.hit_cap = use_hits ? hit_cap : 0;
-    I.onepass = onepass ? (onepass_redo_all ? 2 : 1) : 0;
+    I.onepass = (onepass && !spec) ? (onepass_redo_all ? 2 : 1) : 0;
+    I.speculative = spec ? 1 : (ctx->spec_failed ? 2 : 0);
+    I.est_min_degree = est_min_deg;
     I.pipeline_parts = pipelined ? n_up : 0;
     I.pipeline_refill = pipelined ? (onepass_redo_all ? 2 : (max_deg > row_cap_1p ? 1 : 0)) : 0;
-    I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
+    I.onepass_fallback_rows = (onepass && !spec) ? n_fallback_rows : 0;
     return DGNN_OK;
 }
 

@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
                                 L[2] * (L[3] * L[7] - L[4] * L[6]));
         const double est = (double)G.natoms * 4.18879020478639 * rcm * rcm * rcm / det;
         atomicMax(&stats->est_deg, est < 1.0e6 ? (int)est + 1 : 1000000);
+        atomicMax(&stats->est_sparse, 1000000 - (est < 999999.0 ? (int)est : 999999));
         if (G.mode != DG_MODE_CELL)
             atomicAdd(&stats->est_edges, (unsigned long long)((double)G.natoms * (est < 1.0e6 ? est + 1.0 : 1.0e6)));
     }
@@ -917,6 +918,90 @@ cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, 
                                : launch_direct_e<false, 3, true>(st, a, sm_count, smem, threads);
     return min_blocks <= 2 ? launch_direct_e<false, 2, false>(st, a, sm_count, smem, threads)
                            : launch_direct_e<false, 3, false>(st, a, sm_count, smem, threads);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Speculative capped build (the reference's default call: max_neighbors = 20 at r_c = 10, every atom of a crystal has
+// hundreds of candidates).  With every row truncated to the cap the CSR offsets are known before any distance is
+// computed: row a starts at a * cap.  One kernel sweeps a row into its shared-memory buffer, sorts, keeps the first
+// `cap` entries and emits them (+ features); a row that comes up short (or outgrows the buffer sized from the density
+// estimate) raises spec_fail and the host redoes the batch with counted offsets.
+// ---------------------------------------------------------------------------------------------------------------------
+template <int EPS>
+__global__ void __launch_bounds__(256, 2) k_direct_spec(const DgDirectArgs A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const RowBuf rb = dg_rowbuf_carve(smem_raw + (size_t)warp * dg_rowbuf_bytes(A.row_cap, A.n_buckets), A.row_cap);
+    unsigned near = 0;
+    int maxdeg = 0;
+    bool fail = false;
+    const int cap = A.max_neighbors;
+    const long long n_chunks = (A.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+        const long long a_end = (chunk + 1) * DG_ROW_CHUNK < A.n_atoms ? (chunk + 1) * DG_ROW_CHUNK : A.n_atoms;
+        for (long long a = chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
+            const DgSmall* __restrict__ G = A.small + A.astruct[a];
+            const int mode = G->mode;
+            if (mode == DG_MODE_CELL || G->status != DG_ST_OK) {  // (the host speculates on direct-path batches only)
+                fail = true;
+                continue;
+            }
+            const int m = traverse_row<true, EPS, false, true>(A, G, a, mode, rb, nullptr, nullptr, lane, lt_mask, near);
+            maxdeg = m > maxdeg ? m : maxdeg;
+            if (lane == 0) {
+                A.deg_raw[a] = m;
+                A.deg_capped[a] = m < cap ? m : cap;
+            }
+            if (m < cap || m > A.row_cap) {
+                fail = true;
+                continue;
+            }
+            dg_row_sort_emit(rb, m, cap, A.n_buckets, A.inv_rc, A.key_scale, a * (long long)cap, A.dst, A.image, A.dist,
+                             A.stats, lane, A.rbf);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) near += __shfl_xor_sync(FULL_MASK, near, o);
+    if (lane == 0) {
+        if (near) atomicAdd(&A.stats->n_near, (unsigned long long)near);
+        if (maxdeg) atomicMax(&A.stats->max_deg, maxdeg);
+        if (fail) atomicExch(&A.stats->spec_fail, 1);
+    }
+}
+
+__global__ void k_spec_offsets(long long N, long long cap, long long* __restrict__ row_ptr) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i <= N; i += stride) row_ptr[i] = i * cap;
+}
+
+template <int EPS>
+static cudaError_t launch_spec_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem) {
+    cudaError_t e = cudaFuncSetAttribute(k_direct_spec<EPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int occ = 1;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct_spec<EPS>, a.n_warps * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (occ < 1) return cudaErrorLaunchOutOfResources;
+    const long long want = (a.n_atoms + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    long long grid = (long long)sm_count * occ;
+    if (grid > want) grid = want;
+    k_direct_spec<EPS><<<(unsigned)grid, a.n_warps * 32, smem, st>>>(a);
+    return cudaGetLastError();
+}
+
+cudaError_t dg_launch_direct_spec(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
+    if (a.n_atoms <= 0) return cudaSuccess;
+    long long g = (a.n_atoms + 1 + 255) / 256;
+    if (g > (long long)sm_count * 8) g = (long long)sm_count * 8;
+    k_spec_offsets<<<(unsigned)g, 256, 0, st>>>(a.n_atoms, (long long)a.max_neighbors, a.row_ptr_out);
+    const size_t smem = dg_direct_smem_bytes(a, true);
+    g_direct_launches += 2;
+    switch (a.eps_mode) {
+        case 0: return launch_spec_t<0>(st, a, sm_count, smem);
+        case 1: return launch_spec_t<1>(st, a, sm_count, smem);
+        default: return launch_spec_t<2>(st, a, sm_count, smem);
+    }
 }
 
 // single-pass build: a.lb_status ([ceil(N / n_warps)] chunk status words) must be zeroed on the stream before the launch

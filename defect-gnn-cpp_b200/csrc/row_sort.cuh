@@ -275,16 +275,24 @@ __device__ __forceinline__ uint32_t dg_dist_key(double d, double key_scale) {
 //
 // Payload policies give the sort access to an entry's (dst, packed image):
 // ---------------------------------------------------------------------------------------------------------------------
+// (load_item / store_item move an entry inside the row buffer: the top-k prefilter compacts the survivors in place)
 struct RowBufPayload {  // traversal kernels: rj / rn arrays filled by the ballot compaction
-    const int* rj;
-    const uint32_t* rn;
+    int* rj;
+    uint32_t* rn;
     __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
         j = rj[e];
         img = rn[e];
     }
+    __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2((uint32_t)rj[e], rn[e]); }
+    __device__ __forceinline__ void store_item(int e, uint2 v) const {
+        rj[e] = (int)v.x;
+        rn[e] = v.y;
+    }
 };
 struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (dg_pack_hit in dgnn_direct.cu)
-    const uint32_t* hw;
+    uint32_t* hw;
+    __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
+    __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
     __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
         const uint32_t v = hw[e];
         j = (int)(v & 0x1ffffu);
@@ -292,7 +300,9 @@ struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (d
     }
 };
 struct CloudPayload {  // hit-list fill pass, cell-list structures: hit word = index into the binned image cloud
-    const uint32_t* hw;
+    uint32_t* hw;
+    __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
+    __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
     const int* cj;
     const uint32_t* cn;
     __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
@@ -528,11 +538,88 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
     return o;
 }
 
+// Top-k prefilter of truncated rows (max_neighbors = 20 of ~330 candidates at the reference's defaults): instead of
+// sorting all m entries, find a d2 threshold that keeps a little more than keep + 1 of them, compact the survivors to
+// the front of the row buffer and sort only those.  The threshold is searched on fp32 copies of d2 held in registers
+// (the count of a cubic-law guess, then a bracketed search); exactness: the first keep + 1 entries of the canonical
+// order all lie below T' (count(f < T') >= keep + 1), the survivors are everything below T = T' (1 + 2^-19), and two
+// entries whose rounded square roots tie differ by < 2^-50 relative in d2 -- far less than the 2^-19 gap minus fp32
+// rounding -- so every entry that ties with one of the first keep + 1 survives too (tie order and the tie statistic see
+// the same candidates as a full sort).  Returns the new entry count (m if the row is left alone).
+template <int EPL, class Payload>
+__device__ __forceinline__ int dg_row_prefilter_t(double* __restrict__ rd, const Payload& P, int m, int keep, float r2,
+                                                  int lane) {
+    float f[EPL];
+#pragma unroll
+    for (int r = 0; r < EPL; ++r) {
+        const int e = r * 32 + lane;
+        f[r] = e < m ? (float)rd[e] : 3.0e38f;
+    }
+    const int need = keep + 1;
+    const int good = need + 48 > 2 * need ? need + 48 : 2 * need;  // stop when need <= count <= good
+    const float x = (float)(need + 8) / (float)m;
+    float T = r2 * cbrtf(x * x) * 1.1f;  // count ~ d^3
+    float lo = 0.0f, hi = 0.0f;          // lo: count < need, hi: count >= need (0: not bracketed yet)
+    int chi = m;
+    for (int it = 0; it < 10; ++it) {
+        int c = 0;
+#pragma unroll
+        for (int r = 0; r < EPL; ++r) c += f[r] < T ? 1 : 0;
+        c = __reduce_add_sync(FULL_MASK, c);
+        if (c < need) {
+            lo = T;
+        } else {
+            hi = T;
+            chi = c;
+            if (c <= good) break;
+        }
+        if (hi == 0.0f) T = lo * 1.3f;
+        else if (lo == 0.0f) T = hi * 0.75f;
+        else T = 0.5f * (lo + hi);
+        if (hi != 0.0f && !(T > lo && T < hi)) break;  // bracket closed (a large shell of equal distances)
+    }
+    if (hi == 0.0f || chi >= m - (m >> 2)) return m;  // nothing found worth a compaction pass
+    const float Tk = hi * (1.0f + 1.9073486328125e-6f);
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int base = 0;
+    for (int c0 = 0; c0 < m; c0 += 32) {
+        const int e = c0 + lane;
+        double d2 = 0.0;
+        uint2 item = make_uint2(0u, 0u);
+        bool pred = false;
+        if (e < m) {
+            d2 = rd[e];
+            pred = (float)d2 < Tk;
+            if (pred) item = P.load_item(e);
+        }
+        const unsigned mask = __ballot_sync(FULL_MASK, pred);
+        __syncwarp();
+        if (pred) {
+            const int pos = base + __popc(mask & lt_mask);  // pos <= e: never ahead of an unread entry
+            rd[pos] = d2;
+            P.store_item(pos, item);
+        }
+        base += __popc(mask);
+        __syncwarp();
+    }
+    return base;
+}
+template <class Payload>
+__device__ __forceinline__ int dg_row_prefilter(double* rd, const Payload& P, int m, int keep, double key_scale,
+                                                int lane) {
+    if (keep >= m || m <= 128 || 3 * (keep + 1) + 48 > m) return m;
+    const float rc = (float)((4294967296.0 - 4096.0) / key_scale);  // key_scale = (2^32 - 4096) / r_c
+    const float r2 = rc * rc;
+    if (m <= 256) return dg_row_prefilter_t<8>(rd, P, m, keep, r2, lane);
+    return dg_row_prefilter_t<16>(rd, P, m, keep, r2, lane);
+}
+
 template <class Payload, class OP>
 __device__ __forceinline__ long long dg_row_sort_bitonic_any_op(double* rd, uint32_t* sk, float* fd, int* tie,
                                                                 const Payload& P, int m, int keep, double key_scale,
                                                                 OP& op, int* dst, uint32_t* image, double* dist,
                                                                 DgStats* stats, int lane) {
+    m = dg_row_prefilter(rd, P, m, keep, key_scale, lane);
     if (m <= 128) return dg_row_sort_bitonic<4>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
     if (m <= 256) return dg_row_sort_bitonic<8>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
     return dg_row_sort_bitonic<16>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);

@@ -200,6 +200,10 @@ typedef struct {
     int32_t pipeline_parts;  /* > 0: pipelined plan, fill of part k + count of part k+1 per kernel, this many parts */
     int32_t pipeline_refill; /* pipelined plan: 1 = a fill pass completed rows beyond the estimated row buffer,
                               * 2 = the estimated arena was too small and the fill pass rewrote every row */
+    int32_t speculative;     /* capped batches: 1 = speculative build (every row assumed to reach max_neighbors, so
+                              * row a starts at a * max_neighbors: one sweep + sort + emit kernel, no count pass) held,
+                              * 2 = a row came up short and the batch was rebuilt with counted offsets, 0 = not tried */
+    int32_t est_min_degree;  /* density estimate of the sparsest structure's degree (what the speculation goes by) */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 

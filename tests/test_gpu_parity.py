@@ -394,6 +394,78 @@ def test_offset_sinks_receive_row_ptr_during_the_build(pkg, oracle, syn, onepass
     gb.close()
 
 
+def test_speculative_capped_build(pkg, oracle, syn):
+    """Capped batches whose sparsest structure still promises far more candidates than max_neighbors are built
+    speculatively (row a at a * cap, one kernel, no count pass); a row that comes up short -- a sparse cell, an empty
+    structure in between is fine -- makes the build fall back to counted offsets.  Both outcomes equal the oracle, ties
+    at the truncation included."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    gb.set_option("speculative", 1)          # also on batches small enough for the single-pass plan
+    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
+    dense = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=71)[:4], none, syn.perovskite_supercell(3, 3, 3, seed=72)[:4],
+                        syn.triclinic_cell(73)[:4], syn.perovskite_supercell(2, 2, 2, seed=74, jitter=0.0)[:4]])
+    for rc, cap, dr in ((10.0, 20, 0.1), (8.0, 12, 0.2), (6.0, 1, 0.25), (8.0, 20, None)):
+        check_batch(gb, oracle, dense, rc, cap, dr=dr)
+        info = gb.info()
+        assert info.speculative == 1 and info.onepass == 0 and info.hit_cap == 0, (rc, cap)
+        assert info.est_min_degree >= 2 * cap
+    # ideal simple cubic lattice: the truncation cuts through a shell of equal distances (tie statistic)
+    sc = syn.simple_cubic(2.0, 4)
+    h = check_batch(gb, oracle, sc, 6.5, 20, dr=0.1, algo=oracle.ALGO_BRUTE, rbf_rc=8.0)
+    assert gb.info().speculative == 1 and h.n_tie_rows > 0
+    # a sparse structure among dense ones: 2 atoms in a 14 A box see 2 * 2 candidates at most within 8 A
+    lone = (np.array([1.0, 3.5]), np.array([1.0, 2.0]), np.array([1.0, 2.5]), np.diag([14.0, 14.0, 14.0]))
+    mixed = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=75)[:4], lone, syn.perovskite_supercell(3, 3, 3, seed=76)[:4]])
+    check_batch(gb, oracle, mixed, 8.0, 12, dr=0.2)
+    info = gb.info()
+    assert info.speculative == 2, "forced speculation must fail on the sparse structure and be rebuilt"
+    # auto policy: the sparse structure's density estimate vetoes the speculation up front
+    gb.set_option("speculative", -1)
+    check_batch(gb, oracle, mixed, 8.0, 12, dr=0.2)
+    assert gb.info().speculative == 0 and gb.info().est_min_degree < 4 * 12 + 32
+    # ... uncapped calls never speculate
+    check_batch(gb, oracle, dense, 8.0, None, dr=0.2)
+    assert gb.info().speculative == 0
+    # a large capped batch takes it by itself, and equals the counted build bit for bit
+    big = syn.c2_batch(40, seed0=31000)
+    gb.set_option("onepass", 0)
+    h1 = build_and_fetch(gb, big, 10.0, 20, 10.0, 0.1)
+    assert gb.info().speculative == 1
+    gb.set_option("speculative", 0)
+    h0 = build_and_fetch(gb, big, 10.0, 20, 10.0, 0.1)
+    assert gb.info().speculative == 0
+    for f in ("row_ptr", "dst", "image", "dist", "rbf", "struct_edge_offsets"):
+        assert np.array_equal(getattr(h1, f), getattr(h0, f)), f
+    assert h1.n_near_cutoff == h0.n_near_cutoff and h1.n_tie_rows == h0.n_tie_rows and h1.max_degree == h0.max_degree
+    gb.close()
+
+
+@pytest.mark.parametrize("opts", [{"onepass": 0}, {"onepass": 1}, {"onepass": 0, "hit_cap": 0}, {"speculative": 1}],
+                         ids=["hit-lists", "single-pass", "traversal-fill", "speculative"])
+def test_truncated_rows_topk_prefilter(pkg, oracle, syn, opts):
+    """Capped rows are not sorted in full: a d2 threshold keeps a little more than max_neighbors + 1 candidates, which
+    are compacted and sorted.  Caps from 1 to most of the row, jittered and ideal lattices (whole shells of equal
+    distances at the threshold and at the truncation), skewed cells -- rows, tie order and the tie statistic must equal
+    the exhaustive oracle in every build plan."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    for k, v in opts.items():
+        gb.set_option(k, v)
+    batches = [syn.concat([syn.perovskite_supercell(4, 4, 2, seed=1)[:4], syn.triclinic_cell(5)[:4]]),
+               syn.concat([syn.perovskite_supercell(3, 3, 2, seed=9, jitter=0.0)[:4], syn.simple_cubic(2.0, 4).structure(0)])]
+    for b in batches:
+        for rc, dr in ((8.0, 0.2), (10.0, 0.25)):
+            for cap in (1, 7, 20, 33, 64, 100):
+                check_batch(gb, oracle, b, rc, cap, dr=dr, algo=oracle.ALGO_BRUTE)
+    check_batch(gb, oracle, syn.adversarial_cells(), 8.0, 20, dr=0.2, algo=oracle.ALGO_BRUTE)
+    gb.close()
+
+
 @pytest.mark.parametrize("sym", [0, 1])
 def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
     """The symmetric count pass (one sweep decides i -> j and j -> i, the near-cutoff band recomputes the mirror) must

@@ -23,10 +23,10 @@ for jitter in (0.02, 0.0):
     for rc, cap in ((8.0, UNCAPPED), (10.0, 20), (10.0, UNCAPPED)):
         ms = []
         for _ in range(4):
-            g = gb.build(*d_in, r_cutoff=rc, max_neighbors=cap, rbf_r_cutoff=rc, dr=0.2, device_inputs=True)
+            g = gb.build(*d_in, r_cutoff=rc, max_neighbors=cap, rbf_r_cutoff=rc, dr=0.25, device_inputs=True)
             i = gb.info()
             ms.append((i.total_ms, i.count_ms, i.fill_ms))
         t = min(ms)
         print(json.dumps({"jitter": jitter, "r_c": rc, "cap": None if cap == UNCAPPED else cap, "edges": int(g.n_edges),
                           "total_ms": round(t[0], 3), "count_ms": round(t[1], 3), "fill_ms": round(t[2], 3),
-                          "tie_rows": int(i.n_tie_rows) if hasattr(i, "n_tie_rows") else None}))
+                          "speculative": int(i.speculative), "est_min_degree": int(i.est_min_degree), "launches": int(i.kernel_launches)}))
