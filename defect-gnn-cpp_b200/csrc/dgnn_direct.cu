@@ -367,7 +367,8 @@ __device__ __forceinline__ long long dg_lookback(const unsigned long long* __res
     return excl;
 }
 
-template <bool FILL, int MINB, int EPS, bool HITS>
+// LEAN (fill pass of batches no row of which is truncated, max_neighbors >= row_cap): the lean row sort (row_sort.cuh)
+template <bool FILL, int MINB, int EPS, bool HITS, bool LEAN = false>
 __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -407,8 +408,8 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
             } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
                 if (lane == 0) atomicExch(&A.stats->overflow, 1);
             } else {
-                dg_row_sort_emit(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image, A.dist, A.stats,
-                                 lane, A.rbf);
+                dg_row_sort_emit<LEAN>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image, A.dist,
+                                       A.stats, lane, A.rbf);
             }
         }
     }
@@ -876,13 +877,13 @@ size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a) {
     return (size_t)a.n_warps * dg_one_warp_bytes(a.row_cap, a.n_buckets);
 }
 
-template <bool FILL, int MINB, int EPS, bool HITS>
+template <bool FILL, int MINB, int EPS, bool HITS, bool LEAN = false>
 static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB, EPS, HITS>,
+    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB, EPS, HITS, LEAN>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int occ = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS, HITS>, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS, HITS, LEAN>, threads, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin (the single-pass
@@ -892,16 +893,16 @@ static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int s
     long long grid = (long long)sm_count * occ;
     if (grid > want) grid = want;
     if (grid < 1) return cudaSuccess;
-    k_direct<FILL, MINB, EPS, HITS><<<(unsigned)grid, threads, smem, st>>>(a);
+    k_direct<FILL, MINB, EPS, HITS, LEAN><<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
-template <bool FILL, int MINB, bool HITS>
+template <bool FILL, int MINB, bool HITS, bool LEAN = false>
 static cudaError_t launch_direct_e(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
     switch (a.eps_mode) {
-        case 0: return launch_direct_t<FILL, MINB, 0, HITS>(st, a, sm_count, smem, threads);
-        case 1: return launch_direct_t<FILL, MINB, 1, HITS>(st, a, sm_count, smem, threads);
-        default: return launch_direct_t<FILL, MINB, 2, HITS>(st, a, sm_count, smem, threads);
+        case 0: return launch_direct_t<FILL, MINB, 0, HITS, LEAN>(st, a, sm_count, smem, threads);
+        case 1: return launch_direct_t<FILL, MINB, 1, HITS, LEAN>(st, a, sm_count, smem, threads);
+        default: return launch_direct_t<FILL, MINB, 2, HITS, LEAN>(st, a, sm_count, smem, threads);
     }
 }
 
@@ -910,6 +911,9 @@ cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, 
     const size_t smem = dg_direct_smem_bytes(a, fill);
     const int threads = a.n_warps * 32;
     ++g_direct_launches;
+    if (fill && a.max_neighbors >= a.row_cap)  // no row is truncated: the lean sort
+        return min_blocks <= 2 ? launch_direct_e<true, 2, false, true>(st, a, sm_count, smem, threads)
+                               : launch_direct_e<true, 3, false, true>(st, a, sm_count, smem, threads);
     if (fill)
         return min_blocks <= 2 ? launch_direct_e<true, 2, false>(st, a, sm_count, smem, threads)
                                : launch_direct_e<true, 3, false>(st, a, sm_count, smem, threads);

@@ -343,7 +343,11 @@ struct DgFixedOffset {
 #endif
 #define DG_SK_WORDS(n) ((n) + (((n) >> 5) + 4))
 
-template <int EPL, class Payload, class OP>
+// LEAN: the variant the uncapped sweep-fill kernel (the headline kernel, 128 registers, bound by instruction issue)
+// instantiates -- no top-k prefilter (its rows are never truncated) and the compact per-entry tie ranking instead of
+// the warp-cooperative one.  Same results; measured on the same box, the full variant costs that kernel 6 % (8.82
+// against 8.33 ms: two registers spill), and calling either piece out of line costs more (8.96 - 9.0 ms).
+template <int EPL, class Payload, class OP, bool LEAN = false>
 __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
                                                          float* __restrict__ fd, int* __restrict__ tie,
                                                          const Payload& P, int m, int keep, double key_scale, OP& op,
@@ -439,6 +443,43 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
             fd[p] = (float)d;
         }
     } else {
+        if (LEAN) {
+        // truncated rows: a position beyond `keep` whose key differs from the key AT position keep belongs to a run that
+        // starts after it -- its rank can neither be emitted (rank < keep) nor enter the tie statistic (rank <= keep),
+        // so only the runs that reach into [0, keep] are resolved (capped rows of ideal lattices: 20 of ~300 entries)
+        const uint32_t tk_edge = keep < m ? (sk[DG_SKI(keep)] & ~IDMASK) : 0u;
+        for (int p = lane; p < m; p += 32) {
+            const uint32_t w = sk[DG_SKI(p)];
+            const uint32_t tk = w & ~IDMASK;
+            if (p > keep && tk != tk_edge) continue;
+            const int e = (int)(w & IDMASK);
+            const double de = rd[e];
+            int s = p, t = p + 1;
+            while (s > 0 && (sk[DG_SKI(s - 1)] & ~IDMASK) == tk) --s;
+            while (t < m && (sk[DG_SKI(t)] & ~IDMASK) == tk) ++t;
+            int rank = p;
+            if (t - s > 1) {  // run of equal truncated keys: exact canonical rank inside it
+                const unsigned long long ke = dg_payload_tie_key(P, e);
+                rank = s;
+                for (int q = s; q < t; ++q) {
+                    if (q == p) continue;
+                    const int f = (int)(sk[DG_SKI(q)] & IDMASK);
+                    const double df = rd[f];
+                    if (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ++rank;
+                }
+            }
+            if (rank < keep) {
+                int j;
+                uint32_t img;
+                P.get(e, j, img);
+                dst[o + rank] = j;
+                image[o + rank] = img;
+                dist[o + rank] = de;
+                fd[rank] = (float)de;
+            }
+            if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
+        }
+        } else {
         // Runs of equal truncated keys (coordination shells of an ideal lattice: every shell is one run) get their
         // exact canonical order (distance, dst, image).  Truncated rows: a position beyond `keep` whose key differs
         // from the key AT position keep belongs to a run that starts after it -- its rank can neither be emitted
@@ -529,6 +570,7 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                 if (m > keep && (rank == keep - 1 || rank == keep)) tie[rank - keep + 1] = e;
             }
         }
+        }
         if (m > keep && keep > 0) {  // truncated through a distance tie?  (statistic of rule R8)
             __syncwarp();
             if (lane == 0 && rd[tie[0]] == rd[tie[1]]) atomicAdd(&stats->n_tie_rows, 1);
@@ -614,15 +656,17 @@ __device__ __forceinline__ int dg_row_prefilter(double* rd, const Payload& P, in
     return dg_row_prefilter_t<16>(rd, P, m, keep, r2, lane);
 }
 
-template <class Payload, class OP>
+template <class Payload, class OP, bool LEAN = false>
 __device__ __forceinline__ long long dg_row_sort_bitonic_any_op(double* rd, uint32_t* sk, float* fd, int* tie,
                                                                 const Payload& P, int m, int keep, double key_scale,
                                                                 OP& op, int* dst, uint32_t* image, double* dist,
                                                                 DgStats* stats, int lane) {
-    m = dg_row_prefilter(rd, P, m, keep, key_scale, lane);
-    if (m <= 128) return dg_row_sort_bitonic<4>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
-    if (m <= 256) return dg_row_sort_bitonic<8>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
-    return dg_row_sort_bitonic<16>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    if (!LEAN) m = dg_row_prefilter(rd, P, m, keep, key_scale, lane);
+    if (m <= 128)
+        return dg_row_sort_bitonic<4, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    if (m <= 256)
+        return dg_row_sort_bitonic<8, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    return dg_row_sort_bitonic<16, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
 }
 template <class Payload>
 __device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk, float* fd, int* tie, const Payload& P,
@@ -635,7 +679,7 @@ __device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
 // NBk (number of buckets) is a power of two, 32 <= NBk <= 2048.  All 32 lanes must call.
 // rbf.K4 > 0: fused Gaussian RBF epilogue straight from the sorted distances in shared memory.
-template <class OP>
+template <class OP, bool LEAN = false>
 __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
                                                     double key_scale, OP& op, int* __restrict__ dst,
                                                     uint32_t* __restrict__ image, double* __restrict__ dist,
@@ -643,8 +687,9 @@ __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int
     if (m <= DG_BITONIC_MAX) {
         const RowBufPayload P{sm.rj, sm.rn};
         // padded sorted words: bs (unused by this path) and sk are adjacent, 2 * row_cap words
-        const long long o = dg_row_sort_bitonic_any_op(sm.rd, sm.bs, sm.fd, sm.cnt, P, m, keep, key_scale, op, dst,
-                                                       image, dist, stats, lane);
+        const long long o = dg_row_sort_bitonic_any_op<RowBufPayload, OP, LEAN>(sm.rd, sm.bs, sm.fd, sm.cnt, P, m, keep,
+                                                                                key_scale, op, dst, image, dist, stats,
+                                                                                lane);
         if (o >= 0 && rbf.K4 > 0) {
             dg_rbf_row(sm.fd, keep, o, lane, rbf);
             __syncwarp();
@@ -746,10 +791,11 @@ __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int
     }
 }
 
+template <bool LEAN = false>
 __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
                                                  double key_scale, long long o, int* __restrict__ dst,
                                                  uint32_t* __restrict__ image, double* __restrict__ dist,
                                                  DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     DgFixedOffset op{o};
-    dg_row_sort_emit_op(sm, m, keep, NBk, inv_rc, key_scale, op, dst, image, dist, stats, lane, rbf);
+    dg_row_sort_emit_op<DgFixedOffset, LEAN>(sm, m, keep, NBk, inv_rc, key_scale, op, dst, image, dist, stats, lane, rbf);
 }

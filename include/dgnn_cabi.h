@@ -214,7 +214,10 @@ void* dgnn_stream(dgnn_ctx* ctx);
  * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048);
  * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off);
  * onepass: single-pass build (no count pass) of batches without cell-list structures: -1 auto (small batches),
- * 0 off (count + fill), 1 wherever legal. */
+ * 0 off (count + fill), 1 wherever legal;
+ * speculative: capped batches built with a priori offsets row a = a * max_neighbors (see dgnn_build_info.speculative):
+ * 0 off (default: measured slower than the hit-list plan, it saves the hit lists' memory), -1 auto (large batches whose
+ * sparsest structure's density estimate is >= 4 * max_neighbors + 32), 1 wherever legal. */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus
