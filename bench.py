@@ -11,8 +11,9 @@ row_ptr back (D2H inside) -- graphs stay device-resident by design (north_star: 
 N > 1: launched by torchrun, one rank per GPU, structures sharded by rank, NO collective on the data path; only the
 timing all-reduce and the final host-side gather of per-shard edge counts use torch.distributed.
 
---impl reference: the reference's own CPU algorithm for the same path (the oracle port: image cloud -> KD-tree ->
-radius search -> sort -> fp64 RBF; the verbatim reference cannot be compiled here) on all host cores,
+--impl reference: the reference's own CPU implementation of the same path -- its src/graph/*.cpp and structure.cpp
+compiled verbatim against interface shims for its two un-vendored headers (oracle/_ref; the
+oracle's KD-tree port only when that library is missing) -- on all host cores, on the same S structures per step,
 rank 0 only.
 """
 from __future__ import annotations
@@ -114,40 +115,81 @@ class ClockSampler:
         return out
 
 
-def cpu_reference_leg(O, syn, n_structs, threads, seed0=1234):
-    """The reference algorithm on host cores (oracle port, KD-tree variant) on a bounded C2 sample."""
-    b = syn.c2_batch(n_structs, seed0=seed0)
-    edges, _, sec, used = O.build_batch(b.atom_offsets, b.x, b.y, b.z, b.lattices, R_CUTOFF, UNCAPPED, 1e-10,
-                                        R_CUTOFF, DR, O.ALGO_KDTREE, threads)
-    return edges, sec, used, b.n_structs
+def load_reference():
+    """The CPU arm: the reference's OWN sources compiled verbatim against interface shims (oracle/_ref, kind
+    "reference+shim") when that library is present, else the oracle's KD-tree port (kind "port")."""
+    odir = os.path.join(ROOT, "oracle")
+    if odir not in sys.path:
+        sys.path.insert(0, odir)
+    try:
+        import ref_py
+        if ref_py.available():
+            ref_py.lib()
+            return ref_py, "reference+shim"
+    except Exception as exc:  # noqa: BLE001
+        print(f"bench.py: oracle/_ref unavailable ({exc}); timing the oracle port instead", file=sys.stderr)
+    return None, "port"
+
+
+REF_NOTE = {
+    "reference+shim": "the reference's own src/graph/*.cpp + src/crystal/structure.cpp compiled verbatim (oracle/_ref; "
+                      "Eigen / nanoflann headers replaced by interface shims): Structure + NeighborList + CrystalGraph "
+                      "per structure, std::threads over structures",
+    "port": "CPU port of the reference algorithm (image cloud -> KD-tree leaf 10 -> radius search -> sort -> fp64 exp "
+            "RBF), std::threads over structures; oracle/_ref not present",
+}
+
+
+def cpu_reference_leg(b, threads, n_structs=None):
+    """The reference path on host cores over the first n_structs structures of batch b -> (edges, seconds, threads,
+    structures, kind)."""
+    R, kind = load_reference()
+    if n_structs is not None and n_structs < b.n_structs:
+        b = b.slice(0, n_structs)
+    if R is not None:
+        edges, _, sec, used = R.build_batch(b.atom_offsets, b.frac, b.lattices, b.species, R_CUTOFF, UNCAPPED, 1e-10,
+                                            R_CUTOFF, DR, 92, threads)
+    else:
+        O = entry.load_oracle()
+        edges, _, sec, used = O.build_batch(b.atom_offsets, b.x, b.y, b.z, b.lattices, R_CUTOFF, UNCAPPED, 1e-10,
+                                            R_CUTOFF, DR, O.ALGO_KDTREE, threads)
+    return edges, sec, used, b.n_structs, kind
+
+
+def bench_config(S, out_gb):
+    """`config` of the JSON line -- identical in both arms (same workload, same structures per step)."""
+    return {"workload": WORKLOAD, "structures_per_gpu_per_step": S,
+            "l2": "no flush: every step streams ~%.1f GB of outputs per GPU (>> 126 MB L2)" % out_gb}
 
 
 def run_reference(args, rank):
     if rank != 0:
         return 0
-    O = entry.load_oracle()
     pkg = entry.load_package()
     cores = os.cpu_count() or 1
-    sample = 64 * cores if args.structures is None else args.structures
-    for _ in range(args.warmup):
-        cpu_reference_leg(O, pkg.synthetic, max(cores, 8), cores)
+    S = args.structures or 10_000
+    b = pkg.synthetic.c2_batch(S, seed0=1234)       # the GPU arm's rank-0 batch, structure for structure
+    kind = load_reference()[1]
+    for _ in range(args.warmup):                    # warm-up steps only need to page the code and the pool in
+        cpu_reference_leg(b, cores, max(min(S, 8 * cores), 1))
     tot_e, tot_s, tot_n = 0, 0.0, 0
     for _ in range(args.steps):
-        e, sec, used, n = cpu_reference_leg(O, pkg.synthetic, sample, cores)
+        e, sec, used, n, kind = cpu_reference_leg(b, cores)
         tot_e += e
         tot_s += sec
         tot_n += n
     val = tot_e / tot_s
+    E = tot_e // max(args.steps, 1)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * tot_s / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "structures_per_sec": tot_n / tot_s,
-        "config": {"workload": WORKLOAD, "structures_per_step": sample,
-                   "note": "CPU port of the reference algorithm (image cloud -> KD-tree leaf 10 -> radius search -> "
-                           "sort -> fp64 exp RBF); verbatim reference unbuildable here (Eigen/nanoflann absent)"},
-        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{sample} C2 structures per step x {args.steps} steps, all host threads"},
+        "config": bench_config(S, (E * (16 + 4 * K_BINS)) / 1e9),
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{S} C2 structures per step x {args.steps} steps (the GPU arm's batch), all host "
+                                   f"threads; warm-up steps run {max(min(S, 8 * cores), 1)} structures",
+                         "note": REF_NOTE[kind]},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -192,7 +234,9 @@ def main():
     syn, sh = pkg.synthetic, pkg.sharding
 
     S = args.structures or 10_000
-    warm = max(args.warmup, 3)
+    warm = args.warmup
+    if warm < 3:
+        print(f"bench.py: --warmup {warm} < 3: the timing rules want at least 3 warm-up steps", file=sys.stderr)
     # structure-sharded: rank r owns structures [r*S, (r+1)*S) of the N*S-structure job (disjoint seeds)
     b = syn.c2_batch(S, seed0=1234 + rank * S)
     gb = pkg.GraphBuilder(local)
@@ -312,9 +356,9 @@ def main():
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64 (accept test, distances) + f32 (RBF features)", "data": "synthetic",
         "structures_per_sec": world * S * args.steps / sec,
-        "config": {"workload": WORKLOAD, "structures_per_gpu_per_step": S, "edges_per_gpu_per_step": E,
-                   "sharding": f"by structure, {world} rank(s), no collective on the data path",
-                   "l2": "no flush: every step streams ~%.1f GB of outputs per GPU (>> 126 MB L2)" % (all_bytes / 1e9)},
+        "config": bench_config(S, (E * (16 + 4 * K_BINS)) / 1e9),
+        "edges_per_gpu_per_step": E,
+        "sharding": f"by structure, {world} rank(s), no collective on the data path",
         "roofline": {"bound": "hbm", "kernel": top_name,
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "frac_of_8TBs_nominal": achieved / 8000.0, "peak_source": peak_src,
@@ -338,17 +382,17 @@ def main():
     }
 
     if rank == 0 and not args.no_cpu_baseline and world == 1:
-        O = entry.load_oracle()
         cores = os.cpu_count() or 1
         t0 = time.time()
-        e1c, s1c, _, n1c = cpu_reference_leg(O, syn, 96, 1)
-        eac, sac, used, nac = cpu_reference_leg(O, syn, 96 * cores, cores)
-        line["cpu_baseline"] = {"value": eac / sac, "unit": UNIT, "cores": used, "kind": "port",
+        e1c, s1c, _, n1c, kind = cpu_reference_leg(b, 1, 64)
+        eac, sac, used, nac, kind = cpu_reference_leg(b, cores, min(S, 256 * cores))
+        line["cpu_baseline"] = {"value": eac / sac, "unit": UNIT, "cores": used, "kind": kind,
                                 "structures_per_sec": nac / sac,
-                                "sample": f"{nac} C2 structures, all {used} host threads over structures "
-                                          f"({time.time() - t0:.1f} s of wall time incl. 1-core leg)"}
-        line["cpu_baseline_1core"] = {"value": e1c / s1c, "unit": UNIT, "cores": 1, "kind": "port",
-                                      "structures_per_sec": n1c / s1c, "sample": f"{n1c} C2 structures"}
+                                "sample": f"first {nac} structures of the step's batch, all {used} host threads over "
+                                          f"structures ({time.time() - t0:.1f} s of wall time incl. 1-core leg)",
+                                "note": REF_NOTE[kind]}
+        line["cpu_baseline_1core"] = {"value": e1c / s1c, "unit": UNIT, "cores": 1, "kind": kind,
+                                      "structures_per_sec": n1c / s1c, "sample": f"first {n1c} structures of the batch"}
     if rank == 0:
         sys.stdout.flush()
         os.write(json_fd, (json.dumps(line) + "\n").encode())

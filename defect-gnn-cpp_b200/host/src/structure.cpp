@@ -11,12 +11,13 @@ Structure::Structure(const io::VASPStructure& vasp) : lattice_(vasp.lattice), in
     for (size_t e = 0; e < vasp.counts.size(); ++e) counts_[static_cast<int>(e)] = vasp.counts[e];
     const auto n = static_cast<size_t>(vasp.frac_coords.rows());
     atoms_.reserve(n);
-    const Eigen::Matrix3d lt = lattice_.transpose();
     for (size_t i = 0; i < n; ++i) {
         Atom a;
         a.element = vasp.atom_types[i];
         a.frac_position = vasp.frac_coords.row(static_cast<Eigen::Index>(i));
-        a.position = lt * a.frac_position;
+        // the reference's own expression (structure.cpp:17): with real Eigen the evaluation order -- (e0 + e1) + e2,
+        // vectorised redux over a contiguous column of the lattice -- comes from the expression type, so keep it
+        a.position = lattice_.transpose() * a.frac_position;
         atoms_.push_back(a);
     }
 }

@@ -121,11 +121,11 @@ void parse_text(const char* text, size_t len, Parsed& out, const std::string& wh
                 f[1] = cx * inv[1] + cy * inv[4] + cz * inv[7];
                 f[2] = cx * inv[2] + cy * inv[5] + cz * inv[8];
             }
-            // position = lattice^T * frac (structure.cpp:17): component k = e0 + (e1 + e2), e_r = L(r,k) f_r -- the
-            // order of Eigen's unrolled 3-term reduction (same as the facade's Structure)
-            out.x.push_back(L[0] * f[0] + (L[3] * f[1] + L[6] * f[2]));
-            out.y.push_back(L[1] * f[0] + (L[4] * f[1] + L[7] * f[2]));
-            out.z.push_back(L[2] * f[0] + (L[5] * f[1] + L[8] * f[2]));
+            // position = lattice^T * frac (structure.cpp:17): component k = (e0 + e1) + e2, e_r = L(r,k) f_r -- the
+            // order of Eigen 3.4's vectorised 3-term reduction on x86-64 (pinned on oracle/_ref; same as the facade's Structure)
+            out.x.push_back((L[0] * f[0] + L[3] * f[1]) + L[6] * f[2]);
+            out.y.push_back((L[1] * f[0] + L[4] * f[1]) + L[7] * f[2]);
+            out.z.push_back((L[2] * f[0] + L[5] * f[1]) + L[8] * f[2]);
             out.element.push_back(static_cast<int>(el));
         }
     }

@@ -637,7 +637,7 @@ void orc_frac_to_cart(int64_t n, const double* frac, const double lattice[9], do
     for (int64_t i = 0; i < n; ++i) {
         const double* f = frac + 3 * i;
         for (int k = 0; k < 3; ++k)
-            outs[k][i] = lattice[0 + k] * f[0] + (lattice[3 + k] * f[1] + lattice[6 + k] * f[2]);
+            outs[k][i] = (lattice[0 + k] * f[0] + lattice[3 + k] * f[1]) + lattice[6 + k] * f[2];
     }
 }
 

@@ -13,8 +13,13 @@ Outputs
   c1_capped_edges.npz full oracle edge lists for the reference-default parameters (r_c=10, cap 20) -- small
   kat.json            analytic known answers (simple-cubic shells, closed-form Gaussians)
 
-The reference has no tests / golden vectors for this path ("parity unpinned"), so these pin the
-ORACLE: any later change to oracle/ that alters a digest fails tests/test_oracle.py.
+The reference has no tests / golden vectors for this path.  The fixtures are therefore generated
+from the REFERENCE'S OWN CODE run here: oracle/_ref/libref_graph.so = the reference's src/graph/*.cpp, structure.cpp and
+vasp_parser.cpp compiled verbatim (oracle/Makefile `ref`).  Inputs come from the reference's io::parse_vasp, positions
+from crystal::Structure, edge counts / distance sums from graph::NeighborList; the canonical edge-list digest (which
+needs the integer image offsets the reference does not store) comes from the oracle AFTER the oracle's rows have been
+checked to be the reference's rows as sets of (idx, distance bits, displacement bits) -- tests/test_ref_pin.py keeps
+checking exactly that.  Any later change to oracle/ that alters a digest fails tests/test_oracle.py.
 """
 import glob
 import hashlib
@@ -30,6 +35,10 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, os.path.join(ROOT, "oracle"))
 import oracle_py as O  # noqa: E402
+import ref_py as R  # noqa: E402
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, ROOT)
+from test_ref_pin import assert_same_lists  # noqa: E402
 
 spec = importlib.util.spec_from_file_location("dgnn_synthetic", os.path.join(ROOT, "defect-gnn-cpp_b200", "synthetic.py"))
 syn = importlib.util.module_from_spec(spec)
@@ -71,8 +80,14 @@ def main():
     capped = {}
     for f in files:
         name = os.path.splitext(os.path.basename(f))[0]
-        L, frac, species = syn.parse_poscar(open(f).read())
-        x, y, z = syn.frac_to_cart(frac, L)
+        L, frac, species = R.parse_vasp(f)                       # the reference's parser
+        Lp, fp, sp_ = syn.parse_poscar(open(f).read())           # the fixture loader must agree with it bit for bit
+        assert np.array_equal(L, Lp) and np.array_equal(frac, fp) and np.array_equal(species, sp_), name
+        st = R.Structure(frac, L, species, 3.0, 1)
+        pos = st.neighbor_list().pos                             # crystal::Structure positions (structure.cpp:17)
+        st.close()
+        x, y, z = (np.ascontiguousarray(pos[:, k]) for k in range(3))
+        assert all(np.array_equal(a, b) for a, b in zip((x, y, z), syn.frac_to_cart(frac, L))), name
         names.append(name)
         store[f"{name}__lattice"] = L
         store[f"{name}__frac"] = frac
@@ -81,8 +96,11 @@ def main():
         expected[name] = {"n_atoms": int(len(x))}
         for pname, rc, cap, dr in PARAM_SETS:
             g = O.neighbor_list(x, y, z, L, rc, cap, 1e-10, O.ALGO_BRUTE)
+            ref = R.neighbor_list(frac, L, rc, cap, 1e-10)
+            assert_same_lists(ref, g, None if cap == O.UNCAPPED else cap, f"{name}/{pname}")
+            assert ref.n_edges == g.n_edges and float(np.sum(ref.dist)) == float(np.sum(g.dist))
             deg = np.diff(g.row_ptr)
-            rec = {
+            rec = {"source": "oracle/_ref",
                 "r_cutoff": rc, "max_neighbors": (None if cap == O.UNCAPPED else cap), "dr": dr,
                 "num_images": g.num_images, "n_edges": g.n_edges, "deg_min": int(deg.min()), "deg_max": int(deg.max()),
                 "n_near_cutoff": g.n_near_cutoff, "n_tie_rows": g.n_tie_rows, "edge_sha256": edge_digest(g),
