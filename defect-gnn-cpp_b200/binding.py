@@ -73,8 +73,6 @@ class DgnnBuildInfo(C.Structure):
         ("staged_tile_cap", C.c_int32), ("row_cap", C.c_int32),
         ("n_cell_structs", C.c_int32), ("direct_warps", C.c_int32), ("rbf_fused", C.c_int32), ("hit_cap", C.c_int32),
         ("onepass", C.c_int32), ("onepass_fallback_rows", C.c_int32),
-        ("pipeline_parts", C.c_int32), ("pipeline_refill", C.c_int32),
-        ("speculative", C.c_int32), ("est_min_degree", C.c_int32),
     ]
 
 

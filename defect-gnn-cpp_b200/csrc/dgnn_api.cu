@@ -66,18 +66,8 @@ struct dgnn_ctx {
     int64_t* sink_seo = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
     int fill_hits_bulk = 1;               // k_fill_hits feature stores: bulk-copy engine (1) or st.global.cs (0)
-    int pipeline = 0;                     // fill of part k and count of part k+1 in one kernel.  Evaluated and kept OFF:
-                                          // the fill kernel is bound by instruction issue, the interleaved count does not
-                                          // hide (C2, same box: 11.12 ms against 10.37 ms with the passes back to back)
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
-    // speculative capped build: 0 off, -1 auto (large capped batches whose density estimate allows it), 1 wherever legal.
-    // Off by default: measured SLOWER than count-with-hit-lists + hit-list fill (2 k C2 structures, r_c = 10, cap 20:
-    // 3.23 vs 2.97 ms) -- the sweep into the shared-memory row buffer runs at 2 CTAs per SM, the hit-list count at full
-    // occupancy.  What it saves is memory: no hit lists (12 B x hit_cap per atom).
-    int spec_opt = 0;
-    bool spec_skip = false;               // (set while a failed speculation is being rebuilt)
-    int spec_failed = 0;                  // the rebuild reports it in dgnn_build_info
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
     // the last successful build, for the CSR consumers (collation, viewer arrays, neighbourhood clouds)
@@ -340,11 +330,6 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->upload_chunks = (int)value;
     } else if (!strcmp(name, "fill_hits_bulk")) {
         ctx->fill_hits_bulk = value != 0.0;
-    } else if (!strcmp(name, "speculative")) {
-        if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "speculative must be -1, 0 or 1");
-        ctx->spec_opt = (int)value;
-    } else if (!strcmp(name, "pipeline")) {
-        ctx->pipeline = value != 0.0;
     } else if (!strcmp(name, "sym_count")) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
@@ -517,18 +502,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         if (r != DGNN_OK) return r;
         have_est = true;
     }
-    // Speculative capped build: when even the sparsest structure's density promises several times max_neighbors
-    // candidates per atom (surface atoms of a slab still see half of it), every row will be truncated to the cap and row a starts at a * cap -- no count pass, no hit lists.
-    const long long onepass_small_rows = (long long)ctx->sm_count * 2 * 8 * 2;
-    const int est_min_deg = have_est && ctx->h_stats->est_sparse > 0 ? 1000000 - ctx->h_stats->est_sparse : 0;
-    const bool spec_try = have_est && ctx->spec_opt != 0 && !ctx->spec_skip && N > 0 && ctx->h_stats->err_status == 0 &&
-                          ctx->h_stats->n_cell_structs == 0 && b->max_neighbors >= 1 && b->max_neighbors <= 4096 &&
-                          (long long)b->max_neighbors * N < (1LL << 40) &&
-                          (!want_rbf || (ctx->fuse_rbf && (K & 3) == 0 &&
-                                         (long long)b->max_neighbors * (K / 4) < (1LL << 22))) &&
-                          (ctx->spec_opt > 0 || ((long long)est_min_deg >= 4 * (long long)b->max_neighbors + 32 &&
-                                                 !(ctx->onepass_opt != 0 && N <= onepass_small_rows)));
-    if (ctx->hit_cap_opt < 0 && N > 0 && !spec_try) {
+    if (ctx->hit_cap_opt < 0 && N > 0) {
         const long long est = ctx->h_stats->est_deg;
         // Worth it only where the fill pass is bound by the traversal, not by the bytes it writes: the lists cost the
         // count pass ~35 % more time and the fill pass 12 B of extra reads per accepted pair.  Measured on C2: uncapped
@@ -594,57 +568,14 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // ---- single-pass build (direct-path batches): traversal + look-back row offsets + sort + emit in one kernel --
     // The edge arena and the row buffers are sized from the density estimate; rows that outgrow the buffer, or an
     // arena that turns out too small, are completed by the regular fill pass afterwards (row_ptr is final either way).
-    bool onepass = false, onepass_fused_rbf = false, pipelined = false;
+    bool onepass = false, onepass_fused_rbf = false;
     int row_cap_1p = 0;
     // Auto policy: the look-back couples every CTA to its predecessors with one step of slack, which costs large batches
     // more than the count pass saves (C2 10 k structures: 11.8 ms vs 10.9 ms count + fill), but a batch of a few steps
     // per CTA -- the reference's one-structure-per-call API above all -- finishes in one kernel and one sync less
     // (9 shipped POSCARs: 0.31 ms vs 1.37 ms).
-    bool spec = false;
-    if (spec_try) {
-        const long long est = ctx->h_stats->est_deg;
-        long long rc = est + est / 8 + 8;
-        if (rc < max_nb) rc = max_nb;
-        if (rc > DGNN_MAX_DEGREE) rc = DGNN_MAX_DEGREE;
-        if (ctx->onepass_row_cap > 0) rc = ctx->onepass_row_cap;
-        row_cap_1p = round_up((int)(rc > 32 ? rc : 32), 32);
-        DgDirectArgs O = D;
-        O.hit_cap = 0;
-        O.hits = nullptr;
-        O.hits_d2 = nullptr;
-        O.row_cap = row_cap_1p;
-        O.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap_1p <= 256 ? 256 : (row_cap_1p <= 1024 ? 512 : 1024));
-        O.n_warps = 8;
-        while (O.n_warps > 1 && (int)dg_direct_smem_bytes(O, true) > ctx->smem_optin) O.n_warps >>= 1;
-        onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 && (long long)max_nb * (K / 4) < (1LL << 22);
-        if ((int)dg_direct_smem_bytes(O, true) <= ctx->smem_optin && row_cap_1p >= max_nb &&
-            (!want_rbf || onepass_fused_rbf)) {
-            const size_t e_spec = (size_t)N * (size_t)max_nb;
-            ENSURE(ctx->dst, (e_spec + 1) * 4);
-            ENSURE(ctx->image, (e_spec + 1) * 4);
-            ENSURE(ctx->dist, (e_spec + 1) * 8);
-            if (want_rbf) ENSURE(ctx->rbf, e_spec * (size_t)K * 4 + 16);
-            O.dst = (int*)ctx->dst.p;
-            O.image = (uint32_t*)ctx->image.p;
-            O.dist = (double*)ctx->dist.p;
-            O.row_ptr_out = (long long*)ctx->row_ptr.p;
-            if (onepass_fused_rbf) {
-                O.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
-                O.rbf.recur = ctx->rbf_recur;
-            }
-            for (int c = 0; c < n_up; ++c) {
-                if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
-                dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
-                                      (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
-            }
-            CU(cudaEventRecord(ctx->ev.e[3], st));
-            CU(dg_launch_direct_spec(st, O, ctx->sm_count));
-            onepass = true;
-            spec = true;
-        }
-    }
     const long long onepass_auto_rows = (long long)ctx->sm_count * 2 * 8 * 2;  // two steps of a full grid
-    if (!spec && have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
+    if (have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
         ctx->h_stats->n_cell_structs == 0 &&
         (ctx->onepass_opt > 0 || (N <= onepass_auto_rows && (hit_cap == 0 || ctx->hit_cap_opt < 0)))) {
         const long long est = ctx->h_stats->est_deg;
@@ -709,80 +640,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             D.sym_band = (D.near_d2_hi - D.near_d2_lo) + 1.0e-9 * r2;
             CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
         }
-        // Pipelined plan (large direct-path batches, symmetric count): the fill of part k and the count of part k+1
-        // share one kernel, so the issue-bound count hides under the store-bound fill.  Row offsets chain from part to
-        // part on the device; arena and row buffer come from the density estimate like the single-pass plan's.
-        DgDirectArgs F = D;
-        if (sym && ctx->pipeline && n_up >= 2 && have_est && ctx->h_stats->err_status == 0 &&
-            ctx->h_stats->n_cell_structs == 0 && ctx->direct_min_blocks <= 2) {
-            const long long est = ctx->h_stats->est_deg;
-            long long rc = est + est / 8 + 8;
-            if (rc > DGNN_MAX_DEGREE) rc = DGNN_MAX_DEGREE;
-            if (ctx->onepass_row_cap > 0) rc = ctx->onepass_row_cap;
-            row_cap_1p = round_up((int)(rc > 32 ? rc : 32), 32);
-            double est_e = (double)ctx->h_stats->est_edges;
-            if (est_e > (double)N * (double)max_nb) est_e = (double)N * (double)max_nb;
-            est_e = est_e * ctx->onepass_arena_scale + (ctx->onepass_arena_scale >= 1.0 ? 64.0 * 1024.0 : 0.0);
-            F.row_cap = row_cap_1p;
-            F.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap_1p <= 256 ? 256 : (row_cap_1p <= 1024 ? 512 : 1024));
-            F.n_warps = 8;
-            if ((int)dg_direct_smem_bytes(F, true) <= ctx->smem_optin && est_e < 9.0e18) {
-                const size_t e_est = (size_t)est_e;
-                ENSURE(ctx->dst, (e_est + 1) * 4);
-                ENSURE(ctx->image, (e_est + 1) * 4);
-                ENSURE(ctx->dist, (e_est + 1) * 8);
-                if (want_rbf) ENSURE(ctx->rbf, e_est * (size_t)K * 4 + 16);
-                size_t cap_e = ctx->dst.cap / 4;
-                if (ctx->image.cap / 4 < cap_e) cap_e = ctx->image.cap / 4;
-                if (ctx->dist.cap / 8 < cap_e) cap_e = ctx->dist.cap / 8;
-                if (want_rbf && (ctx->rbf.cap - 16) / ((size_t)K * 4) < cap_e) cap_e = (ctx->rbf.cap - 16) / ((size_t)K * 4);
-                F.edge_cap = (long long)cap_e - 1;
-                F.row_ptr = (const long long*)ctx->row_ptr.p;
-                F.dst = (int*)ctx->dst.p;
-                F.image = (uint32_t*)ctx->image.p;
-                F.dist = (double*)ctx->dist.p;
-                const int keep_max_1p = row_cap_1p < max_nb ? row_cap_1p : max_nb;
-                onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 &&
-                                    (long long)keep_max_1p * (K / 4) < (1LL << 22);
-                if (onepass_fused_rbf) {
-                    F.rbf = dg_make_rbf_epi(K, b->rbf_r_cutoff, b->dr, (float*)ctx->rbf.p);
-                    F.rbf.recur = ctx->rbf_recur;
-                }
-                pipelined = true;
-            }
-        }
-        if (pipelined) {
-            if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[0], 0));
-            dg_launch_direct_prep(st, up_a[0], up_a[1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
-                                  (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
-            D.row_begin = up_a[0];
-            D.row_end = up_a[1];
-            if (up_a[1] > up_a[0]) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
-            CU(cudaEventRecord(ctx->ev.e[3], st));
-            for (int c = 0; c < n_up; ++c) {
-                const long long p0 = up_a[c], p1 = up_a[c + 1];
-                dg_scan_i32_i64_based(st, (const int*)ctx->deg.p + p0, (long long*)ctx->row_ptr.p + p0, p1 - p0,
-                                      (long long*)ctx->scratch.p, c > 0 ? (const long long*)ctx->row_ptr.p + p0 : nullptr);
-                F.row_begin = p0;
-                F.row_end = p1;
-                F.cnt_begin = F.cnt_end = 0;
-                if (c + 1 < n_up) {
-                    if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c + 1], 0));
-                    dg_launch_direct_prep(st, up_a[c + 1], up_a[c + 2], S, d_off, d_x, d_y, d_z, small,
-                                          (int*)ctx->astruct.p, (double*)ctx->fa.p, (double*)ctx->fb.p,
-                                          (double*)ctx->fc.p, d_stats);
-                    F.cnt_begin = up_a[c + 1];
-                    F.cnt_end = up_a[c + 2];
-                }
-                if (p1 > p0 || F.cnt_end > F.cnt_begin) CU(dg_launch_direct_fill_cnt(st, F, ctx->sm_count));
-                if (c + 1 < n_up && up_a[c + 2] > up_a[c + 1]) {
-                    D.row_begin = up_a[c + 1];
-                    D.row_end = up_a[c + 2];
-                    dg_launch_cap_degrees(st, D, ctx->sm_count);
-                }
-            }
-            D.row_begin = D.row_end = 0;
-        } else {
+        {
             for (int c = 0; c < n_up; ++c) {
                 if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
                 dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
@@ -808,20 +666,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
     if (ctx->h_stats->lb_timeout) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
-    if (spec && ctx->h_stats->spec_fail) {
-        // a row came up short of max_neighbors (vacuum, a sparse corner of a cell): the offsets were wrong -- rebuild
-        // the batch with counted offsets (inputs are re-read from the caller's buffers)
-        if (upload.armed) CU(cudaStreamSynchronize(ctx->copy_stream));
-        ctx->spec_skip = true;
-        ctx->spec_failed = 1;
-        const int r = dgnn_build(ctx, b, out);
-        ctx->spec_skip = false;
-        ctx->spec_failed = 0;
-        return r;
-    }
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
     int n_fallback_rows = ctx->h_stats->n_fallback_rows;
-    const bool onepass_redo_all = (onepass || pipelined) && ctx->h_stats->cap_overflow != 0;
+    const bool onepass_redo_all = onepass && ctx->h_stats->cap_overflow != 0;
 
     // ---- cell-list path (large structures): binning + count pass ---------------------------------------------
     DgTraverseArgs A;
@@ -939,11 +786,11 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         n_fallback_rows = ctx->h_stats->n_fallback_rows;
     }
-    if (!onepass && !pipelined) CU(cudaEventRecord(ctx->ev.e[3], st));
+    if (!onepass) CU(cudaEventRecord(ctx->ev.e[3], st));
     // offset sinks: row_ptr and the per-structure offsets are final here for the two-pass plans (the stream has just
     // been synchronised), so they travel back on the copy stream while the fill pass runs
     const bool sinks = ctx->sink_row_ptr != nullptr || ctx->sink_seo != nullptr;
-    const bool sinks_early = sinks && !onepass && !pipelined;
+    const bool sinks_early = sinks && !onepass;
     if (sinks_early) {
         upload.armed = true;  // (the guard also keeps these copies from outliving an early return)
         if (ctx->sink_row_ptr)
@@ -971,7 +818,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.n_warps = 8;
     // fused RBF epilogue: rows stream their K features right after the sort (needs K % 4 == 0 for the float4 stores)
     const int keep_max = max_deg < max_nb ? max_deg : max_nb;
-    const bool fuse_rbf = (onepass || pipelined) ? (onepass_fused_rbf && E > 0)
+    const bool fuse_rbf = onepass ? (onepass_fused_rbf && E > 0)
                                   : (want_rbf && E > 0 && ctx->fuse_rbf && (K & 3) == 0 &&
                                      (long long)keep_max * (K / 4) < (1LL << 22));
     if (want_rbf && E > 0) ENSURE(ctx->rbf, (size_t)E * (size_t)K * 4 + 16);
@@ -989,17 +836,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         H.cloud_j = (const int*)ctx->cj.p;
         H.cloud_n = (const uint32_t*)ctx->cn.p;
     }
-    bool use_hits = hit_cap > 0 && !onepass && !pipelined;
-    if (pipelined) {
-        // rows within the estimated row buffer are written; longer ones (and everything, if the estimated arena was
-        // too small and has just been regrown) go through the regular fill pass
-        D.hit_cap = 0;
-        D.skip_deg_le = onepass_redo_all ? 0 : row_cap_1p;
-        if (E > 0 && (onepass_redo_all || max_deg > row_cap_1p)) {
-            if (onepass_redo_all) CU(cudaMemsetAsync(&((DgStats*)ctx->stats.p)->n_tie_rows, 0, sizeof(int), st));
-            CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
-        }
-    }
+    bool use_hits = hit_cap > 0 && !onepass;
     if (onepass) {
         // everything is already written, except rows that outgrew the estimated row buffer (or all rows, when the
         // estimated arena was too small and has just been regrown by the ENSUREs above)
@@ -1017,7 +854,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     if (!use_hits) D.hit_cap = 0;
     if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
-    if (E > 0 && !onepass && !pipelined && (!use_hits || n_fallback_rows > 0))
+    if (E > 0 && !onepass && (!use_hits || n_fallback_rows > 0))
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
     if (n_cell_structs > 0 && E > 0 && (!use_hits || n_fallback_rows > 0)) {
         A.hit_cap = use_hits ? hit_cap : 0;
@@ -1095,12 +932,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.direct_warps = D.n_warps;
     I.rbf_fused = fuse_rbf ? 1 : 0;
     I.hit_cap = use_hits ? hit_cap : 0;
-    I.onepass = (onepass && !spec) ? (onepass_redo_all ? 2 : 1) : 0;
-    I.speculative = spec ? 1 : (ctx->spec_failed ? 2 : 0);
-    I.est_min_degree = est_min_deg;
-    I.pipeline_parts = pipelined ? n_up : 0;
-    I.pipeline_refill = pipelined ? (onepass_redo_all ? 2 : (max_deg > row_cap_1p ? 1 : 0)) : 0;
-    I.onepass_fallback_rows = (onepass && !spec) ? n_fallback_rows : 0;
+    I.onepass = onepass ? (onepass_redo_all ? 2 : 1) : 0;
+    I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
     return DGNN_OK;
 }
 

@@ -27,8 +27,6 @@ struct DgStats {
     int lb_timeout;              // single-pass build: a look-back spin gave up (must not happen: all CTAs are resident)
     unsigned long long est_edges;  // density estimate of the edge total, sum over structures of N_s * est_deg_s
     int est_sparse;              // 1000000 - smallest per-structure degree estimate (0: no non-empty structure)
-    int spec_fail;               // speculative capped build: a row had fewer than max_neighbors entries (or outgrew
-                                 // the row buffer) -> the build is redone with counted offsets
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -160,7 +158,6 @@ struct DgDirectArgs {
     long long edge_cap;             // edges the output arrays can hold
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
     long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
-    long long cnt_begin, cnt_end;   // k_direct_fill_cnt: rows whose symmetric count runs next to the fill of [row_begin, row_end)
     int fill_hits_bulk;             // k_fill_hits: features through the bulk-copy engine (1) or st.global.cs (0)
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
 };
@@ -176,14 +173,9 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
                            const DgSmall* small, int* astruct, double* fa, double* fb, double* fc, DgStats* stats);
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
-cudaError_t dg_launch_direct_fill_cnt(cudaStream_t st, const DgDirectArgs& a, int sm_count);
 void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count);
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
-// Speculative capped build: every row is assumed to reach max_neighbors, so row a starts at a * max_neighbors -- one
-// sweep + sort + emit kernel, no count pass, no scan, no hit lists.  stats->spec_fail tells whether the assumption held.
-// Writes row_ptr_out [N+1], deg_raw / deg_capped, max_deg, n_near, n_tie_rows.
-cudaError_t dg_launch_direct_spec(cudaStream_t st, const DgDirectArgs& a, int sm_count);
 cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 // fill pass from the count pass's hit lists (rows with degree <= hit_cap and image range <= DG_HIT_NMAX)
 size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a);

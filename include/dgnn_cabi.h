@@ -197,13 +197,6 @@ typedef struct {
     int32_t onepass;         /* 1: single-pass build (no count pass; row offsets by look-back), 2: its estimated edge
                               * arena was too small and the fill pass rewrote every row, 0: count + fill */
     int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
-    int32_t pipeline_parts;  /* > 0: pipelined plan, fill of part k + count of part k+1 per kernel, this many parts */
-    int32_t pipeline_refill; /* pipelined plan: 1 = a fill pass completed rows beyond the estimated row buffer,
-                              * 2 = the estimated arena was too small and the fill pass rewrote every row */
-    int32_t speculative;     /* capped batches: 1 = speculative build (every row assumed to reach max_neighbors, so
-                              * row a starts at a * max_neighbors: one sweep + sort + emit kernel, no count pass) held,
-                              * 2 = a row came up short and the batch was rebuilt with counted offsets, 0 = not tried */
-    int32_t est_min_degree;  /* density estimate of the sparsest structure's degree (what the speculation goes by) */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 
@@ -214,10 +207,7 @@ void* dgnn_stream(dgnn_ctx* ctx);
  * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048);
  * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off);
  * onepass: single-pass build (no count pass) of batches without cell-list structures: -1 auto (small batches),
- * 0 off (count + fill), 1 wherever legal;
- * speculative: capped batches built with a priori offsets row a = a * max_neighbors (see dgnn_build_info.speculative):
- * 0 off (default: measured slower than the hit-list plan, it saves the hit lists' memory), -1 auto (large batches whose
- * sparsest structure's density estimate is >= 4 * max_neighbors + 32), 1 wherever legal. */
+ * 0 off (count + fill), 1 wherever legal. */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus

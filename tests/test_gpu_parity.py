@@ -394,57 +394,8 @@ def test_offset_sinks_receive_row_ptr_during_the_build(pkg, oracle, syn, onepass
     gb.close()
 
 
-def test_speculative_capped_build(pkg, oracle, syn):
-    """Capped batches whose sparsest structure still promises far more candidates than max_neighbors are built
-    speculatively (row a at a * cap, one kernel, no count pass); a row that comes up short -- a sparse cell, an empty
-    structure in between is fine -- makes the build fall back to counted offsets.  Both outcomes equal the oracle, ties
-    at the truncation included."""
-    import torch
-    if not torch.cuda.is_available():
-        pytest.skip("no CUDA device")
-    gb = pkg.GraphBuilder(0)
-    gb.set_option("speculative", 1)          # also on batches small enough for the single-pass plan
-    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
-    dense = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=71)[:4], none, syn.perovskite_supercell(3, 3, 3, seed=72)[:4],
-                        syn.triclinic_cell(73)[:4], syn.perovskite_supercell(2, 2, 2, seed=74, jitter=0.0)[:4]])
-    for rc, cap, dr in ((10.0, 20, 0.1), (8.0, 12, 0.2), (6.0, 1, 0.25), (8.0, 20, None)):
-        check_batch(gb, oracle, dense, rc, cap, dr=dr)
-        info = gb.info()
-        assert info.speculative == 1 and info.onepass == 0 and info.hit_cap == 0, (rc, cap)
-        assert info.est_min_degree >= 2 * cap
-    # ideal simple cubic lattice: the truncation cuts through a shell of equal distances (tie statistic)
-    sc = syn.simple_cubic(2.0, 4)
-    h = check_batch(gb, oracle, sc, 6.5, 20, dr=0.1, algo=oracle.ALGO_BRUTE, rbf_rc=8.0)
-    assert gb.info().speculative == 1 and h.n_tie_rows > 0
-    # a sparse structure among dense ones: 2 atoms in a 14 A box see 2 * 2 candidates at most within 8 A
-    lone = (np.array([1.0, 3.5]), np.array([1.0, 2.0]), np.array([1.0, 2.5]), np.diag([14.0, 14.0, 14.0]))
-    mixed = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=75)[:4], lone, syn.perovskite_supercell(3, 3, 3, seed=76)[:4]])
-    check_batch(gb, oracle, mixed, 8.0, 12, dr=0.2)
-    info = gb.info()
-    assert info.speculative == 2, "forced speculation must fail on the sparse structure and be rebuilt"
-    # auto policy: the sparse structure's density estimate vetoes the speculation up front
-    gb.set_option("speculative", -1)
-    check_batch(gb, oracle, mixed, 8.0, 12, dr=0.2)
-    assert gb.info().speculative == 0 and gb.info().est_min_degree < 4 * 12 + 32
-    # ... uncapped calls never speculate
-    check_batch(gb, oracle, dense, 8.0, None, dr=0.2)
-    assert gb.info().speculative == 0
-    # a large capped batch takes it by itself, and equals the counted build bit for bit
-    big = syn.c2_batch(40, seed0=31000)
-    gb.set_option("onepass", 0)
-    h1 = build_and_fetch(gb, big, 10.0, 20, 10.0, 0.1)
-    assert gb.info().speculative == 1
-    gb.set_option("speculative", 0)
-    h0 = build_and_fetch(gb, big, 10.0, 20, 10.0, 0.1)
-    assert gb.info().speculative == 0
-    for f in ("row_ptr", "dst", "image", "dist", "rbf", "struct_edge_offsets"):
-        assert np.array_equal(getattr(h1, f), getattr(h0, f)), f
-    assert h1.n_near_cutoff == h0.n_near_cutoff and h1.n_tie_rows == h0.n_tie_rows and h1.max_degree == h0.max_degree
-    gb.close()
-
-
-@pytest.mark.parametrize("opts", [{"onepass": 0}, {"onepass": 1}, {"onepass": 0, "hit_cap": 0}, {"speculative": 1}],
-                         ids=["hit-lists", "single-pass", "traversal-fill", "speculative"])
+@pytest.mark.parametrize("opts", [{"onepass": 0}, {"onepass": 1}, {"onepass": 0, "hit_cap": 0}],
+                         ids=["hit-lists", "single-pass", "traversal-fill"])
 def test_truncated_rows_topk_prefilter(pkg, oracle, syn, opts):
     """Capped rows are not sorted in full: a d2 threshold keeps a little more than max_neighbors + 1 candidates, which
     are compacted and sorted.  Caps from 1 to most of the row, jittered and ideal lattices (whole shells of equal
@@ -490,54 +441,19 @@ def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
     shift = 7.0 * L[0] - 5.0 * L[1] + 1000.0 * L[2]
     far = (x + shift[0], y + shift[1], z + shift[2], L)
     check_batch(gb, oracle, syn.concat([(x2, y2, z2, L), far]), 6.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+    # lattice shells EXACTLY at r_c with unwrapped coordinates around 1e3 A (the mirror-band logic of the symmetric count
+    # and any reduced-precision pre-filter must leave these to the fp64 reference arithmetic)
+    b3 = syn.simple_cubic(2.0, 3)
+    for sh in ((1024.0, -2048.0, 512.0), (1000.0, 3000.0, -1500.0)):
+        moved = (b3.x + sh[0], b3.y + sh[1], b3.z + sh[2], b3.lattices[0].reshape(3, 3))
+        for rc in (4.0, 2.0 * np.sqrt(2.0), 6.0, np.nextafter(6.0, 7.0)):
+            check_batch(gb, oracle, syn.concat([moved]), rc, None, algo=oracle.ALGO_BRUTE)
+    rng = np.random.default_rng(3)
+    x, y, z, L = syn.perovskite_supercell(3, 3, 2, seed=8)[:4]
+    for _ in range(3):
+        n = rng.integers(-60, 60, size=3).astype(np.float64)
+        sh = n @ L
+        check_batch(gb, oracle, syn.concat([(x + sh[0], y + sh[1], z + sh[2], L)]), 8.0, None, dr=0.2)
     gb.close()
 
 
-@pytest.mark.parametrize("opts,refill", [
-    ({"upload_chunks": 2}, 0),
-    ({"upload_chunks": 5}, 0),
-    ({"upload_chunks": 4, "onepass_row_cap": 64}, 1),          # rows beyond the estimated row buffer -> fill pass
-    ({"upload_chunks": 3, "onepass_arena_scale": 0.25}, 2),    # estimated arena too small -> everything refilled
-    ({"upload_chunks": 4, "rbf_recur": 0}, 0),
-])
-@pytest.mark.parametrize("device_inputs", [False, True])
-def test_pipelined_plan_fill_and_count_share_a_kernel(pkg, oracle, syn, opts, refill, device_inputs):
-    """Large direct-path batches: fill of part k + symmetric count of part k+1 in one kernel, offsets chained on the
-    device, arena / row buffer from the density estimate with both recovery routes."""
-    import torch
-    if not torch.cuda.is_available():
-        pytest.skip("no CUDA device")
-    gb = pkg.GraphBuilder(0)
-    gb.set_option("upload_min_atoms", 0)
-    gb.set_option("onepass", 0)
-    gb.set_option("pipeline", 1)          # off by default (measured slower than the passes back to back)
-    for k, v in opts.items():
-        gb.set_option(k, v)
-    none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
-    parts = [syn.perovskite_supercell(4, 4, 2, seed=61)[:4], none, syn.triclinic_cell(41)[:4],
-             syn.perovskite_supercell(3, 3, 3, seed=62)[:4], syn.perovskite_supercell(4, 4, 2, seed=63)[:4],
-             syn.triclinic_cell(43)[:4], none, syn.perovskite_supercell(4, 4, 4, seed=64)[:4],
-             syn.perovskite_supercell(2, 2, 2, seed=65)[:4], syn.perovskite_supercell(4, 4, 2, seed=66)[:4]]
-    b = syn.concat(parts)
-    if device_inputs:
-        dev = torch.device("cuda:0")
-        t = [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
-        torch.cuda.synchronize()
-        g = gb.build(*t, r_cutoff=8.0, max_neighbors=oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2, device_inputs=True)
-        h = gb.to_host(g)
-        info = gb.info()
-        e0 = 0
-        for s in range(b.n_structs):
-            o = oracle.neighbor_list(*b.structure(s), 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
-            e0 = assert_graph_equal(h, e0, int(b.atom_offsets[s]), int(b.atom_offsets[s + 1]), o, what=f"structure {s}")
-        assert e0 == h.n_edges
-    else:
-        check_batch(gb, oracle, b, 8.0, None, dr=0.2)
-        info = gb.info()
-    assert info.pipeline_parts == opts["upload_chunks"] and info.onepass == 0
-    assert info.pipeline_refill == refill
-    if not device_inputs:
-        check_batch(gb, oracle, b, 10.0, None, dr=0.1)        # K = 100, longer rows
-        check_batch(gb, oracle, b, 8.0, None, dr=0.3)         # K = 26: separate RBF launch
-        check_batch(gb, oracle, b, 8.0, None)                 # no features (still no hit lists: bytes/pair < 64 -> hits)
-    gb.close()

@@ -36,7 +36,7 @@ def run(gb, torch, name, b, rc, cap, dr, reps, peak):
             "whole_path_gbs": bytes_all / (ms * 1e-3) / 1e9, "frac_of_measured_peak": bytes_all / (ms * 1e-3) / 1e9 / peak,
             "phases_ms": {k: statistics.median(getattr(i, k) for i in infos)
                           for k in ("bin_ms", "count_ms", "fill_ms", "rbf_ms")},
-            "launches": infos[-1].kernel_launches, "onepass": infos[-1].onepass, "speculative": infos[-1].speculative, "est_min_degree": infos[-1].est_min_degree, "onepass_fallback_rows": infos[-1].onepass_fallback_rows, "hit_cap": infos[-1].hit_cap, "cell_list_structs": infos[-1].n_cell_structs,
+            "launches": infos[-1].kernel_launches, "onepass": infos[-1].onepass, "onepass_fallback_rows": infos[-1].onepass_fallback_rows, "hit_cap": infos[-1].hit_cap, "cell_list_structs": infos[-1].n_cell_structs,
             "max_degree": int(g.max_degree), "near_cutoff_pairs": int(g.n_near_cutoff), "tie_rows": int(g.n_tie_rows)}
     print(json.dumps(line), flush=True)
     del t

@@ -15,6 +15,6 @@ for l in open("$out/${tag}_cfg.jsonl"):
     d=json.loads(l)
     if 'device_ms' in d: print(d['config'][:60],'ms',round(d['device_ms'],3),'GB/s',round(d['achieved_gbs'],1))
     elif 'ms_per_call' in d: print(d['config'][:50],'onepass',d['onepass'],'ms/call',round(d['ms_per_call'],3))
-    else: print(d['config'][:50],'ms',round(d['ms_per_build'],3),{k:round(v,3) for k,v in d['phases_ms'].items()},'onepass',d.get('onepass'),'spec',d.get('speculative'),'hit',d.get('hit_cap'))
+    else: print(d['config'][:50],'ms',round(d['ms_per_build'],3),{k:round(v,3) for k,v in d['phases_ms'].items()},'onepass',d.get('onepass'),'hit',d.get('hit_cap'))
 PY
 tail -n 3 $out/${tag}_bench.err; tail -n 3 $out/${tag}_cfg.err; true
