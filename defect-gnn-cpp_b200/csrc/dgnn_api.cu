@@ -66,6 +66,9 @@ struct dgnn_ctx {
     int64_t* sink_seo = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
     int fill_hits_bulk = 1;               // k_fill_hits feature stores: bulk-copy engine (1) or st.global.cs (0)
+    int cell32 = 1;                       // cell-list structures: fp32 tiles staged in shared memory + fp64 decision in the
+                                          // guard band (dgnn_cell32.cu); 0: the fp64 traversal with hit lists (A/B reference)
+    int cell32_fill_warps = 16;
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
@@ -330,6 +333,12 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->upload_chunks = (int)value;
     } else if (!strcmp(name, "fill_hits_bulk")) {
         ctx->fill_hits_bulk = value != 0.0;
+    } else if (!strcmp(name, "cell32_fill_warps")) {
+        if (!(value == 8 || value == 16 || value == 20 || value == 24))
+            return fail(ctx, DGNN_ERR_INVALID_ARG, "cell32_fill_warps must be 8, 16, 20 or 24");
+        ctx->cell32_fill_warps = (int)value;
+    } else if (!strcmp(name, "cell32")) {
+        ctx->cell32 = value != 0.0;
     } else if (!strcmp(name, "sym_count")) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
@@ -514,7 +523,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         // (small direct-path batches take the single-pass build instead, see below)
         const bool onepass_likely = ctx->onepass_opt > 0 ||
                                     (ctx->onepass_opt < 0 && N <= (long long)ctx->sm_count * 2 * 8 * 2);
-        if (est > 0 && (ctx->h_stats->n_cell_structs > 0 || (bytes_per_pair < 64.0 && !onepass_likely)))
+        // (the fp32-tile traversal of cell-list structures needs no lists; only the fp64 one, option cell32 = 0, does)
+        if (est > 0 && ((ctx->h_stats->n_cell_structs > 0 && !ctx->cell32) || (bytes_per_pair < 64.0 && !onepass_likely)))
             hit_cap = round_up((int)(est + est / 4 + 16 < DGNN_MAX_DEGREE ? est + est / 4 + 16 : DGNN_MAX_DEGREE), 32);
     }
     if (hit_cap > 512) hit_cap = 512;  // the hit-list fill pass sorts in registers: rows of up to 512 entries
@@ -631,7 +641,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             onepass = true;
         }
     }
-    if (!onepass) {
+    // (a batch of cell-list structures only -- config 4 -- has no rows for the direct kernels: they are not launched)
+    const bool any_direct = !have_est || ctx->h_stats->n_direct_structs > 0;
+    if (!onepass && any_direct) {
         // per upload chunk (structure-aligned): fractional coordinates, then the count pass of its rows -- the next
         // chunk's coordinates cross PCIe meanwhile
         // without hit lists the count pass is symmetric: one sweep decides i -> j and j -> i (dgnn_direct.cu)
@@ -655,6 +667,13 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             D.row_begin = D.row_end = 0;
             dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
         }
+    } else if (!onepass) {
+        // the cell-list kernels still need the uploaded coordinates, and empty batches a valid (all zero) row_ptr
+        for (int c = 0; c < n_up; ++c)
+            if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
+        CU(cudaMemsetAsync(ctx->deg.p, 0, (size_t)(N + 1) * 4, st));
+        CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
+        dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
     }
     dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
     CU(cudaGetLastError());
@@ -675,6 +694,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     memset(&A, 0, sizeof(A));
     long long n_items = 0, P = 0;
     int grid = 1;
+    bool cell32 = false;
+    int tile_cap_report = 0;
     if (n_cell_structs > 0) {
         ENSURE(ctx->geoms, (size_t)(S + 1) * sizeof(DgGeom));
         ENSURE(ctx->acell, (size_t)(N + 1) * 12);
@@ -774,9 +795,30 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         grid = (int)((long long)ctx->sm_count * ctx->traverse_grid_mult < n_items
                          ? (long long)ctx->sm_count * ctx->traverse_grid_mult
                          : (n_items > 0 ? n_items : 1));
-        if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)
-            return fail(ctx, DGNN_ERR_UNSUPPORTED, "count-pass shared memory plan does not fit");
-        CU(dg_launch_traverse(st, A, false, grid));
+        // fp32-tile traversal: the whole tile of every item must fit (float4 per point, 16-bit slots)
+        {
+            DgTraverseArgs C = A;
+            C.tile_cap = round_up(ctx->h_stats->max_tile_pts > 32 ? ctx->h_stats->max_tile_pts : 32, 32);
+            C.row_cap = 0;
+            C.src_cap = 1024;  // (fp32-tile traversal: slot list entries per warp)
+            cell32 = ctx->cell32 && C.tile_cap <= 65504 && ctx->h_stats->max_tile_tcs <= 4096 &&
+                     (int)dg_cell32_smem_bytes(C, false) <= ctx->smem_optin;
+            if (cell32) {
+                A.tile_cap = C.tile_cap;
+                A.src_cap = 1024;
+                A.hits = nullptr;
+                A.hits_d2 = nullptr;
+                A.hit_cap = 0;
+            }
+        }
+        tile_cap_report = A.tile_cap;
+        if (cell32) {
+            CU(dg_launch_cell32(st, A, false, grid));
+        } else {
+            if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)
+                return fail(ctx, DGNN_ERR_UNSUPPORTED, "count-pass shared memory plan does not fit");
+            CU(dg_launch_traverse(st, A, false, grid));
+        }
         dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
         dg_launch_finish_rows(st, N, S, d_off, (const long long*)ctx->row_ptr.p, (long long*)ctx->seo.p, d_stats);
         CU(cudaGetLastError());
@@ -832,7 +874,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // rows with a stored hit list are filled from it; the traversal fill pass takes whatever is left
     DgDirectArgs H = D;
     H.fill_hits_bulk = ctx->fill_hits_bulk;
-    if (n_cell_structs > 0) {
+    if (n_cell_structs > 0 && !cell32) {
         H.cloud_j = (const int*)ctx->cj.p;
         H.cloud_n = (const uint32_t*)ctx->cn.p;
     }
@@ -853,11 +895,40 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         if ((int)dg_fill_hits_smem_bytes(H) > ctx->smem_optin) use_hits = false;
     }
     if (!use_hits) D.hit_cap = 0;
-    if (E > 0 && use_hits) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
-    if (E > 0 && !onepass && (!use_hits || n_fallback_rows > 0))
+    if (E > 0 && use_hits && (any_direct || (n_cell_structs > 0 && !cell32))) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
+    if (E > 0 && !onepass && any_direct && (!use_hits || n_fallback_rows > 0))
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
-    if (n_cell_structs > 0 && E > 0 && (!use_hits || n_fallback_rows > 0)) {
-        A.hit_cap = use_hits ? hit_cap : 0;
+    bool cell32_rest = false;  // rows the fp32-tile fill left to the fp64 traversal (degree beyond the register sort)
+    if (cell32 && E > 0) {
+        A.row_ptr = (const long long*)ctx->row_ptr.p;
+        A.dst = (int*)ctx->dst.p;
+        A.image = (uint32_t*)ctx->image.p;
+        A.dist = (double*)ctx->dist.p;
+        A.row_cap = row_cap < 512 ? row_cap : 512;
+        A.n_warps = ctx->cell32_fill_warps;  // the tile is staged in fp32 and in fp64: one CTA per SM shares it
+        if (A.row_cap > 256 && A.n_warps > 16) A.n_warps = 16;  // (the 512-entry sort network needs 128 registers)
+        A.rbf = D.rbf;
+        // shared memory: first the slot list shrinks (cells whose stencil outgrows it take the range-by-range sweep),
+        // then warps go
+        if ((int)dg_cell32_smem_bytes(A, true) > ctx->smem_optin) A.src_cap = 768;
+        while (A.n_warps > 8 && (int)dg_cell32_smem_bytes(A, true) > ctx->smem_optin) A.n_warps = A.n_warps > 16 ? A.n_warps - 4 : A.n_warps / 2;
+        if ((int)dg_cell32_smem_bytes(A, true) <= ctx->smem_optin) {
+            const int fgrid = (int)((long long)ctx->sm_count * 4 < n_items ? (long long)ctx->sm_count * 4 : n_items);
+            CU(dg_launch_cell32(st, A, true, fgrid));
+            A.n_warps = 8;
+            A.src_cap = 1024;
+            cell32_rest = max_deg > 512;
+        } else {
+            cell32_rest = true;
+            A.row_cap = 0;  // (nothing written: the fp64 traversal takes every row)
+        }
+    }
+    if (n_cell_structs > 0 && E > 0 && (cell32 ? cell32_rest : (!use_hits || n_fallback_rows > 0))) {
+        A.hit_cap = cell32 ? A.row_cap : (use_hits ? hit_cap : 0);
+        if (cell32) {
+            A.tile_cap = 0;
+            A.tcs_cap = 4;
+        }
         A.row_ptr = (const long long*)ctx->row_ptr.p;
         A.dst = (int*)ctx->dst.p;
         A.image = (uint32_t*)ctx->image.p;
@@ -926,7 +997,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.kernel_launches = dg_num_kernel_launches_reset() + dg_rbf_launch_count_reset() + dg_direct_launch_count_reset();
     I.n_items = (int32_t)n_items;
     I.cloud_points = P;
-    I.staged_tile_cap = A.tile_cap;
+    I.staged_tile_cap = tile_cap_report;
     I.row_cap = row_cap;
     I.n_cell_structs = n_cell_structs;
     I.direct_warps = D.n_warps;

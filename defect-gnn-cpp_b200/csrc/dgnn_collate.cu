@@ -17,7 +17,7 @@
 
 #include "dgnn_internal.h"
 
-static int g_collate_launches = 0;
+static thread_local int g_collate_launches = 0;
 int dg_collate_launch_count_reset() {
     int v = g_collate_launches;
     g_collate_launches = 0;

@@ -55,6 +55,7 @@ __global__ void __launch_bounds__(128) k_small_geom(long long S, const long long
         if (atomicCAS(&stats->err_status, 0, G.status) == 0) stats->err_struct = (int)s;
     } else if (G.natoms > 0) {
         if (G.mode == DG_MODE_CELL) atomicAdd(&stats->n_cell_structs, 1);
+        else atomicAdd(&stats->n_direct_structs, 1);
         // density estimate of the degree: N * (4/3) pi r^3 / V, V = h_0 h_1 h_2 / (the sines) >= rcm^3 / (w0 w1 w2)
         const double rcm = DG_RCM(r_cutoff);
         const double det = fabs(L[0] * (L[4] * L[8] - L[5] * L[7]) + L[1] * (L[5] * L[6] - L[3] * L[8]) +

@@ -21,6 +21,7 @@ struct DgStats {
     int err_struct;              // and the structure it was seen on
     int overflow;                // a row did not fit the row buffer (must not happen)
     int n_cell_structs;          // non-empty structures routed to the cell-list path
+    int n_direct_structs;        // ... and to the direct path
     int n_fallback_rows;         // direct-path rows whose hit list was not stored (degree > hit_cap or image range > 15)
     int est_deg;                 // density estimate of the largest degree (sizes the hit lists of a ctx's first build)
     int cap_overflow;            // single-pass build: a row did not fit the (estimated) edge arena -> rerun as two passes
@@ -105,6 +106,9 @@ void dg_launch_cloud_scatter(cudaStream_t st, long long N, const DgGeom* geoms, 
                              const int* acell, const double* x, const double* y, const double* z,
                              const long long* cellstart, int* cellcount, double* cx, double* cy, double* cz,
                              int* cj, uint32_t* cn);
+// fp32-tile traversal (dgnn_cell32.cu): rows of up to 512 entries; the fp64 traversal keeps the rest and oversize tiles
+size_t dg_cell32_smem_bytes(const DgTraverseArgs& a, bool fill);
+cudaError_t dg_launch_cell32(cudaStream_t st, const DgTraverseArgs& a, bool fill, int grid);
 size_t dg_traverse_smem_bytes(const DgTraverseArgs& a, bool fill);
 cudaError_t dg_launch_traverse(cudaStream_t st, const DgTraverseArgs& a, bool fill, int grid);
 void dg_launch_finish_rows(cudaStream_t st, long long N, long long S, const long long* atom_offsets,

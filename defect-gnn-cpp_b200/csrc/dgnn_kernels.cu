@@ -14,14 +14,16 @@
 
 #include "dgnn_internal.h"
 #include "row_sort.cuh"
+#include "cell_items.cuh"
 
-static int g_launches = 0;
+static thread_local int g_launches = 0;  // per calling thread: a build runs wholly on one thread
 int dg_num_kernel_launches_reset() {
     int v = g_launches;
     g_launches = 0;
     return v;
 }
 #define DG_COUNT_LAUNCH() (++g_launches)
+void dg_kernel_launch_bump(int n) { g_launches += n; }
 
 #ifndef FULL_MASK
 #define FULL_MASK 0xffffffffu
@@ -293,26 +295,28 @@ __device__ __forceinline__ long long halo_cell_id(const DgGeom* G, int X0, int X
 __global__ void __launch_bounds__(256) k_cloud_count(long long N, const DgGeom* __restrict__ geoms,
                                                      const int* __restrict__ astruct, const int* __restrict__ acell,
                                                      int* __restrict__ cellcount) {
-    const long long a = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+    // one THREAD per atom: in a large cell almost every atom contributes exactly one cloud point (itself); the few
+    // images of boundary atoms -- or the ~100 of an atom in a tiny cell -- are a short serial loop
+    const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (a >= N) return;
     const DgGeom* G = geoms + astruct[a];
     if (G->status != DG_ST_OK) return;
     const int c[3] = {acell[3 * a], acell[3 * a + 1], acell[3 * a + 2]};
     const ImageBox b = image_box(G, c);
-    for (int t = lane; t < b.total; t += 32) {
-        const int ic = t % b.cnt[2], ib = (t / b.cnt[2]) % b.cnt[1], ia = t / (b.cnt[2] * b.cnt[1]);
-        const int X0 = c[0] + (b.nlo[0] + ia) * G->g[0];
-        const int X1 = c[1] + (b.nlo[1] + ib) * G->g[1];
-        const int X2 = c[2] + (b.nlo[2] + ic) * G->g[2];
-        atomicAdd(&cellcount[halo_cell_id(G, X0, X1, X2)], 1);
-    }
+    for (int ia = 0; ia < b.cnt[0]; ++ia)
+        for (int ib = 0; ib < b.cnt[1]; ++ib)
+            for (int ic = 0; ic < b.cnt[2]; ++ic) {
+                const int X0 = c[0] + (b.nlo[0] + ia) * G->g[0];
+                const int X1 = c[1] + (b.nlo[1] + ib) * G->g[1];
+                const int X2 = c[2] + (b.nlo[2] + ic) * G->g[2];
+                atomicAdd(&cellcount[halo_cell_id(G, X0, X1, X2)], 1);
+            }
 }
 
 void dg_launch_cloud_count(cudaStream_t st, long long N, const DgGeom* geoms, const int* astruct,
                            const int* acell, int* cellcount) {
     if (N <= 0) return;
-    k_cloud_count<<<(unsigned)((N * 32 + 255) / 256), 256, 0, st>>>(N, geoms, astruct, acell, cellcount);
+    k_cloud_count<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, geoms, astruct, acell, cellcount);
     DG_COUNT_LAUNCH();
 }
 
@@ -324,8 +328,7 @@ __global__ void __launch_bounds__(256) k_cloud_scatter(long long N, const DgGeom
                                                        int* __restrict__ cellcount, double* __restrict__ cx,
                                                        double* __restrict__ cy, double* __restrict__ cz,
                                                        int* __restrict__ cj, uint32_t* __restrict__ cn) {
-    const long long a = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const int lane = threadIdx.x & 31;
+    const long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // one thread per atom (see k_cloud_count)
     if (a >= N) return;
     const DgGeom* G = geoms + astruct[a];
     if (G->status != DG_ST_OK) return;
@@ -333,19 +336,20 @@ __global__ void __launch_bounds__(256) k_cloud_scatter(long long N, const DgGeom
     const ImageBox b = image_box(G, c);
     const double px = x[a], py = y[a], pz = z[a];
     const int jloc = (int)(a - G->atom_base);
-    for (int t = lane; t < b.total; t += 32) {
-        const int ic = t % b.cnt[2], ib = (t / b.cnt[2]) % b.cnt[1], ia = t / (b.cnt[2] * b.cnt[1]);
-        const int na = b.nlo[0] + ia, nb = b.nlo[1] + ib, nc = b.nlo[2] + ic;
-        const long long cid = halo_cell_id(G, c[0] + na * G->g[0], c[1] + nb * G->g[1], c[2] + nc * G->g[2]);
-        const int slot = atomicSub(&cellcount[cid], 1) - 1;  // counts down to zero: cell fill order is free
-        const long long p = cellstart[cid] + slot;
-        // reference cloud point: position + offset, offset = (n_a*row0 + n_b*row1) + n_c*row2
-        cx[p] = DG_ADD(px, dg_image_offset(G->L, 0, na, nb, nc));
-        cy[p] = DG_ADD(py, dg_image_offset(G->L, 1, na, nb, nc));
-        cz[p] = DG_ADD(pz, dg_image_offset(G->L, 2, na, nb, nc));
-        cj[p] = jloc;
-        cn[p] = dg_pack_image(na, nb, nc);
-    }
+    for (int ia = 0; ia < b.cnt[0]; ++ia)
+        for (int ib = 0; ib < b.cnt[1]; ++ib)
+            for (int ic = 0; ic < b.cnt[2]; ++ic) {
+                const int na = b.nlo[0] + ia, nb = b.nlo[1] + ib, nc = b.nlo[2] + ic;
+                const long long cid = halo_cell_id(G, c[0] + na * G->g[0], c[1] + nb * G->g[1], c[2] + nc * G->g[2]);
+                const int slot = atomicSub(&cellcount[cid], 1) - 1;  // counts down to zero: cell fill order is free
+                const long long p = cellstart[cid] + slot;
+                // reference cloud point: position + offset, offset = (n_a*row0 + n_b*row1) + n_c*row2
+                cx[p] = DG_ADD(px, dg_image_offset(G->L, 0, na, nb, nc));
+                cy[p] = DG_ADD(py, dg_image_offset(G->L, 1, na, nb, nc));
+                cz[p] = DG_ADD(pz, dg_image_offset(G->L, 2, na, nb, nc));
+                cj[p] = jloc;
+                cn[p] = dg_pack_image(na, nb, nc);
+            }
 }
 
 void dg_launch_cloud_scatter(cudaStream_t st, long long N, const DgGeom* geoms, const int* astruct,
@@ -353,7 +357,7 @@ void dg_launch_cloud_scatter(cudaStream_t st, long long N, const DgGeom* geoms, 
                              const long long* cellstart, int* cellcount, double* cx, double* cy, double* cz,
                              int* cj, uint32_t* cn) {
     if (N <= 0) return;
-    k_cloud_scatter<<<(unsigned)((N * 32 + 255) / 256), 256, 0, st>>>(N, geoms, astruct, acell, x, y, z, cellstart,
+    k_cloud_scatter<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, geoms, astruct, acell, x, y, z, cellstart,
                                                                        cellcount, cx, cy, cz, cj, cn);
     DG_COUNT_LAUNCH();
 }
@@ -361,37 +365,7 @@ void dg_launch_cloud_scatter(cudaStream_t st, long long N, const DgGeom* geoms, 
 // ---------------------------------------------------------------------------------------------------------------------
 // work items: (structure, source-cell block).  Shared decode used by the stats kernel and the traversal.
 // ---------------------------------------------------------------------------------------------------------------------
-struct ItemBox {
-    int c0[3], c1[3];  // source cell box, halo-local coordinates [c0, c1)
-    int t0[3], td[3];  // tile box origin (halo-local) and dims
-};
-
-__device__ __forceinline__ long long find_struct(const long long* __restrict__ item_base, long long S,
-                                                 long long item) {
-    long long lo = 0, hi = S;
-    while (hi - lo > 1) {
-        const long long mid = (lo + hi) >> 1;
-        if (item_base[mid] <= item) lo = mid; else hi = mid;
-    }
-    return lo;
-}
-
-__device__ __forceinline__ ItemBox item_box(const DgGeom* G, int local) {
-    ItemBox B;
-    const int b2 = local % G->nb[2], b1 = (local / G->nb[2]) % G->nb[1], b0 = local / (G->nb[2] * G->nb[1]);
-    const int bb[3] = {b0, b1, b2};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        const int D = G->hd[k] - 2 * G->R[k];
-        B.c0[k] = G->R[k] + bb[k] * G->bd[k];
-        const int e = B.c0[k] + G->bd[k];
-        B.c1[k] = e < G->R[k] + D ? e : G->R[k] + D;
-        B.t0[k] = B.c0[k] - G->R[k];
-        B.td[k] = (B.c1[k] - B.c0[k]) + 2 * G->R[k];
-    }
-    return B;
-}
-
+// (ItemBox / find_struct / item_box: cell_items.cuh)
 __global__ void k_item_stats(long long n_items, long long S, const DgGeom* __restrict__ geoms,
                              const long long* __restrict__ item_base, const long long* __restrict__ cellstart,
                              long long n_cells, DgStats* __restrict__ stats) {

@@ -16,7 +16,7 @@
 #include "dgnn_internal.h"
 #include "rbf_math.cuh"
 
-static int g_rbf_launches = 0;
+static thread_local int g_rbf_launches = 0;
 int dg_rbf_launch_count_reset() {
     int v = g_rbf_launches;
     g_rbf_launches = 0;

@@ -646,27 +646,37 @@ __device__ __forceinline__ int dg_row_prefilter_t(double* __restrict__ rd, const
     }
     return base;
 }
-template <class Payload>
+template <class Payload, int MAXEPL = 16>
 __device__ __forceinline__ int dg_row_prefilter(double* rd, const Payload& P, int m, int keep, double key_scale,
                                                 int lane) {
     if (keep >= m || m <= 128 || 3 * (keep + 1) + 48 > m) return m;
     const float rc = (float)((4294967296.0 - 4096.0) / key_scale);  // key_scale = (2^32 - 4096) / r_c
     const float r2 = rc * rc;
-    if (m <= 256) return dg_row_prefilter_t<8>(rd, P, m, keep, r2, lane);
+    if (MAXEPL <= 8 || m <= 256) return dg_row_prefilter_t<8>(rd, P, m, keep, r2, lane);
     return dg_row_prefilter_t<16>(rd, P, m, keep, r2, lane);
 }
 
-template <class Payload, class OP, bool LEAN = false>
+// MAXEPL: largest network compiled in (rows of up to 32 * MAXEPL entries) -- a kernel that only ever sees rows of up to
+// 256 entries saves the registers of the 512-entry network
+template <class Payload, class OP, bool LEAN = false, int MAXEPL = 16>
 __device__ __forceinline__ long long dg_row_sort_bitonic_any_op(double* rd, uint32_t* sk, float* fd, int* tie,
                                                                 const Payload& P, int m, int keep, double key_scale,
                                                                 OP& op, int* dst, uint32_t* image, double* dist,
                                                                 DgStats* stats, int lane) {
-    if (!LEAN) m = dg_row_prefilter(rd, P, m, keep, key_scale, lane);
+    if (!LEAN) m = dg_row_prefilter<Payload, MAXEPL>(rd, P, m, keep, key_scale, lane);
     if (m <= 128)
         return dg_row_sort_bitonic<4, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
-    if (m <= 256)
+    if (MAXEPL <= 8 || m <= 256)
         return dg_row_sort_bitonic<8, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
     return dg_row_sort_bitonic<16, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+}
+template <int MAXEPL, class Payload>
+__device__ __forceinline__ void dg_row_sort_bitonic_upto(double* rd, uint32_t* sk, float* fd, int* tie, const Payload& P,
+                                                         int m, int keep, double key_scale, long long o, int* dst,
+                                                         uint32_t* image, double* dist, DgStats* stats, int lane) {
+    DgFixedOffset op{o};
+    dg_row_sort_bitonic_any_op<Payload, DgFixedOffset, false, MAXEPL>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image,
+                                                                      dist, stats, lane);
 }
 template <class Payload>
 __device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk, float* fd, int* tie, const Payload& P,

@@ -187,9 +187,14 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
     x, y, z, L, _ = syn.perovskite_supercell(9, 8, 7, seed=11)
     b = syn.concat([(x, y, z, L)])
     o = oracle.neighbor_list(x, y, z, L, 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
-    for opts in ({}, {"tile_limit": 4096}, {"tile_limit": 4096, "tile_target": 512, "src_target": 48},
-                 {"tile_limit": 4096, "hit_cap": 0}, {"hit_cap": 0}, {"hit_cap": 160}, {"tile_limit": 4096, "hit_cap": 160}, {"cell_frac": 0.3},
-                 {"cell_frac": 1.0}, {"direct_max_atoms": 4096}):
+    # default = fp32 tiles staged in shared memory (dgnn_cell32.cu); cell32 = 0 = the fp64 traversal (staged with
+    # tile_limit > 0, else straight from the L2-resident cloud), with and without hit lists
+    for opts in ({}, {"tile_target": 512, "src_target": 48}, {"tile_target": 4096, "src_target": 1024}, {"cell_frac": 0.3},
+                 {"cell_frac": 1.0}, {"cell_frac": 0.3, "tile_target": 256, "src_target": 16},
+                 {"cell32": 0}, {"cell32": 0, "tile_limit": 4096}, {"cell32": 0, "tile_limit": 4096, "tile_target": 512, "src_target": 48},
+                 {"cell32": 0, "tile_limit": 4096, "hit_cap": 0}, {"cell32": 0, "hit_cap": 0}, {"cell32": 0, "hit_cap": 160},
+                 {"cell32": 0, "tile_limit": 4096, "hit_cap": 160}, {"cell32": 0, "cell_frac": 0.3},
+                 {"cell32": 0, "cell_frac": 1.0}, {"direct_max_atoms": 4096}):
         gb = pkg.GraphBuilder(0)
         if "direct_max_atoms" not in opts:
             gb.set_option("direct_max_atoms", 0)
@@ -199,11 +204,12 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
         h = gb.to_host(g)
         assert_graph_equal(h, 0, 0, len(x), o, what=str(opts))
         info = gb.info()
-        if opts.get("tile_limit", 0) == 0:
-            assert info.staged_tile_cap == 0
-        else:
-            assert info.staged_tile_cap > 0
-        if "tile_target" in opts:
+        if "direct_max_atoms" not in opts:
+            if opts.get("cell32", 1) == 0 and opts.get("tile_limit", 0) == 0:
+                assert info.staged_tile_cap == 0
+            else:
+                assert info.staged_tile_cap > 0
+        if opts.get("tile_target", 4096) <= 512:
             assert info.n_items > 20
         assert info.n_cell_structs == (0 if "direct_max_atoms" in opts else 1)
         gb.close()
