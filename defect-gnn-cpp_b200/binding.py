@@ -26,7 +26,7 @@ EXPORTS = [
     "dgnn_copy_to_host", "dgnn_copy_edges_to_host", "dgnn_rbf_expand", "dgnn_rbf_expand_f64",
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
-    "dgnn_last_consumer_info", "dgnn_set_offset_sinks",
+    "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host",
 ]
 
 
@@ -88,6 +88,21 @@ class DgnnConsumerInfo(C.Structure):
                 ("bytes_written", C.c_int64)]
 
 
+class DgnnDistanceTables(C.Structure):
+    _fields_ = [("n_atoms", C.c_int64), ("n_values", C.c_int64), ("values", C.c_void_p), ("table_ptr", C.c_void_p),
+                ("mode", C.c_int32)]
+
+
+class DgnnStreamInfo(C.Structure):
+    _fields_ = [("n_chunks", C.c_int64), ("n_structs", C.c_int64), ("n_atoms", C.c_int64), ("n_edges", C.c_int64),
+                ("wall_ms", C.c_double), ("build_device_ms", C.c_double), ("h2d_ms", C.c_double),
+                ("sink_ms", C.c_double), ("kernel_launches", C.c_int64)]
+
+
+STREAM_SOURCE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnBatch))
+STREAM_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnGraphs))
+
+
 class DgnnError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"dgnn error {code}: {msg}")
@@ -146,6 +161,14 @@ def load_library():
         L.dgnn_set_offset_sinks.restype = C.c_int
         L.dgnn_last_consumer_info.argtypes = [C.c_void_p, C.POINTER(DgnnConsumerInfo)]
         L.dgnn_last_consumer_info.restype = C.c_int
+        L.dgnn_build_stream.argtypes = [C.c_void_p, STREAM_SOURCE, C.c_void_p, STREAM_SINK, C.c_void_p,
+                                        C.POINTER(DgnnStreamInfo)]
+        L.dgnn_build_stream.restype = C.c_int
+        L.dgnn_distance_tables.argtypes = [C.c_void_p, C.POINTER(DgnnGraphs), C.c_int64, C.c_int64, C.c_int32,
+                                           C.POINTER(DgnnDistanceTables)]
+        L.dgnn_distance_tables.restype = C.c_int
+        L.dgnn_copy_distance_tables_to_host.argtypes = [C.c_void_p, C.POINTER(DgnnDistanceTables), C.c_void_p, C.c_void_p]
+        L.dgnn_copy_distance_tables_to_host.restype = C.c_int
         _lib = L
     return _lib
 
@@ -232,6 +255,52 @@ class GraphBuilder:
         self._check(self.lib.dgnn_build(self.h, C.byref(b), C.byref(g)))
         self.last = g
         return g
+
+    def build_stream(self, source, sink=None, r_cutoff=10.0, max_neighbors=20, epsilon=1e-10, rbf_r_cutoff=10.0,
+                     dr=0.1, device_inputs=False) -> DgnnStreamInfo:
+        """dgnn_build_stream: `source(c)` returns the chunk's (atom_offsets, x, y, z, lattices) -- numpy / pinned torch
+        (host) or device tensors -- or None when the job is finished; `sink(c, graphs)` sees the chunk's DgnnGraphs
+        (device pointers, valid until it returns).  Chunk c + 1 is uploaded and built while sink(c) runs."""
+        keep = {}
+        errs = []
+
+        def _src(_user, c, bp):
+            try:
+                t = source(int(c))
+                if t is None:
+                    return 0
+                off, x, y, z, lat = t
+                if isinstance(off, np.ndarray):
+                    off = np.ascontiguousarray(off, dtype=np.int64)
+                    x, y, z = (np.ascontiguousarray(a, dtype=np.float64) for a in (x, y, z))
+                    lat = np.ascontiguousarray(lat, dtype=np.float64)
+                keep[int(c) & 1] = (off, x, y, z, lat)  # alive until the chunk after next is asked for
+                b = bp.contents
+                b.n_structs = int(off.shape[0]) - 1
+                b.atom_offsets, b.x, b.y, b.z, b.lattice = _ptr(off), _ptr(x), _ptr(y), _ptr(z), _ptr(lat)
+                b.r_cutoff, b.max_neighbors, b.epsilon = float(r_cutoff), int(max_neighbors), float(epsilon)
+                b.rbf_r_cutoff, b.dr = float(rbf_r_cutoff), float(dr if dr is not None else 0.0)
+                b.flags = (INPUT_DEVICE if device_inputs else 0) | (SKIP_RBF if dr is None else 0)
+                return 1
+            except Exception as exc:  # noqa: BLE001 -- must not propagate through the C frames
+                errs.append(exc)
+                return -1
+
+        def _snk(_user, c, gp):
+            try:
+                if sink is not None:
+                    sink(int(c), gp.contents)
+                return 0
+            except Exception as exc:  # noqa: BLE001
+                errs.append(exc)
+                return 1
+
+        info = DgnnStreamInfo()
+        rc = self.lib.dgnn_build_stream(self.h, STREAM_SOURCE(_src), None, STREAM_SINK(_snk), None, C.byref(info))
+        if errs:
+            raise errs[0]
+        self._check(rc)
+        return info
 
     def set_offset_sinks(self, row_ptr=None, struct_edge_offsets=None):
         """dgnn_set_offset_sinks: host (pinned) int64 buffers that receive row_ptr / struct_edge_offsets of every
@@ -330,6 +399,20 @@ class GraphBuilder:
         cptr = np.empty(a1 - a0 + 1, dtype=np.int64)
         self._check(self.lib.dgnn_neighborhood_clouds(self.h, C.byref(g), int(a0), int(a1), _ptr(cloud), _ptr(cptr)))
         return cloud, cptr
+
+    def distance_tables(self, a0: int, a1: int, mode: int = 0, g: DgnnGraphs | None = None, to_host: bool = True):
+        """dgnn_distance_tables for the atoms [a0, a1): mode 0 = full (deg+1)^2 fp64 tables (column-major), mode 1 = the
+        compressed lower triangles in fp32 (Ripser's input).  Returns (values, table_ptr) as numpy arrays, or the
+        device-pointer record with to_host=False."""
+        g = g or self.last
+        t = DgnnDistanceTables()
+        self._check(self.lib.dgnn_distance_tables(self.h, C.byref(g), int(a0), int(a1), int(mode), C.byref(t)))
+        if not to_host:
+            return t
+        vals = np.empty(int(t.n_values), dtype=np.float64 if mode == 0 else np.float32)
+        tptr = np.empty(int(t.n_atoms) + 1, dtype=np.int64)
+        self._check(self.lib.dgnn_copy_distance_tables_to_host(self.h, C.byref(t), _ptr(vals), _ptr(tptr)))
+        return vals, tptr
 
     def consumer_info(self) -> DgnnConsumerInfo:
         i = DgnnConsumerInfo()

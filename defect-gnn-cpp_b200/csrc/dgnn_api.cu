@@ -8,6 +8,7 @@
 #include <cstring>
 #include <new>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/dgnn_cabi.h"
@@ -28,6 +29,8 @@ struct BuildEvents {
 
 struct dgnn_ctx {
     int device = 0;
+    std::vector<std::pair<std::string, double>> opt_log;  // options applied so far (replayed on the streaming twin)
+    dgnn_ctx* twin = nullptr;                              // second arena of dgnn_build_stream (created on first use)
     cudaStream_t stream = nullptr;
     int sm_count = 148;
     int smem_optin = 0;
@@ -77,11 +80,13 @@ struct dgnn_ctx {
     struct {
         bool valid = false;
         long long S = 0, N = 0, E = 0;
+        int max_deg = 0;
         const long long* off = nullptr;
         const double *x = nullptr, *y = nullptr, *z = nullptr;
     } last;
     DevBuf col_x, col_ei, col_batch, col_keys, col_lut, col_table, col_err;  // dgnn_collate outputs / staging
-    DevBuf view_a, view_b;                                                    // edge views / clouds staging
+    DevBuf view_a, view_b;
+    DevBuf tab_cnt, tab_ptr, tab_val;                                         // dgnn_distance_tables outputs / staging                                                    // edge views / clouds staging
     dgnn_consumer_info cinfo{};
     cudaEvent_t cev[2] = {nullptr, nullptr};
     int onepass_row_cap = 0;              // (testing) row buffer entries of the single-pass build, 0: density estimate
@@ -268,6 +273,10 @@ int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out) {
 
 void dgnn_destroy(dgnn_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->twin) {
+        dgnn_destroy(ctx->twin);
+        ctx->twin = nullptr;
+    }
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
@@ -275,7 +284,8 @@ void dgnn_destroy(dgnn_ctx* ctx) {
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
                       &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats, &ctx->col_x, &ctx->col_ei, &ctx->col_batch, &ctx->col_keys,
-                      &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b};
+                      &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b, &ctx->tab_cnt, &ctx->tab_ptr,
+                      &ctx->tab_val};
     for (DevBuf* b : bufs) release(*b);
     if (ctx->h_stats) cudaFreeHost(ctx->h_stats);
     for (auto& e : ctx->ev.e)
@@ -291,6 +301,21 @@ void dgnn_destroy(dgnn_ctx* ctx) {
 }
 
 void* dgnn_stream(dgnn_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+// (dgnn_stream.cu) second context on the same device with the same options: the other arena of the streamed build
+dgnn_ctx* dgnn_internal_twin(dgnn_ctx* ctx) {
+    if (!ctx) return nullptr;
+    if (!ctx->twin) {
+        dgnn_ctx* t = nullptr;
+        if (dgnn_create(ctx->device, 0, &t) != DGNN_OK) return nullptr;
+        for (const auto& kv : ctx->opt_log) dgnn_set_option(t, kv.first.c_str(), kv.second);
+        ctx->twin = t;
+    }
+    return ctx->twin;
+}
+void dgnn_internal_set_error(dgnn_ctx* ctx, const char* msg) {
+    if (ctx) ctx->err = msg ? msg : "";
+}
 
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     if (!ctx || !name) return DGNN_ERR_INVALID_ARG;
@@ -358,6 +383,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else {
         return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s'", name);
     }
+    ctx->opt_log.emplace_back(name, value);
+    if (ctx->twin) dgnn_set_option(ctx->twin, name, value);
     return DGNN_OK;
 }
 
@@ -984,6 +1011,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
 
     ctx->last.valid = true;
     ctx->last.S = S; ctx->last.N = N; ctx->last.E = E;
+    ctx->last.max_deg = max_deg;
     ctx->last.off = d_off;
     ctx->last.x = d_x; ctx->last.y = d_y; ctx->last.z = d_z;
 
@@ -1084,6 +1112,7 @@ int dgnn_rbf_expand_f64(dgnn_ctx* ctx, const double* dist, int64_t n, double r_c
                         int32_t* K_out) {
     return rbf_common(ctx, dist, n, r_cutoff, dr, out, K_out, true);
 }
+
 
 }  // extern "C"
 
@@ -1275,4 +1304,65 @@ int dgnn_neighborhood_clouds(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, in
     CU(cudaMemcpyAsync(cloud, ctx->view_a.p, (size_t)n_points * 24, cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(cloud_ptr, ctx->view_b.p, (size_t)(n + 1) * 8, cudaMemcpyDeviceToHost, st));
     return consumer_end(ctx, 8 * (n + 1) + 24 * n + 8 * (rp[1] - rp[0]), 24 * n_points + 8 * (n + 1));
+}
+
+int dgnn_distance_tables(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, int64_t a1, int32_t mode,
+                         dgnn_distance_tables_out* out) {
+    if (!ctx) return DGNN_ERR_INVALID_ARG;
+    {
+        int r = consumer_begin(ctx, g, "dgnn_distance_tables");
+        if (r != DGNN_OK) return r;
+    }
+    if (!out) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_distance_tables: null output");
+    memset(out, 0, sizeof(*out));
+    if (a0 < 0 || a1 < a0 || a1 > ctx->last.N) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_distance_tables: atom range out of bounds");
+    if (mode != 0 && mode != 1) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_distance_tables: mode must be 0 or 1");
+    cudaStream_t st = ctx->stream;
+    const long long n = a1 - a0;
+    out->mode = mode;
+    out->n_atoms = n;
+    ENSURE(ctx->tab_ptr, (size_t)(n + 2) * 8);
+    out->table_ptr = (const int64_t*)ctx->tab_ptr.p;
+    if (n == 0) {
+        CU(cudaMemsetAsync(ctx->tab_ptr.p, 0, 8, st));
+        CU(cudaStreamSynchronize(st));
+        return DGNN_OK;
+    }
+    const size_t smem = (size_t)(ctx->last.max_deg + 1) * 32;
+    if ((int)smem > ctx->smem_optin)
+        return fail(ctx, DGNN_ERR_DEGREE, "dgnn_distance_tables: a cloud of %d points does not fit in shared memory", ctx->last.max_deg + 1);
+    ENSURE(ctx->tab_cnt, (size_t)(n + 1) * 4);
+    ENSURE(ctx->scratch, (size_t)(n / 2048 + 4) * 8);
+    CU(cudaEventRecord(ctx->cev[0], st));
+    dg_launch_table_counts(st, a0, a1, (const long long*)ctx->row_ptr.p, mode, (int*)ctx->tab_cnt.p);
+    dg_scan_i32_i64(st, (const int*)ctx->tab_cnt.p, (long long*)ctx->tab_ptr.p, n, (long long*)ctx->scratch.p);
+    long long total = 0;
+    CU(cudaMemcpyAsync(&total, (const long long*)ctx->tab_ptr.p + n, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    const size_t esz = mode == 0 ? 8 : 4;
+    ENSURE(ctx->tab_val, (size_t)total * esz + 16);
+    CU(dg_launch_distance_tables(st, a0, a1, (const long long*)ctx->row_ptr.p, (const int*)ctx->astruct.p,
+                                 (const DgSmall*)ctx->small.p, ctx->last.x, ctx->last.y, ctx->last.z,
+                                 (const int*)ctx->dst.p, (const uint32_t*)ctx->image.p,
+                                 (const long long*)ctx->tab_ptr.p, ctx->tab_val.p, mode, ctx->last.max_deg,
+                                 ctx->sm_count));
+    CU(cudaEventRecord(ctx->cev[1], st));
+    out->n_values = total;
+    out->values = ctx->tab_val.p;
+    long long rp[2];
+    CU(cudaMemcpyAsync(&rp[0], (const long long*)ctx->row_ptr.p + a0, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaMemcpyAsync(&rp[1], (const long long*)ctx->row_ptr.p + a1, 8, cudaMemcpyDeviceToHost, st));
+    // read: row_ptr + per edge (dst, image) + the positions they point at; written: tables + offsets
+    return consumer_end(ctx, 8 * (n + 1) + 8 * (rp[1] - rp[0]) + 24 * ((rp[1] - rp[0]) + n), (long long)(total * esz) + 8 * (n + 1));
+}
+
+int dgnn_copy_distance_tables_to_host(dgnn_ctx* ctx, const dgnn_distance_tables_out* t, void* values, int64_t* table_ptr) {
+    if (!ctx || !t) return DGNN_ERR_INVALID_ARG;
+    CU(cudaSetDevice(ctx->device));
+    cudaStream_t st = ctx->stream;
+    if (values && t->n_values > 0)
+        CU(cudaMemcpyAsync(values, t->values, (size_t)t->n_values * (t->mode == 0 ? 8 : 4), cudaMemcpyDeviceToHost, st));
+    if (table_ptr) CU(cudaMemcpyAsync(table_ptr, t->table_ptr, (size_t)(t->n_atoms + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    return DGNN_OK;
 }

@@ -224,6 +224,92 @@ __global__ void __launch_bounds__(DG_COLLATE_THREADS) k_neighborhood_clouds(long
     }
 }
 
+// f2: the (deg + 1) x (deg + 1) pairwise-distance tables the Betti caller builds from every cloud
+// (src/topology/ripser_wrapper.cpp:60-66, Eigen without FMA):
+//   sq_norms = rowwise squaredNorm           s_i  = (x_i x_i + y_i y_i) + z_i z_i
+//   sq_dist  = s_i + s_j - 2 P P^T           d2   = (s_i + s_j) - 2 ((x_i x_j + y_i y_j) + z_i z_j)   (GEMM, depth 3 in order)
+//   dist     = sq_dist.cwiseMax(0).cwiseSqrt()
+// One CTA per atom: the cloud (row 0 = the atom, row 1 + e = position + displacement of neighbour e,
+// betti_features.cpp:67-74) and its squared norms are staged in shared memory, a warp owns a column, lanes the rows, so
+// every store is a contiguous run.  MODE 0: full fp64 table, column-major (the MatrixXd `dist`); MODE 1: the compressed
+// lower triangle in fp32, row i = entries (i, 0..i-1) -- the `distances` vector handed to Ripser (:18-24).
+// No tensor cores: DMMA fuses multiply and add (one rounding), the reference rounds both -- the tables would differ in
+// the last bit, and the Gram product is 5 of the ~14 fp64 operations per entry (the rest: norms, max, IEEE sqrt).
+#define DG_TABLE_THREADS 256
+template <int MODE>
+__global__ void __launch_bounds__(DG_TABLE_THREADS) k_distance_tables(long long a0, long long a1,
+                                                                      const long long* __restrict__ row_ptr,
+                                                                      const int* __restrict__ astruct,
+                                                                      const DgSmall* __restrict__ small,
+                                                                      const double* __restrict__ x,
+                                                                      const double* __restrict__ y,
+                                                                      const double* __restrict__ z,
+                                                                      const int* __restrict__ dst,
+                                                                      const uint32_t* __restrict__ image,
+                                                                      const long long* __restrict__ table_ptr,
+                                                                      void* __restrict__ out, int m_cap) {
+    extern __shared__ __align__(16) double tsm[];
+    double* px = tsm;
+    double* py = px + m_cap;
+    double* pz = py + m_cap;
+    double* ps = pz + m_cap;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    for (long long a = a0 + blockIdx.x; a < a1; a += gridDim.x) {
+        const long long e0 = row_ptr[a], e1 = row_ptr[a + 1];
+        const int m = (int)(e1 - e0) + 1;
+        const DgSmall* __restrict__ G = small + astruct[a];
+        const long long abase = G->atom_base;
+        const double xi = x[a], yi = y[a], zi = z[a];
+        __syncthreads();  // the previous atom's cloud is dead
+        for (int t = tid; t < m; t += blockDim.x) {
+            double cx = xi, cy = yi, cz = zi;
+            if (t > 0) {
+                double dx, dy, dz;
+                const long long e = e0 + t - 1;
+                dg_edge_displacement(G, x, y, z, a, abase + dst[e], image[e], dx, dy, dz);
+                cx = DG_ADD(xi, dx);
+                cy = DG_ADD(yi, dy);
+                cz = DG_ADD(zi, dz);
+            }
+            px[t] = cx; py[t] = cy; pz[t] = cz;
+            ps[t] = DG_ADD(DG_ADD(DG_MUL(cx, cx), DG_MUL(cy, cy)), DG_MUL(cz, cz));
+        }
+        __syncthreads();
+        const long long base = table_ptr[a - a0];
+        if (MODE == 0) {
+            double* __restrict__ o = reinterpret_cast<double*>(out) + base;
+            for (int j = warp; j < m; j += nwarps) {
+                const double xj = px[j], yj = py[j], zj = pz[j], sj = ps[j];
+                for (int i = lane; i < m; i += 32) {
+                    const double dot = DG_ADD(DG_ADD(DG_MUL(px[i], xj), DG_MUL(py[i], yj)), DG_MUL(pz[i], zj));
+                    const double d2 = DG_SUB(DG_ADD(ps[i], sj), DG_MUL(2.0, dot));
+                    o[(long long)j * m + i] = __dsqrt_rn(d2 > 0.0 ? d2 : 0.0);
+                }
+            }
+        } else {
+            float* __restrict__ o = reinterpret_cast<float*>(out) + base;
+            for (int i = 1 + warp; i < m; i += nwarps) {
+                const double xr = px[i], yr = py[i], zr = pz[i], sr = ps[i];
+                float* __restrict__ orow = o + (long long)i * (i - 1) / 2;
+                for (int j = lane; j < i; j += 32) {
+                    const double dot = DG_ADD(DG_ADD(DG_MUL(xr, px[j]), DG_MUL(yr, py[j])), DG_MUL(zr, pz[j]));
+                    const double d2 = DG_SUB(DG_ADD(sr, ps[j]), DG_MUL(2.0, dot));
+                    orow[j] = (float)__dsqrt_rn(d2 > 0.0 ? d2 : 0.0);
+                }
+            }
+        }
+    }
+}
+
+// element counts of the tables of atoms [a0, a1) (int32: (deg + 1)^2 <= 4097^2)
+__global__ void k_table_counts(long long a0, long long a1, const long long* __restrict__ row_ptr, int mode,
+                               int* __restrict__ counts) {
+    const long long a = a0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (a >= a1) return;
+    const long long m = row_ptr[a + 1] - row_ptr[a] + 1;
+    counts[a - a0] = (int)(mode == 0 ? m * m : m * (m - 1) / 2);
+}
+
 static unsigned grid_for(long long work_items, int sm_count, int per_block) {
     long long g = (work_items + per_block - 1) / per_block;
     const long long cap = (long long)sm_count * 16;
@@ -276,4 +362,35 @@ void dg_launch_neighborhood_clouds(cudaStream_t st, long long a0, long long a1, 
     k_neighborhood_clouds<<<grid_for(a1 - a0, sm_count, DG_COLLATE_THREADS / 32), DG_COLLATE_THREADS, 0, st>>>(
         a0, a1, row_ptr, astruct, small, x, y, z, dst, image, cloud, cloud_ptr);
     ++g_collate_launches;
+}
+
+void dg_launch_table_counts(cudaStream_t st, long long a0, long long a1, const long long* row_ptr, int mode, int* counts) {
+    if (a1 <= a0) return;
+    k_table_counts<<<(unsigned)((a1 - a0 + 255) / 256), 256, 0, st>>>(a0, a1, row_ptr, mode, counts);
+    ++g_collate_launches;
+}
+
+cudaError_t dg_launch_distance_tables(cudaStream_t st, long long a0, long long a1, const long long* row_ptr,
+                                      const int* astruct, const DgSmall* small, const double* x, const double* y,
+                                      const double* z, const int* dst, const uint32_t* image, const long long* table_ptr,
+                                      void* out, int mode, int max_degree, int sm_count) {
+    if (a1 <= a0) return cudaSuccess;
+    const int m_cap = max_degree + 1;
+    const size_t smem = (size_t)m_cap * 4 * sizeof(double);
+    long long grid = a1 - a0;
+    if (grid > (long long)sm_count * 16) grid = (long long)sm_count * 16;
+    cudaError_t e;
+    if (mode == 0) {
+        e = cudaFuncSetAttribute(k_distance_tables<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_distance_tables<0><<<(unsigned)grid, DG_TABLE_THREADS, smem, st>>>(a0, a1, row_ptr, astruct, small, x, y, z, dst,
+                                                                              image, table_ptr, out, m_cap);
+    } else {
+        e = cudaFuncSetAttribute(k_distance_tables<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        k_distance_tables<1><<<(unsigned)grid, DG_TABLE_THREADS, smem, st>>>(a0, a1, row_ptr, astruct, small, x, y, z, dst,
+                                                                              image, table_ptr, out, m_cap);
+    }
+    ++g_collate_launches;
+    return cudaGetLastError();
 }

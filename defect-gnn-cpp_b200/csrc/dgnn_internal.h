@@ -207,4 +207,9 @@ void dg_launch_neighborhood_clouds(cudaStream_t st, long long a0, long long a1, 
                                    const int* astruct, const DgSmall* small, const double* x, const double* y,
                                    const double* z, const int* dst, const uint32_t* image, double* cloud,
                                    long long* cloud_ptr, int sm_count);
+void dg_launch_table_counts(cudaStream_t st, long long a0, long long a1, const long long* row_ptr, int mode, int* counts);
+cudaError_t dg_launch_distance_tables(cudaStream_t st, long long a0, long long a1, const long long* row_ptr,
+                                      const int* astruct, const DgSmall* small, const double* x, const double* y,
+                                      const double* z, const int* dst, const uint32_t* image, const long long* table_ptr,
+                                      void* out, int mode, int max_degree, int sm_count);
 int dg_collate_launch_count_reset();

@@ -75,3 +75,15 @@ def shard_edge_base(per_shard_counts: list[np.ndarray]) -> np.ndarray:
     out = np.zeros(tot.shape[0] + 1, dtype=np.int64)
     np.cumsum(tot, out=out[1:])
     return out
+
+
+def stream_plan(total_structs: int, world_size: int, rank: int, chunk_structs: int) -> list[tuple[int, int]]:
+    """Config 5 (a job of `total_structs` structures over `world_size` GPUs, streamed through a two-arena context,
+    dgnn_build_stream): the global structure ranges [s0, s1) rank `rank` builds, chunk by chunk.  Ranks own contiguous
+    equal shares (the job is homogeneous; remainder structures go to the first ranks), chunks are what one arena holds."""
+    if world_size <= 0 or not (0 <= rank < world_size) or chunk_structs <= 0 or total_structs < 0:
+        raise ValueError("bad stream plan arguments")
+    base, rem = divmod(total_structs, world_size)
+    s0 = rank * base + min(rank, rem)
+    s1 = s0 + base + (1 if rank < rem else 0)
+    return [(a, min(a + chunk_structs, s1)) for a in range(s0, s1, chunk_structs)]

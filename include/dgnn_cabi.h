@@ -170,6 +170,25 @@ int dgnn_edge_views(dgnn_ctx* ctx, const dgnn_graphs* g, int32_t* sources, int32
 int dgnn_neighborhood_clouds(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, int64_t a1, double* cloud,
                              int64_t* cloud_ptr);
 
+/* f2: the pairwise-distance tables the Betti caller builds from every cloud (src/topology/ripser_wrapper.cpp:60-66:
+ * sq_norms + sq_norms^T - 2 P P^T, cwiseMax(0), cwiseSqrt, in Eigen's FMA-free operation order), for the atoms [a0, a1):
+ *   mode 0: the full (deg+1) x (deg+1) fp64 table, column-major -- the Eigen::MatrixXd `dist`;
+ *   mode 1: its compressed lower triangle in fp32, entries (i, 0..i-1) for i = 1..deg -- the `distances` vector
+ *           compute_persistence_from_distances hands to Ripser (:18-24).
+ * Atom a0 + i owns values [table_ptr[i], table_ptr[i+1]).  Outputs are DEVICE pointers owned by the ctx (a C2 atom's
+ * full table is 207 kB: chunk the atom range), valid until the next call on this ctx; copy helper below. */
+typedef struct {
+    int64_t n_atoms;
+    int64_t n_values;
+    const void* values;        /* double (mode 0) or float (mode 1), device */
+    const int64_t* table_ptr;  /* [n_atoms + 1], device */
+    int32_t mode;
+} dgnn_distance_tables_out;
+int dgnn_distance_tables(dgnn_ctx* ctx, const dgnn_graphs* g, int64_t a0, int64_t a1, int32_t mode,
+                         dgnn_distance_tables_out* out);
+int dgnn_copy_distance_tables_to_host(dgnn_ctx* ctx, const dgnn_distance_tables_out* t, void* values,
+                                      int64_t* table_ptr);
+
 /* Device time (CUDA events on the ctx stream, kernels only -- no H2D / D2H) and algorithmic bytes of the last
  * dgnn_collate / dgnn_edge_views / dgnn_neighborhood_clouds call. */
 typedef struct {
@@ -199,6 +218,31 @@ typedef struct {
     int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
+
+/* ---- streamed build: jobs larger than one edge arena (BASELINE config 5: 10^6 structures, ~4 TB of graphs) ---------
+ * Replaces the reference's per-file driver loop (src/preprocess/preprocess_betti.cpp:37-79: parse -> Structure ->
+ * NeighborList per file, nothing retained) for batched jobs.  The job is cut into chunks by the caller's SOURCE; chunk c
+ * is built into arena c & 1 (the ctx and an internal twin with the same options) by a producer thread while the SINK
+ * consumes chunk c - 1 on the calling thread, so upload + count + fill of the next chunk overlap the consumer.
+ *   source(user, c, batch): fill *batch (host or device inputs, as for dgnn_build) for chunk c = 0, 1, ...; return 1, or
+ *                           0 when the job is finished, < 0 on error.  Called on the producer thread; the buffers of
+ *                           chunk c must stay valid until source is asked for chunk c + 1.
+ *   sink(user, c, graphs):  the chunk's graphs (device pointers, as from dgnn_build); valid until sink returns -- the
+ *                           arena is then rebuilt for chunk c + 2.  Called on the calling thread, in chunk order.
+ *                           Return 0 to continue.  May be NULL (graphs are built and dropped).
+ * Chunk size is the caller's: what one arena holds (176 B per edge at K = 40: 10 k C2 structures = 45 GB). */
+typedef int (*dgnn_stream_source)(void* user, int64_t chunk, dgnn_batch* batch);
+typedef int (*dgnn_stream_sink)(void* user, int64_t chunk, const dgnn_graphs* graphs);
+typedef struct {
+    int64_t n_chunks, n_structs, n_atoms, n_edges;
+    double wall_ms;          /* first source call to last sink return (host clock) */
+    double build_device_ms;  /* sum of the chunks' device build times (CUDA events) */
+    double h2d_ms;           /* of which input upload */
+    double sink_ms;          /* host time spent inside the sink */
+    int64_t kernel_launches;
+} dgnn_stream_info;
+int dgnn_build_stream(dgnn_ctx* ctx, dgnn_stream_source source, void* source_user, dgnn_stream_sink sink,
+                      void* sink_user, dgnn_stream_info* info);
 
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
 void* dgnn_stream(dgnn_ctx* ctx);

@@ -278,3 +278,24 @@ def neighborhood_cloud(x, y, z, o: OracleGraph, atom: int, disp=None) -> np.ndar
     out[0] = c
     out[1:] = c[None, :] + (o.disp if disp is None else disp)[e0:e1]
     return out
+
+
+def distance_table(cloud: np.ndarray) -> np.ndarray:
+    """compute_persistence's pairwise-distance matrix (src/topology/ripser_wrapper.cpp:60-66), restated with Eigen 3.4's
+    FMA-free operation order: sq_norms = rowwise().squaredNorm() = (x x + y y) + z z; sq_dist = (s_i + s_j) - 2 P P^T with
+    the depth-3 product accumulated in order ((x_i x_j + y_i y_j) + z_i z_j, scaled by 2 exactly); cwiseMax(0).cwiseSqrt().
+    numpy's element-wise fp64 arithmetic rounds once per operation, like the reference's build without -march."""
+    P = _f64(cloud).reshape(-1, 3)
+    x, y, z = P[:, 0], P[:, 1], P[:, 2]
+    s = (x * x + y * y) + z * z
+    dot = (x[:, None] * x[None, :] + y[:, None] * y[None, :]) + z[:, None] * z[None, :]
+    d2 = (s[:, None] + s[None, :]) - 2.0 * dot
+    return np.sqrt(np.maximum(d2, 0.0))
+
+
+def ripser_lower_triangle(dist: np.ndarray) -> np.ndarray:
+    """compute_persistence_from_distances' `distances` vector (ripser_wrapper.cpp:18-24): for i = 1..N-1, j = 0..i-1,
+    static_cast<float>(distance_matrix(i, j))."""
+    n = dist.shape[0]
+    out = [dist[i, :i].astype(np.float32) for i in range(1, n)]
+    return np.concatenate(out) if out else np.zeros(0, dtype=np.float32)

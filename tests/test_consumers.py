@@ -163,6 +163,46 @@ def test_gpu_edge_views_and_clouds_match_restatement(gpu_builder, gpu_builder_ce
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("which", ["direct", "cell"])
+def test_gpu_distance_tables_match_restatement(gpu_builder, gpu_builder_cell, oracle, syn, which):
+    """f2: the Betti caller's (deg+1)^2 pairwise-distance tables (ripser_wrapper.cpp:60-66), bit-exact in fp64 against
+    the numpy restatement of Eigen's operation order; the compressed fp32 lower triangle is what Ripser is handed."""
+    gb = gpu_builder if which == "direct" else gpu_builder_cell
+    b = _mixed_batch(syn)
+    for rc, cap in ((8.0, oracle.UNCAPPED), (5.0, 12)):
+        g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=rc, max_neighbors=cap, skip_rbf=True)
+        og = _oracle_graphs(oracle, b, rc, cap)
+        N = b.n_atoms
+        full, fptr = gb.distance_tables(0, N, mode=0)
+        low, lptr = gb.distance_tables(0, N, mode=1)
+        assert fptr[0] == 0 and lptr[0] == 0 and fptr[-1] == full.shape[0] and lptr[-1] == low.shape[0]
+        for s, o in enumerate(og):
+            x, y, z, L = b.structure(s)
+            d = oracle.displacements(x, y, z, L, o)
+            a0 = int(b.atom_offsets[s])
+            for i in range(len(x)):
+                cloud = oracle.neighborhood_cloud(x, y, z, o, i, d)
+                m = cloud.shape[0]
+                ref = oracle.distance_table(cloud)
+                got = full[fptr[a0 + i]:fptr[a0 + i + 1]]
+                assert got.shape[0] == m * m, (s, i)
+                assert np.array_equal(got.reshape(m, m).T.view(np.int64), ref.view(np.int64)), (s, i)  # column-major
+                assert np.array_equal(low[lptr[a0 + i]:lptr[a0 + i + 1]], oracle.ripser_lower_triangle(ref)), (s, i)
+        # a sub-range, the empty range, bad arguments
+        sub, sptr = gb.distance_tables(2, 5, mode=1)
+        assert np.array_equal(sub, low[lptr[2]:lptr[5]]) and np.array_equal(sptr, lptr[2:6] - lptr[2])
+        e, eptr = gb.distance_tables(4, 4, mode=0)
+        assert e.shape[0] == 0 and eptr[0] == 0
+        gb.distance_tables(0, 3, mode=1)
+        info = gb.consumer_info()
+        assert info.kernel_launches >= 2 and info.device_ms > 0 and info.bytes_written > 0
+        with pytest.raises(Exception):
+            gb.distance_tables(0, N + 1)
+        with pytest.raises(Exception):
+            gb.distance_tables(0, 1, mode=2)
+
+
+@pytest.mark.gpu
 def test_gpu_consumers_reject_stale_graphs(gpu_builder, syn, pkg):
     gb = gpu_builder
     b = syn.c2_batch(2)

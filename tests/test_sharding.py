@@ -86,3 +86,20 @@ def test_gloo_world2_gather_and_offsets(pkg, oracle, syn):
     for rank, parts, offs in res:
         assert offs == expect            # both ranks derive the same global offsets
         assert parts[0][1] == parts[1][0]
+
+
+def test_stream_plan_covers_the_job_once(pkg):
+    """Config 5 sharding: every structure of the job is in exactly one chunk of exactly one rank, in order."""
+    sh = pkg.sharding
+    for total, world, chunk in ((1_000_000, 8, 10_000), (1_000_003, 4, 12_345), (17, 8, 5), (0, 2, 10), (5, 8, 3)):
+        seen = []
+        for r in range(world):
+            plan = sh.stream_plan(total, world, r, chunk)
+            assert all(0 < b - a <= chunk for a, b in plan)
+            assert all(plan[i][1] == plan[i + 1][0] for i in range(len(plan) - 1))
+            seen += plan
+        flat = [s for a, b in seen for s in (a, b)]
+        assert flat == sorted(flat)
+        assert sum(b - a for a, b in seen) == total and (not seen or (seen[0][0] == 0 and seen[-1][1] == total))
+    with pytest.raises(ValueError):
+        sh.stream_plan(10, 0, 0, 5)
