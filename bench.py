@@ -197,6 +197,138 @@ def run_reference(args, rank):
     return 0
 
 
+def golden_digests():
+    """Edge totals of the configs' synthetic workloads from the pinned CPU oracle (committed fixture; generated by
+    tests/golden/make_config_digests.py -- bench.py itself does not execute oracle/ outside the cpu_baseline leg)."""
+    try:
+        return json.load(open(os.path.join(ROOT, "tests", "golden", "config_digests.json")))
+    except Exception:
+        return {}
+
+
+def run_configs(gb, pkg, torch, dev, peak, d_c2, b_c2, reps=5):
+    """Driver-visible sub-measurements of the other BASELINE configs on this GPU (rank 0, N = 1): C1 the 9 shipped POSCARs
+    at the reference defaults, C2 with the reference's cap of 20, C3 10 k triclinic short-vector cells, C4 one 1 M-atom
+    cell.  Device-resident inputs, median of `reps` builds after 2 warm-ups, CUDA-event time of the whole build."""
+    syn = pkg.synthetic
+    gold = golden_digests()
+    out = {}
+
+    def measure(name, t, n_structs, n_atoms, rc, cap, dr, gold_key, parity_test, note=None):
+        infos = []
+        g = None
+        for i in range(reps + 2):
+            g = gb.build(*t, r_cutoff=rc, max_neighbors=cap, epsilon=1e-10, rbf_r_cutoff=rc, dr=dr, device_inputs=True)
+            if i >= 2:
+                infos.append(gb.info())
+        E, K = int(g.n_edges), int(g.K)
+        ms = statistics.median(i.total_ms for i in infos)
+        bytes_all = sum(int(x.numel() * x.element_size()) for x in t) + 8 * (n_atoms + 1) + E * (16 + 4 * K)
+        gd = gold.get(gold_key, {})
+        rec = {"n_structs": n_structs, "n_atoms": n_atoms, "n_edges": E, "K": K, "r_cutoff": rc,
+               "max_neighbors": "uncapped" if cap == UNCAPPED else cap, "ms_per_build": ms,
+               "edges_per_sec": E / (ms * 1e-3), "structures_per_sec": n_structs / (ms * 1e-3),
+               "whole_path_gbs": bytes_all / (ms * 1e-3) / 1e9, "frac_of_measured_peak": bytes_all / (ms * 1e-3) / 1e9 / peak,
+               "phases_ms": {k: statistics.median(getattr(i, k) for i in infos) for k in ("count_ms", "fill_ms")},
+               "launches": int(infos[-1].kernel_launches), "cell_list_structs": int(infos[-1].n_cell_structs),
+               "parity": {"n_edges_equals_oracle_total": (E == gd.get("n_edges")) if gd else None,
+                          "oracle_total": gd.get("n_edges"), "golden": "tests/golden/config_digests.json",
+                          "bit_exact_test": parity_test}}
+        if note:
+            rec["note"] = note
+        out[name] = rec
+
+    d = np.load(os.path.join(ROOT, "tests", "golden", "c1_structures.npz"))
+    parts = []
+    for nm in d["names"]:
+        c = d[f"{nm}__cart"]
+        parts.append((c[:, 0].copy(), c[:, 1].copy(), c[:, 2].copy(), d[f"{nm}__lattice"].copy()))
+    b1 = syn.concat(parts)
+    to_dev = lambda b: [torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+    measure("C1_9_shipped_POSCARs_reference_defaults", to_dev(b1), b1.n_structs, b1.n_atoms, 10.0, 20, 0.1,
+            "C1_reference_defaults", "tests/test_gpu_vs_reference.py::test_gpu_matches_compiled_reference_on_shipped_poscars",
+            note="one batch of 9; the reference API shape (one structure per call) is timed by tools/bench_configs.py")
+    measure("C2_10k_cap20", d_c2, b_c2.n_structs, b_c2.n_atoms, R_CUTOFF, 20, DR, "C2_10k_cap20",
+            "tests/test_gpu_fullsize.py (full-size C2) + tests/test_gpu_parity.py::test_truncated_rows_topk_prefilter")
+    b3 = syn.c3_batch(10_000)
+    measure("C3_10k_triclinic_short_vectors", to_dev(b3), b3.n_structs, b3.n_atoms, R_CUTOFF, UNCAPPED, DR,
+            "C3_10k_uncapped", "tests/test_gpu_parity.py (C3 batches) + tests/test_gpu_vs_reference.py")
+    del b3
+    b4 = syn.c4_structure()
+    measure("C4_one_1M_atom_cell", to_dev(b4), b4.n_structs, b4.n_atoms, R_CUTOFF, UNCAPPED, DR, "C4_1M_atom_cell",
+            "tests/test_gpu_fullsize.py::test_c4_million_atom_cell",
+            note="cell-list path: fp32 tiles staged in shared memory (k_cell32), fp64 decision in the guard band")
+    del b4
+    torch.cuda.empty_cache()
+    return out
+
+
+def run_c5(gb, pkg, torch, dist, dev, world, rank, b, h_in, total_structs=1_000_000):
+    """BASELINE config 5: a job of 10^6 C2-style structures per NODE, sharded by structure over the ranks and streamed
+    through dgnn_build_stream (two arenas per GPU: chunk c + 1 is uploaded and built while the sink reads chunk c's
+    offsets).  Strong scaling: the job is fixed, each rank builds total / N structures in chunks of one arena.  Host
+    inputs come from this rank's pinned pool (the step batch, 10 k distinct structures, cycled: a numpy generator at
+    ~4 k structures/s would dominate otherwise) and cross PCIe afresh for every chunk."""
+    sh = pkg.sharding
+    S = b.n_structs
+    plan = sh.stream_plan(total_structs, world, rank, S)
+    chunk_edges = []
+    h_seo = torch.empty(S + 1, dtype=torch.int64).pin_memory()
+
+    def source(c):
+        if c >= len(plan):
+            return None
+        n = plan[c][1] - plan[c][0]
+        if n == S:
+            return tuple(h_in)
+        a1 = int(b.atom_offsets[n])
+        return (h_in[0][:n + 1], h_in[1][:a1], h_in[2][:a1], h_in[3][:a1], h_in[4][:n])
+
+    def sink(c, g, arena):
+        # the consumer of the path: per-structure edge offsets come back to the host, the graphs stay in HBM
+        arena._check(arena.lib.dgnn_copy_to_host(arena.h, g, None, None, None, None, None, h_seo.data_ptr()))
+        chunk_edges.append(int(g.n_edges))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    stream = torch.cuda.ExternalStream(gb.stream, device=dev)
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    info = gb.build_stream(source, sink, r_cutoff=R_CUTOFF, max_neighbors=UNCAPPED, epsilon=1e-10,
+                           rbf_r_cutoff=R_CUTOFF, dr=DR)
+    e1.record(stream)
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    barrier()
+    vals = torch.tensor([ms, info.wall_ms, info.build_device_ms, info.h2d_ms, info.sink_ms], dtype=torch.float64, device=dev)
+    tot = torch.tensor([info.n_edges, info.n_structs, info.n_chunks], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(vals, op=dist.ReduceOp.MAX)
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    ms, wall_ms, build_ms, h2d_ms, sink_ms = (float(v) for v in vals.tolist())
+    edges, structs, chunks = (int(v) for v in tot.tolist())
+    # host-side gather of per-chunk edge counts -> global chunk offsets (the only cross-rank exchange)
+    t0 = time.perf_counter()
+    gathered = sh.gather_edge_counts(np.asarray(chunk_edges, dtype=np.int64)) if world > 1 else [np.asarray(chunk_edges)]
+    offsets = sh.global_edge_offsets(gathered)
+    scan_ms = (time.perf_counter() - t0) * 1e3
+    assert int(offsets[-1]) == edges and structs == total_structs
+    return {"job_structures": total_structs, "n_gpus": world, "scaling": "strong",
+            "chunk_structures": S, "chunks_total": chunks, "edges_total": edges,
+            "ms": ms, "wall_ms": wall_ms, "edges_per_sec": edges / (ms * 1e-3), "structures_per_sec": structs / (ms * 1e-3),
+            "per_rank_max": {"build_device_ms_sum": build_ms, "h2d_ms_sum": h2d_ms, "sink_host_ms_sum": sink_ms},
+            "build_share_of_wall": build_ms / wall_ms if wall_ms > 0 else None,
+            "host_offset_scan_ms": scan_ms,
+            "h2d_bytes_per_chunk": sum(int(t.numel() * t.element_size()) for t in h_in),
+            "note": "time = CUDA events on the ctx stream around dgnn_build_stream, max over ranks; every chunk's inputs "
+                    "cross PCIe from pinned host memory and its per-structure offsets come back; graphs are dropped when "
+                    "the arena is rebuilt two chunks later; inputs cycle through a pool of %d distinct structures" % S}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -206,6 +338,9 @@ def main():
     ap.add_argument("--structures", type=int, default=None, help="structures per GPU per step (default 10000)")
     ap.add_argument("--e2e-steps", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the C1/C2cap/C3/C4 sub-measurements (N = 1 only)")
+    ap.add_argument("--no-c5", action="store_true", help="skip the streamed 10^6-structure job (config 5)")
+    ap.add_argument("--c5-structures", type=int, default=1_000_000)
     ap.add_argument("--opt", action="append", default=[], help="tuning option name=value (dgnn_set_option), repeatable")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 0)
@@ -370,17 +505,28 @@ def main():
         "phases_ms": {k: statistics.mean(getattr(i, k) for i in infos)
                       for k in ("bin_ms", "count_ms", "fill_ms", "rbf_ms", "total_ms")},
         "e2e": {"value": edges_all_e2e / (ms_e2e / 1e3), "unit": UNIT, "h2d_bytes_per_step": h2d_bytes,
+                "graphs_left_in_hbm_bytes_per_step": int(all_bytes),
                 "d2h_bytes_per_step": d2h_bytes, "steps": e2e_steps, "ms_per_step": ms_e2e / e2e_steps,
                 "phases_ms": {k: statistics.mean(getattr(i, k) for i in infos_e2e)
                               for k in ("h2d_ms", "bin_ms", "count_ms", "fill_ms", "total_ms")},
                 "note": "dgnn_build on pinned host SoA buffers + D2H of row_ptr and per-structure edge offsets; "
-                        "graphs stay in HBM for the consumer"},
+                        "graphs stay in HBM for the consumer (north_star: only counts / offsets come back) -- a consumer "
+                        "on the HOST would add those bytes over PCIe (~0.8 s per step at 55 GB/s), which this number "
+                        "does not contain"},
         "gpu_launches": launches,
         "build": {"onepass": int(infos[-1].onepass), "onepass_fallback_rows": int(infos[-1].onepass_fallback_rows),
                   "rbf_fused": int(infos[-1].rbf_fused), "row_cap": int(infos[-1].row_cap)},
         "clocks": clocks,
     }
 
+    # roofline.traffic is attached only when the committed capture is of the kernel this run timed: say which
+    if traffic is not None:
+        line["roofline"]["traffic_capture"] = {"kernel": tj.get("kernel"), "report": tj.get("source"),
+                                                "gpu_time_ms": tj.get("gpu_time_ms")}
+    if not args.no_c5 and S == 10_000:
+        line["c5"] = run_c5(gb, pkg, torch, dist, dev, world, rank, b, h_in, args.c5_structures)
+    if rank == 0 and world == 1 and not args.no_configs and S == 10_000:
+        line["configs"] = run_configs(gb, pkg, torch, dev, peak, d_in, b)
     if rank == 0 and not args.no_cpu_baseline and world == 1:
         cores = os.cpu_count() or 1
         t0 = time.time()

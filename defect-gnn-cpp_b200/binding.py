@@ -100,7 +100,7 @@ class DgnnStreamInfo(C.Structure):
 
 
 STREAM_SOURCE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnBatch))
-STREAM_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnGraphs))
+STREAM_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnGraphs), C.c_void_p)
 
 
 class DgnnError(RuntimeError):
@@ -215,6 +215,9 @@ class GraphBuilder:
         self.last = None
 
     def close(self):
+        if getattr(self, "_borrowed", False):
+            self.h = None
+            return
         if getattr(self, "h", None):
             self.lib.dgnn_destroy(self.h)
             self.h = None
@@ -259,8 +262,9 @@ class GraphBuilder:
     def build_stream(self, source, sink=None, r_cutoff=10.0, max_neighbors=20, epsilon=1e-10, rbf_r_cutoff=10.0,
                      dr=0.1, device_inputs=False) -> DgnnStreamInfo:
         """dgnn_build_stream: `source(c)` returns the chunk's (atom_offsets, x, y, z, lattices) -- numpy / pinned torch
-        (host) or device tensors -- or None when the job is finished; `sink(c, graphs)` sees the chunk's DgnnGraphs
-        (device pointers, valid until it returns).  Chunk c + 1 is uploaded and built while sink(c) runs."""
+        (host) or device tensors -- or None when the job is finished; `sink(c, graphs, arena)` sees the chunk's DgnnGraphs
+        (device pointers, valid until it returns) and a GraphBuilder view of the context that owns them (use IT for
+        to_host / collate / distance_tables of this chunk).  Chunk c + 1 is uploaded and built while sink(c) runs."""
         keep = {}
         errs = []
 
@@ -286,10 +290,15 @@ class GraphBuilder:
                 errs.append(exc)
                 return -1
 
-        def _snk(_user, c, gp):
+        def _snk(_user, c, gp, arena):
             try:
                 if sink is not None:
-                    sink(int(c), gp.contents)
+                    view = GraphBuilder.__new__(GraphBuilder)   # borrowed handle: never destroyed from here
+                    view.lib, view.h, view.device, view.last = self.lib, None, self.device, gp.contents
+                    view.__dict__["h"] = C.c_void_p(arena)
+                    view._borrowed = True
+                    sink(int(c), gp.contents, view)
+                    view.__dict__["h"] = None
                 return 0
             except Exception as exc:  # noqa: BLE001
                 errs.append(exc)

@@ -92,7 +92,7 @@ extern "C" int dgnn_build_stream(dgnn_ctx* ctx, dgnn_stream_source source, void*
             break;
         }
         const auto k0 = std::chrono::steady_clock::now();
-        const int kr = sink ? sink(sink_user, s.chunk, &s.g) : 0;
+        const int kr = sink ? sink(sink_user, s.chunk, &s.g, arena[c & 1]) : 0;
         I.sink_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - k0).count();
         I.n_chunks += 1;
         I.n_structs += s.g.n_structs;

@@ -227,12 +227,14 @@ int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
  *   source(user, c, batch): fill *batch (host or device inputs, as for dgnn_build) for chunk c = 0, 1, ...; return 1, or
  *                           0 when the job is finished, < 0 on error.  Called on the producer thread; the buffers of
  *                           chunk c must stay valid until source is asked for chunk c + 1.
- *   sink(user, c, graphs):  the chunk's graphs (device pointers, as from dgnn_build); valid until sink returns -- the
- *                           arena is then rebuilt for chunk c + 2.  Called on the calling thread, in chunk order.
- *                           Return 0 to continue.  May be NULL (graphs are built and dropped).
+ *   sink(user, c, graphs, arena): the chunk's graphs (device pointers, as from dgnn_build) and the context that owns
+ *                           them -- pass `arena` (not the ctx given to dgnn_build_stream) to dgnn_copy_to_host,
+ *                           dgnn_collate, dgnn_distance_tables ... for this chunk; the other arena is busy building the
+ *                           next one.  Valid until sink returns: the arena is then rebuilt for chunk c + 2.  Called on
+ *                           the calling thread, in chunk order.  Return 0 to continue.  May be NULL (build and drop).
  * Chunk size is the caller's: what one arena holds (176 B per edge at K = 40: 10 k C2 structures = 45 GB). */
 typedef int (*dgnn_stream_source)(void* user, int64_t chunk, dgnn_batch* batch);
-typedef int (*dgnn_stream_sink)(void* user, int64_t chunk, const dgnn_graphs* graphs);
+typedef int (*dgnn_stream_sink)(void* user, int64_t chunk, const dgnn_graphs* graphs, dgnn_ctx* arena);
 typedef struct {
     int64_t n_chunks, n_structs, n_atoms, n_edges;
     double wall_ms;          /* first source call to last sink return (host clock) */

@@ -24,9 +24,9 @@ def test_streamed_build_equals_chunkwise_builds(pkg, oracle, syn, gpu_builder):
         b = job.slice(*bounds[c])
         return b.atom_offsets, b.x, b.y, b.z, b.lattices
 
-    def sink(c, g):
+    def sink(c, g, arena):
         order.append(c)
-        got[c] = gs.to_host(g)
+        got[c] = arena.to_host(g)       # the arena that owns this chunk (the other one is building chunk c + 1)
 
     info = gs.build_stream(source, sink, r_cutoff=8.0, max_neighbors=pkg.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
     assert order == list(range(len(bounds))) and info.n_chunks == len(bounds)
@@ -54,7 +54,7 @@ def test_streamed_build_equals_chunkwise_builds(pkg, oracle, syn, gpu_builder):
     with pytest.raises(ValueError):
         gs.build_stream(lambda c: (_ for _ in ()).throw(ValueError("source broke")), None, r_cutoff=8.0)
 
-    def bad_sink(c, g):
+    def bad_sink(c, g, arena):
         raise KeyError("sink broke")
     with pytest.raises(KeyError):
         gs.build_stream(source, bad_sink, r_cutoff=8.0, max_neighbors=pkg.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
