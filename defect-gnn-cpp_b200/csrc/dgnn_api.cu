@@ -72,6 +72,7 @@ struct dgnn_ctx {
     int cell32 = 1;                       // cell-list structures: fp32 tiles staged in shared memory + fp64 decision in the
                                           // guard band (dgnn_cell32.cu); 0: the fp64 traversal with hit lists (A/B reference)
     int cell32_fill_warps = 16;
+    int dyn_rows = 1;                     // small batches: dynamic per-warp row schedule in the direct kernels
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
@@ -364,6 +365,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->cell32_fill_warps = (int)value;
     } else if (!strcmp(name, "cell32")) {
         ctx->cell32 = value != 0.0;
+    } else if (!strcmp(name, "dyn_rows")) {
+        ctx->dyn_rows = value != 0.0;
     } else if (!strcmp(name, "sym_count")) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
@@ -602,6 +605,20 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.hits_d2 = hit_cap > 0 ? (double*)ctx->hits_d2.p : nullptr;
     D.hit_cap = hit_cap;
     D.stats = d_stats;
+    // small batches (fewer than two rounds of 64-row chunks over a full grid): rows go to warps a few at a time from a
+    // device counter -- uneven rows (tiny triclinic cells: 2-8 atoms, 343-729 images per pair) otherwise leave most of
+    // the grid waiting for the CTAs that drew the expensive structures
+    const bool dyn_rows = ctx->dyn_rows && N > 0 && N < (long long)ctx->sm_count * 2 * 8 * 64 * 2;
+    int dyn_launch = 0;
+    auto dyn_arm = [&](DgDirectArgs& X) {
+        if (dyn_rows && dyn_launch < 8) {
+            X.dyn_unit = 4;
+            X.unit_ctr = &((DgStats*)ctx->stats.p)->unit_ctr[dyn_launch++];
+        } else {
+            X.dyn_unit = 0;
+            X.unit_ctr = nullptr;
+        }
+    };
     // ---- single-pass build (direct-path batches): traversal + look-back row offsets + sort + emit in one kernel --
     // The edge arena and the row buffers are sized from the density estimate; rows that outgrow the buffer, or an
     // arena that turns out too small, are completed by the regular fill pass afterwards (row_ptr is final either way).
@@ -688,7 +705,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
                     D.row_begin = up_a[c];
                     D.row_end = up_a[c + 1];
                     if (sym) CU(dg_launch_direct_count_sym(st, D, ctx->sm_count, ctx->direct_min_blocks));
-                    else CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+                    else {
+                        dyn_arm(D);
+                        CU(dg_launch_direct(st, D, false, ctx->sm_count, ctx->direct_min_blocks));
+                    }
                 }
             }
             D.row_begin = D.row_end = 0;
@@ -923,8 +943,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     if (!use_hits) D.hit_cap = 0;
     if (E > 0 && use_hits && (any_direct || (n_cell_structs > 0 && !cell32))) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
-    if (E > 0 && !onepass && any_direct && (!use_hits || n_fallback_rows > 0))
+    if (E > 0 && !onepass && any_direct && (!use_hits || n_fallback_rows > 0)) {
+        dyn_arm(D);
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+    }
     bool cell32_rest = false;  // rows the fp32-tile fill left to the fp64 traversal (degree beyond the register sort)
     if (cell32 && E > 0) {
         A.row_ptr = (const long long*)ctx->row_ptr.p;

@@ -117,7 +117,10 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
     dg_direct_launch_bump(1);
 }
 
-template <bool FILL, int MINB, int EPS, bool HITS, bool LEAN = false>
+// DYN: rows are handed out to WARPS in units of A.dyn_unit consecutive rows from a device counter instead of the static
+// round-robin of 64-row chunks over CTAs -- for small batches of uneven rows (config 3: 2-8 atoms per cell, 343-729
+// images per pair) the static schedule leaves most of the grid waiting for the CTAs that drew the expensive cells.
+template <bool FILL, int MINB, int EPS, bool HITS, bool LEAN = false, bool DYN = false>
 __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -130,38 +133,57 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
     const long long r0 = A.row_begin, r1 = A.row_end > 0 ? A.row_end : A.n_atoms;
     const long long n_chunks = (r1 - r0 + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
 
-    for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
-        const long long a_end = r0 + (chunk + 1) * DG_ROW_CHUNK < r1 ? r0 + (chunk + 1) * DG_ROW_CHUNK : r1;
-        for (long long a = r0 + chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
-            const DgSmall* __restrict__ G = A.small + A.astruct[a];
-            const int mode = G->mode;
-            if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;  // the cell-list path owns this structure
-            const int nimg = G->nimg;
-            // rows the hit-list fill pass (k_fill_hits) owns are skipped here; this pass takes the rest
-            if (FILL && A.hit_cap > 0 && nimg <= DG_HIT_NMAX && A.deg_raw[a] <= A.hit_cap) continue;  // (row_cap >= deg)
-            // ... and so are rows the single-pass build has already written
-            if (FILL && A.skip_deg_le > 0 && A.deg_raw[a] <= A.skip_deg_le) continue;
-            const bool store_hits = HITS && nimg <= DG_HIT_NMAX;
-            uint32_t* __restrict__ hrow = HITS ? A.hits + (size_t)a * (size_t)A.hit_cap : nullptr;
-            double* __restrict__ hd2 = HITS ? A.hits_d2 + (size_t)a * (size_t)A.hit_cap : nullptr;
-            int m = traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);
-            if (!FILL && !HITS) m = __reduce_add_sync(FULL_MASK, m);
-            maxdeg = m > maxdeg ? m : maxdeg;
-            const int keep = m < A.max_neighbors ? m : A.max_neighbors;
-            if (!FILL) {
-                if (lane == 0) {
-                    A.deg_capped[a] = keep;
-                    A.deg_raw[a] = m;
-                    if (HITS && (m > A.hit_cap || !store_hits)) atomicAdd(&A.stats->n_fallback_rows, 1);
-                }
-            } else if (m > A.row_cap) {  // cannot happen: row_cap >= max degree of the count pass
-                if (lane == 0) atomicExch(&A.stats->overflow, 1);
-            } else {
-                dg_row_sort_emit<LEAN>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image, A.dist,
-                                       A.stats, lane, A.rbf);
+    // (the row body is a macro shared by the two schedules: the static loop nest must stay exactly as it was -- routing
+    // both through one generic loop cost the headline kernel 4.7 %, same-box A/B 8.72 against 8.32 ms)
+#define DG_DIRECT_ROW_BODY                                                                                               \
+            const DgSmall* __restrict__ G = A.small + A.astruct[a];                                                      \
+            const int mode = G->mode;                                                                                    \
+            if (mode == DG_MODE_CELL || G->status != DG_ST_OK) continue; /* the cell-list path owns this structure */    \
+            const int nimg = G->nimg;                                                                                    \
+            /* rows the hit-list fill pass (k_fill_hits) owns are skipped here; this pass takes the rest */              \
+            if (FILL && A.hit_cap > 0 && nimg <= DG_HIT_NMAX && A.deg_raw[a] <= A.hit_cap) continue;                     \
+            /* ... and so are rows the single-pass build has already written */                                          \
+            if (FILL && A.skip_deg_le > 0 && A.deg_raw[a] <= A.skip_deg_le) continue;                                    \
+            const bool store_hits = HITS && nimg <= DG_HIT_NMAX;                                                         \
+            uint32_t* __restrict__ hrow = HITS ? A.hits + (size_t)a * (size_t)A.hit_cap : nullptr;                       \
+            double* __restrict__ hd2 = HITS ? A.hits_d2 + (size_t)a * (size_t)A.hit_cap : nullptr;                       \
+            int m = traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);             \
+            if (!FILL && !HITS) m = __reduce_add_sync(FULL_MASK, m);                                                     \
+            maxdeg = m > maxdeg ? m : maxdeg;                                                                            \
+            const int keep = m < A.max_neighbors ? m : A.max_neighbors;                                                  \
+            if (!FILL) {                                                                                                 \
+                if (lane == 0) {                                                                                         \
+                    A.deg_capped[a] = keep;                                                                              \
+                    A.deg_raw[a] = m;                                                                                    \
+                    if (HITS && (m > A.hit_cap || !store_hits)) atomicAdd(&A.stats->n_fallback_rows, 1);                 \
+                }                                                                                                        \
+            } else if (m > A.row_cap) { /* cannot happen: row_cap >= max degree of the count pass */                     \
+                if (lane == 0) atomicExch(&A.stats->overflow, 1);                                                        \
+            } else {                                                                                                     \
+                dg_row_sort_emit<LEAN>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image,    \
+                                       A.dist, A.stats, lane, A.rbf);                                                    \
+            }
+    if (DYN) {
+        for (;;) {
+            unsigned long long u = 0;
+            if (lane == 0) u = atomicAdd(A.unit_ctr, 1ULL);
+            u = __shfl_sync(FULL_MASK, u, 0);
+            const long long a_first = r0 + (long long)u * A.dyn_unit;
+            if (a_first >= r1) break;
+            const long long a_end = a_first + A.dyn_unit < r1 ? a_first + A.dyn_unit : r1;
+            for (long long a = a_first; a < a_end; ++a) {
+                DG_DIRECT_ROW_BODY
+            }
+        }
+    } else {
+        for (long long chunk = blockIdx.x; chunk < n_chunks; chunk += gridDim.x) {
+            const long long a_end = r0 + (chunk + 1) * DG_ROW_CHUNK < r1 ? r0 + (chunk + 1) * DG_ROW_CHUNK : r1;
+            for (long long a = r0 + chunk * DG_ROW_CHUNK + warp; a < a_end; a += nwarps) {
+                DG_DIRECT_ROW_BODY
             }
         }
     }
+#undef DG_DIRECT_ROW_BODY
     if (!FILL) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) near += __shfl_xor_sync(FULL_MASK, near, o);
@@ -175,50 +197,51 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {
     return fill ? (size_t)a.n_warps * dg_rowbuf_bytes(a.row_cap, a.n_buckets) : 0;
 }
-template <bool FILL, int MINB, int EPS, bool HITS, bool LEAN = false>
+template <bool FILL, int EPS, bool HITS, bool LEAN, bool DYN>
 static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, MINB, EPS, HITS, LEAN>,
+    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, 2, EPS, HITS, LEAN, DYN>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     int occ = 1;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, MINB, EPS, HITS, LEAN>, threads, smem);
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, 2, EPS, HITS, LEAN, DYN>, threads, smem);
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
-    // persistent grid: every SM full, chunks of DG_ROW_CHUNK consecutive rows handed out round-robin (the single-pass
-    // look-back relies on the grid being fully resident: never more CTAs than the occupancy query allows)
+    // persistent grid: every SM full; static schedule = chunks of DG_ROW_CHUNK consecutive rows round-robin over CTAs
     const long long rows = (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
-    const long long want = (rows + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
+    const long long want = DYN ? (rows + (long long)a.dyn_unit * (threads / 32) - 1) / ((long long)a.dyn_unit * (threads / 32))
+                               : (rows + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
     long long grid = (long long)sm_count * occ;
     if (grid > want) grid = want;
     if (grid < 1) return cudaSuccess;
-    k_direct<FILL, MINB, EPS, HITS, LEAN><<<(unsigned)grid, threads, smem, st>>>(a);
+    k_direct<FILL, 2, EPS, HITS, LEAN, DYN><<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
 }
 
-template <bool FILL, int MINB, bool HITS, bool LEAN = false>
+template <bool FILL, bool HITS, bool LEAN>
 static cudaError_t launch_direct_e(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
+    const bool dyn = a.dyn_unit > 0 && a.unit_ctr != nullptr;
+#define DG_LD(E)                                                                              \
+    return dyn ? launch_direct_t<FILL, E, HITS, LEAN, true>(st, a, sm_count, smem, threads)   \
+               : launch_direct_t<FILL, E, HITS, LEAN, false>(st, a, sm_count, smem, threads);
     switch (a.eps_mode) {
-        case 0: return launch_direct_t<FILL, MINB, 0, HITS, LEAN>(st, a, sm_count, smem, threads);
-        case 1: return launch_direct_t<FILL, MINB, 1, HITS, LEAN>(st, a, sm_count, smem, threads);
-        default: return launch_direct_t<FILL, MINB, 2, HITS, LEAN>(st, a, sm_count, smem, threads);
+        case 0: DG_LD(0)
+        case 1: DG_LD(1)
+        default: DG_LD(2)
     }
+#undef DG_LD
 }
 
+// (a.dyn_unit > 0 with a zeroed a.unit_ctr: dynamic per-warp schedule, see k_direct)
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks) {
+    (void)min_blocks;  // (3 CTAs per SM at 80 registers measured slower, round 1: the variant is no longer compiled)
     if (a.n_atoms <= 0) return cudaSuccess;
     const size_t smem = dg_direct_smem_bytes(a, fill);
     const int threads = a.n_warps * 32;
     dg_direct_launch_bump(1);
     if (fill && a.max_neighbors >= a.row_cap)  // no row is truncated: the lean sort
-        return min_blocks <= 2 ? launch_direct_e<true, 2, false, true>(st, a, sm_count, smem, threads)
-                               : launch_direct_e<true, 3, false, true>(st, a, sm_count, smem, threads);
-    if (fill)
-        return min_blocks <= 2 ? launch_direct_e<true, 2, false>(st, a, sm_count, smem, threads)
-                               : launch_direct_e<true, 3, false>(st, a, sm_count, smem, threads);
-    if (a.hit_cap > 0 && a.hits)
-        return min_blocks <= 2 ? launch_direct_e<false, 2, true>(st, a, sm_count, smem, threads)
-                               : launch_direct_e<false, 3, true>(st, a, sm_count, smem, threads);
-    return min_blocks <= 2 ? launch_direct_e<false, 2, false>(st, a, sm_count, smem, threads)
-                           : launch_direct_e<false, 3, false>(st, a, sm_count, smem, threads);
+        return launch_direct_e<true, false, true>(st, a, sm_count, smem, threads);
+    if (fill) return launch_direct_e<true, false, false>(st, a, sm_count, smem, threads);
+    if (a.hit_cap > 0 && a.hits) return launch_direct_e<false, true, false>(st, a, sm_count, smem, threads);
+    return launch_direct_e<false, false, false>(st, a, sm_count, smem, threads);
 }
 

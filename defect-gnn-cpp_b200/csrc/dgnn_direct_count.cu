@@ -196,6 +196,7 @@ void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count)
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks) {
     if (a.n_atoms <= 0) return cudaSuccess;
     if (a.eps_mode > 1) return cudaErrorInvalidValue;
-    return min_blocks <= 2 ? launch_count_sym_m<2>(st, a, sm_count) : launch_count_sym_m<3>(st, a, sm_count);
+    (void)min_blocks;  // (3 CTAs per SM at 80 registers spills: not compiled)
+    return launch_count_sym_m<2>(st, a, sm_count);
 }
 

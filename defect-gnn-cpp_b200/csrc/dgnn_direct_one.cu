@@ -292,6 +292,7 @@ cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int
     const size_t smem = dg_direct_onepass_smem_bytes(a);
     const int threads = a.n_warps * 32;
     dg_direct_launch_bump(1);
-    return min_blocks <= 2 ? launch_one_e<2>(st, a, sm_count, smem, threads) : launch_one_e<3>(st, a, sm_count, smem, threads);
+    (void)min_blocks;
+    return launch_one_e<2>(st, a, sm_count, smem, threads);
 }
 

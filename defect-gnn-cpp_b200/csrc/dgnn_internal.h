@@ -27,6 +27,7 @@ struct DgStats {
     int cap_overflow;            // single-pass build: a row did not fit the (estimated) edge arena -> rerun as two passes
     int lb_timeout;              // single-pass build: a look-back spin gave up (must not happen: all CTAs are resident)
     unsigned long long est_edges;  // density estimate of the edge total, sum over structures of N_s * est_deg_s
+    unsigned long long unit_ctr[8];  // row-unit counters of dynamically scheduled launches (one per launch)
     int est_sparse;              // 1000000 - smallest per-structure degree estimate (0: no non-empty structure)
 };
 
@@ -163,6 +164,8 @@ struct DgDirectArgs {
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
     long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
     int fill_hits_bulk;             // k_fill_hits: features through the bulk-copy engine (1) or st.global.cs (0)
+    int dyn_unit;                   // > 0: rows are handed out to warps in units of this many rows from *unit_ctr (zeroed)
+    unsigned long long* unit_ctr;
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
 };
 #define DG_EPS_FAST 1.0e-3

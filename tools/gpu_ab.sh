@@ -6,7 +6,7 @@ out=gpurun_out; mkdir -p $out
 for i in 1 2 3; do
   for v in base alt; do
     if [ $v = alt ]; then export DGNN_LIB=$alt; else unset DGNN_LIB; fi
-    timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --e2e-steps 2 > $out/${tag}_${v}_$i.json 2> $out/${tag}_${v}_$i.err
+    timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-configs --no-c5 --e2e-steps 2 > $out/${tag}_${v}_$i.json 2> $out/${tag}_${v}_$i.err
     python - <<PY
 import json
 try:
