@@ -75,6 +75,9 @@ struct dgnn_ctx {
     int dyn_rows = 1;                     // small batches: dynamic per-warp row schedule in the direct kernels
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
+    bool onepass_skip = false;            // (set while a build whose look-back timed out is being redone in two passes)
+    int lb_fallbacks = 0;                 // builds redone that way since the context was created
+    int lb_spin_limit = 0;                // (testing) look-back spins before giving up, 0: default
     int onepass_opt = -1;                 // single-pass build of direct-path batches: -1 auto, 0 off, 1 wherever legal
     DevBuf lb_status;                     // per-row look-back status words of the single-pass build
     // the last successful build, for the CSR consumers (collation, viewer arrays, neighbourhood clouds)
@@ -374,6 +377,9 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "onepass")) {
         if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass must be -1, 0 or 1");
         ctx->onepass_opt = (int)value;  // single-pass build (look-back row offsets) instead of count + fill
+    } else if (!strcmp(name, "lb_spin_limit")) {
+        if (!(value >= 0 && value <= 1e9)) return fail(ctx, DGNN_ERR_INVALID_ARG, "lb_spin_limit out of range");
+        ctx->lb_spin_limit = (int)value;
     } else if (!strcmp(name, "onepass_row_cap")) {
         if (!(value >= 0 && value <= DGNN_MAX_DEGREE)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass_row_cap out of range");
         ctx->onepass_row_cap = (int)value;
@@ -629,7 +635,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // per CTA -- the reference's one-structure-per-call API above all -- finishes in one kernel and one sync less
     // (9 shipped POSCARs: 0.31 ms vs 1.37 ms).
     const long long onepass_auto_rows = (long long)ctx->sm_count * 2 * 8 * 2;  // two steps of a full grid
-    if (have_est && ctx->onepass_opt != 0 && N > 0 && ctx->h_stats->err_status == 0 &&
+    if (have_est && ctx->onepass_opt != 0 && !ctx->onepass_skip && N > 0 && ctx->h_stats->err_status == 0 &&
         ctx->h_stats->n_cell_structs == 0 &&
         (ctx->onepass_opt > 0 || (N <= onepass_auto_rows && (hit_cap == 0 || ctx->hit_cap_opt < 0)))) {
         const long long est = ctx->h_stats->est_deg;
@@ -666,6 +672,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             O.image = (uint32_t*)ctx->image.p;
             O.dist = (double*)ctx->dist.p;
             O.lb_status = (unsigned long long*)ctx->lb_status.p;
+            O.lb_spin_limit = ctx->lb_spin_limit;
             O.row_ptr_out = (long long*)ctx->row_ptr.p;
             const int keep_max_1p = row_cap_1p < max_nb ? row_cap_1p : max_nb;
             onepass_fused_rbf = want_rbf && ctx->fuse_rbf && (K & 3) == 0 &&
@@ -731,7 +738,21 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (ctx->h_stats->err_status != 0)
         return fail(ctx, status_to_code(ctx->h_stats->err_status), "structure %d: %s", ctx->h_stats->err_struct,
                     dgnn_strerror(status_to_code(ctx->h_stats->err_status)));
-    if (ctx->h_stats->lb_timeout) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
+    if (ctx->h_stats->lb_timeout) {
+        // The look-back of the single-pass build waits for predecessor CTAs; if something else holds SMs (another
+        // stream of the process, an MPS client) the missing CTAs may never start within the spin bound and the row
+        // offsets are then wrong.  Redo the batch with count + scan + fill, which needs no co-residency.
+        if (ctx->onepass_skip) return fail(ctx, DGNN_ERR_CUDA, "internal: single-pass look-back timed out");
+        if (upload.armed) CU(cudaStreamSynchronize(ctx->copy_stream));
+        ctx->onepass_skip = true;
+        const int r = dgnn_build(ctx, b, out);
+        ctx->onepass_skip = false;
+        if (r == DGNN_OK) {
+            ctx->lb_fallbacks += 1;
+            ctx->info.onepass = 3;
+        }
+        return r;
+    }
     const int n_cell_structs = ctx->h_stats->n_cell_structs;
     int n_fallback_rows = ctx->h_stats->n_fallback_rows;
     const bool onepass_redo_all = onepass && ctx->h_stats->cap_overflow != 0;

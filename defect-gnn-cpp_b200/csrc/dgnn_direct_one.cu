@@ -32,7 +32,7 @@ __device__ __forceinline__ void dg_lb_store(unsigned long long* p, unsigned long
 // resolved prefix takes one to three L2 latencies.
 #define DG_LB_WIDE 2
 __device__ __forceinline__ long long dg_lookback(const unsigned long long* __restrict__ status, long long a, int lane,
-                                                 DgStats* __restrict__ stats) {
+                                                 DgStats* __restrict__ stats, unsigned spin_limit) {
     long long excl = 0;
     long long pos = a - 1;
     unsigned spins = 0;
@@ -68,7 +68,7 @@ __device__ __forceinline__ long long dg_lookback(const unsigned long long* __res
             }
         }
         if (retry) {
-            if (++spins > DG_LB_SPIN_LIMIT) {
+            if (++spins > spin_limit) {
                 if (lane == 0) atomicExch(&stats->lb_timeout, 1);
                 break;
             }
@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(256, MINB) k_direct_one(const DgDirectArgs A) 
             }
             const int total = __shfl_sync(FULL_MASK, incl, nwarps - 1);
             if (lane == 0) dg_lb_store(A.lb_status + chunk, DG_LB_AGG | (unsigned long long)total);
-            const long long excl = dg_lookback(A.lb_status, chunk, lane, A.stats);
+            const long long excl = dg_lookback(A.lb_status, chunk, lane, A.stats, A.lb_spin_limit > 0 ? (unsigned)A.lb_spin_limit : DG_LB_SPIN_LIMIT);
             if (lane == 0) {
                 dg_lb_store(A.lb_status + chunk, DG_LB_INC | (unsigned long long)(excl + total));
                 sh.arrived[par] = 0;  // next used two steps from now

@@ -164,6 +164,7 @@ struct DgDirectArgs {
     int skip_deg_le;                // fill pass: skip rows with deg_raw <= this (0: off), they are already written
     long long row_begin, row_end;   // k_direct: rows [row_begin, row_end) only (row_end = 0: all rows)
     int fill_hits_bulk;             // k_fill_hits: features through the bulk-copy engine (1) or st.global.cs (0)
+    int lb_spin_limit;              // single-pass build: look-back spins before giving up (0: default 2^22)
     int dyn_unit;                   // > 0: rows are handed out to warps in units of this many rows from *unit_ctr (zeroed)
     unsigned long long* unit_ctr;
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly

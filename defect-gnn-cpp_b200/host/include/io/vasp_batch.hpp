@@ -2,8 +2,9 @@
 // reference's one-file-at-a-time std::stringstream parser (src/io/vasp_parser.cpp:13-78; string variant
 // src/viz/wasm_bindings.cpp:91-116) is what starves the device, so files are parsed by a pool of threads with a
 // strtod tokenizer straight into the SoA buffers dgnn_build reads (graph::SoABatch).  Parser semantics are the
-// reference's: line 2 scale, lines 3-5 lattice rows (* scale), line 6 symbols, line 7 counts, line 8 Direct |
-// Cartesian (first letter), one triple per atom; Cartesian triples are converted with the inverse lattice;
+// reference's (io/poscar_rules.hpp): line 2 scale, lines 3-5 lattice rows (* scale), line 6 symbols, line 7 counts,
+// line 8 Direct iff it starts with 'd' / 'D', one triple per atom; Cartesian triples are converted as
+// cart * inverse(lattice), unscaled, like vasp_parser.cpp:72-75;
 // positions = lattice^T * frac exactly as crystal::Structure computes them (src/crystal/structure.cpp:17).
 #pragma once
 

@@ -1,6 +1,8 @@
 // io::load_vasp_batch -- multi-threaded POSCAR -> SoA ingest (see io/vasp_batch.hpp).
 #include "io/vasp_batch.hpp"
 
+#include "io/poscar_rules.hpp"
+
 #include <atomic>
 #include <cctype>
 #include <cstdio>
@@ -84,26 +86,11 @@ void parse_text(const char* text, size_t len, Parsed& out, const std::string& wh
     if (counts.empty() || static_cast<int>(counts.size()) != n_sym)
         throw std::runtime_error("parse_vasp: element / count lines do not match in " + what);
     need("mode");
-    auto first = [&]() {
-        for (const char* q = b; q < e; ++q)
-            if (!isspace(static_cast<unsigned char>(*q))) return static_cast<char>(tolower(static_cast<unsigned char>(*q)));
-        return '\0';
-    };
-    if (first() == 's') need("mode");  // Selective dynamics
-    const char m = first();
-    const bool cartesian = m == 'c' || m == 'k';
+    if (rules::is_selective(b, e)) need("mode");  // (see io/poscar_rules.hpp)
+    const bool cartesian = !rules::is_direct(b, e);
     const double* L = out.lattice;
-    // inverse lattice (for Cartesian input): frac = cart * L^-1  <=>  frac_k = sum_r cart_r * inv[r][k]
     double inv[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
-    if (cartesian) {
-        const double c00 = L[4] * L[8] - L[5] * L[7], c01 = L[5] * L[6] - L[3] * L[8], c02 = L[3] * L[7] - L[4] * L[6];
-        const double det = L[0] * c00 + L[1] * c01 + L[2] * c02;
-        if (det == 0.0) throw std::runtime_error("parse_vasp: singular lattice in " + what);
-        const double id = 1.0 / det;
-        inv[0] = c00 * id; inv[1] = (L[2] * L[7] - L[1] * L[8]) * id; inv[2] = (L[1] * L[5] - L[2] * L[4]) * id;
-        inv[3] = c01 * id; inv[4] = (L[0] * L[8] - L[2] * L[6]) * id; inv[5] = (L[2] * L[3] - L[0] * L[5]) * id;
-        inv[6] = c02 * id; inv[7] = (L[1] * L[6] - L[0] * L[7]) * id; inv[8] = (L[0] * L[4] - L[1] * L[3]) * id;
-    }
+    if (cartesian) rules::inverse3(L, inv);
     long total = 0;
     for (int n : counts) total += n;
     out.x.reserve(static_cast<size_t>(total));
@@ -115,11 +102,10 @@ void parse_text(const char* text, size_t len, Parsed& out, const std::string& wh
             need("coordinates");
             double f[3];
             if (read_doubles(b, e, f, 3) != 3) throw std::runtime_error("parse_vasp: bad coordinate line in " + what);
-            if (cartesian) {
-                const double cx = f[0] * scale, cy = f[1] * scale, cz = f[2] * scale;
-                f[0] = cx * inv[0] + cy * inv[3] + cz * inv[6];
-                f[1] = cx * inv[1] + cy * inv[4] + cz * inv[7];
-                f[2] = cx * inv[2] + cy * inv[5] + cz * inv[8];
+            if (cartesian) {  // frac = cart * inverse(lattice), coordinates unscaled (vasp_parser.cpp:72-75)
+                double g[3];
+                rules::cart_to_frac_row(static_cast<int64_t>(out.x.size()), total, f, inv, g);
+                f[0] = g[0]; f[1] = g[1]; f[2] = g[2];
             }
             // position = lattice^T * frac (structure.cpp:17): component k = (e0 + e1) + e2, e_r = L(r,k) f_r -- the
             // order of Eigen 3.4's vectorised 3-term reduction on x86-64 (pinned on oracle/_ref; same as the facade's Structure)

@@ -220,6 +220,20 @@ int facade_collate_batch(int64_t n_structs, const int64_t* atom_offsets, const d
     }
 }
 
+// io::parse_vasp of one file: lattice rows, fractional coordinates, species indices; returns the atom count via *n.
+int facade_parse_vasp(const char* path, double* lattice, double* frac, int* types, int64_t cap, int64_t* n) {
+    return guarded([&] {
+        const io::VASPStructure v = io::parse_vasp(path);
+        for (int i = 0; i < 3; ++i)
+            for (int j = 0; j < 3; ++j) lattice[3 * i + j] = v.lattice(i, j);
+        *n = v.frac_coords.rows();
+        for (int64_t i = 0; i < *n && i < cap; ++i) {
+            for (int j = 0; j < 3; ++j) frac[3 * i + j] = v.frac_coords(i, j);
+            types[i] = v.atom_types[static_cast<size_t>(i)];
+        }
+    });
+}
+
 // Bulk ingest: newline-separated file paths -> SoA arrays (io::load_vasp_batch).
 int facade_load_batch(const char* paths_nl, unsigned n_threads, int64_t atom_cap, int64_t struct_cap,
                       int64_t* atom_offsets, double* x, double* y, double* z, double* lattices, int* element,

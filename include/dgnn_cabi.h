@@ -214,7 +214,8 @@ typedef struct {
     int32_t rbf_fused;       /* 1: features were written by the fill pass's fused epilogue (rbf_ms is then 0) */
     int32_t hit_cap;         /* per-row hit-list slots the count pass wrote (0: the fill pass repeated the traversal) */
     int32_t onepass;         /* 1: single-pass build (no count pass; row offsets by look-back), 2: its estimated edge
-                              * arena was too small and the fill pass rewrote every row, 0: count + fill */
+                              * arena was too small and the fill pass rewrote every row, 3: its look-back timed out (SMs
+                              * held by other work) and the batch was rebuilt with count + fill, 0: count + fill */
     int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);

@@ -131,7 +131,7 @@ def test_bulk_poscar_ingest_matches_per_file_parser(tmp_path, facade, c1_structu
             if k % 2:
                 f.write("Selective dynamics\n")
             f.write("Cartesian\n" if cart else "Direct\n")
-            pts = (np.stack([x, y, z], axis=1) / scale) if cart else frac
+            pts = np.stack([x, y, z], axis=1) if cart else frac   # (the reference does not scale Cartesian coordinates)
             for p_ in pts:
                 f.write(" ".join(repr(float(v)) for v in p_) + (" T T T" if k % 2 else "") + "\n")
         paths.append(str(path))
@@ -169,6 +169,58 @@ def test_bulk_poscar_ingest_matches_per_file_parser(tmp_path, facade, c1_structu
                                        _p(Y, C.c_double), _p(Z, C.c_double), _p(Ls, C.c_double), _p(el, C.c_int32),
                                        C.byref(ns))
         assert rc_ != 0 and b"parse_vasp" in facade.facade_last_error()
+
+
+def test_parsers_keep_the_reference_semantics(tmp_path, facade, c1_structures):
+    """io::parse_vasp and io::load_vasp_batch against the reference's own parser + Structure (oracle/_ref, compiled
+    verbatim from src/io/vasp_parser.cpp and src/crystal/structure.cpp): Direct iff the mode line STARTS with d / D,
+    Cartesian coordinates converted with the scaled lattice's inverse and not scaled themselves -- bit for bit."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import ref_py as R
+    if not R.available():
+        pytest.skip("oracle/_ref not built")
+    i32p, i64p, dp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+    facade.facade_load_batch.argtypes = [C.c_char_p, C.c_uint, C.c_int64, C.c_int64, i64p, dp, dp, dp, dp, i32p, i64p]
+    facade.facade_parse_vasp.argtypes = [C.c_char_p, dp, dp, i32p, C.c_int64, i64p]
+    items = list(c1_structures.items())
+    cases = []
+    for k, mode_line in enumerate(["Direct", "direct", "Cartesian", "cartesian", "Kartesisch", " Direct", "", "Direct"]):
+        nm, (x, y, z, L, species, frac) = items[k % len(items)]
+        n = len(x) - (k % 2)                      # odd and even atom counts (Eigen's packet boundaries differ)
+        counts = np.bincount(species[:n])
+        scale = (1.0, 1.5, 0.7)[k % 3]
+        as_direct = mode_line[:1] in ("d", "D")
+        path = tmp_path / f"case{k}.vasp"
+        with open(path, "w") as f:
+            f.write(f"case {k}\n{scale!r}\n")
+            for r in L / scale:
+                f.write("  ".join(repr(float(v)) for v in r) + "\n")
+            f.write(" ".join(f"E{i}" for i in range(len(counts))) + "\n" + "  ".join(str(int(c)) for c in counts) + "\n")
+            f.write(mode_line + "\n")
+            pts = frac[:n] if as_direct else np.stack([x, y, z], axis=1)[:n]
+            for p_ in pts:
+                f.write(" ".join(repr(float(v)) for v in p_) + "\n")
+        cases.append((str(path), n))
+    for path, n in cases:
+        Lr, fr, tr = R.parse_vasp(path)
+        st = R.Structure(fr, Lr, tr, 3.0, 1)
+        pos_ref = st.neighbor_list().pos
+        st.close()
+        # per-file parser
+        Lf, ff, tf, nn = np.zeros(9), np.zeros((n, 3)), np.zeros(n, np.int32), C.c_int64()
+        assert facade.facade_parse_vasp(path.encode(), _p(Lf, C.c_double), _p(ff, C.c_double), _p(tf, C.c_int32), n,
+                                        C.byref(nn)) == 0, facade.facade_last_error()
+        assert nn.value == n and np.array_equal(tf, tr)
+        assert np.array_equal(Lf.reshape(3, 3).view(np.int64), Lr.view(np.int64)), path
+        assert np.array_equal(ff.view(np.int64), fr.view(np.int64)), path
+        # bulk ingest: positions as crystal::Structure computes them
+        offs, X, Y, Z = np.zeros(2, np.int64), np.zeros(n), np.zeros(n), np.zeros(n)
+        Ls, el, ns = np.zeros(9), np.zeros(n, np.int32), C.c_int64()
+        assert facade.facade_load_batch(path.encode(), 1, n, 1, _p(offs, C.c_int64), _p(X, C.c_double), _p(Y, C.c_double),
+                                        _p(Z, C.c_double), _p(Ls, C.c_double), _p(el, C.c_int32), C.byref(ns)) == 0
+        assert np.array_equal(Ls.view(np.int64), Lr.reshape(9).view(np.int64)), path
+        assert np.array_equal(np.stack([X, Y, Z], axis=1).view(np.int64), pos_ref.view(np.int64)), path
 
 
 # ---- GPU: reference-shaped API against the oracle -------------------------------------------------------------------

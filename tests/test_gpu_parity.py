@@ -302,7 +302,7 @@ def test_hit_list_and_traversal_fill_paths_agree(pkg, oracle, syn, hit_cap):
     ({"onepass": 1}, 1),                                      # single pass, row buffer / arena from the density estimate
     ({"onepass": 1, "onepass_row_cap": 64}, 1),               # most rows outgrow the row buffer -> completed by a fill pass
     ({"onepass": 1, "onepass_arena_scale": 0.25}, 2),         # arena estimate too small -> every row rewritten
-    ({"onepass": 1, "direct_min_blocks": 3}, 1),
+    ({"onepass": 1, "lb_spin_limit": 1}, 3),                  # look-back gives up at once -> rebuilt with count + fill
 ])
 def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
     """The single-pass build (k_direct<ONE>: look-back row offsets, no count pass) and its two recovery routes must
@@ -319,7 +319,9 @@ def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
                     syn.perovskite_supercell(4, 4, 4, seed=33)[:4], syn.perovskite_supercell(2, 2, 2, seed=34)[:4]])
     check_batch(gb, oracle, b, 8.0, None, dr=0.2)
     info = gb.info()
-    assert info.onepass == expect
+    # (a look-back only times out if it has to wait at all: with the spin limit at 1 that is near certain on the many
+    # chunks of the larger batch below, not guaranteed on this small one)
+    assert info.onepass == expect or (expect == 3 and info.onepass == 1)
     if opts.get("onepass_row_cap"):
         assert info.onepass_fallback_rows > 0
     check_batch(gb, oracle, b, 10.0, 20, dr=0.1)           # capped rows, K = 100
@@ -330,7 +332,12 @@ def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
     assert h0.n_edges == 0
     # a larger homogeneous batch: many chunks per CTA, look-back across CTAs
     big = syn.c2_batch(96, seed0=31000)
-    check_batch(gb, oracle, big, 8.0, None, dr=0.2)
+    seen = set()
+    for _ in range(3):
+        check_batch(gb, oracle, big, 8.0, None, dr=0.2)
+        seen.add(gb.info().onepass)
+    if expect == 3:
+        assert 3 in seen, "the timed-out look-back must have been redone with count + fill at least once"
     gb.close()
 
 
