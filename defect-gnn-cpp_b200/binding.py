@@ -26,7 +26,7 @@ EXPORTS = [
     "dgnn_copy_to_host", "dgnn_copy_edges_to_host", "dgnn_rbf_expand", "dgnn_rbf_expand_f64",
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
-    "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host",
+    "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host", "dgnn_host_alloc", "dgnn_host_free",
 ]
 
 

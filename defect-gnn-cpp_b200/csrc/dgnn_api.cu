@@ -306,6 +306,20 @@ void dgnn_destroy(dgnn_ctx* ctx) {
 
 void* dgnn_stream(dgnn_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
 
+int dgnn_host_alloc(size_t bytes, void** out) {
+    if (!out) return DGNN_ERR_INVALID_ARG;
+    *out = nullptr;
+    if (cudaMallocHost(out, bytes > 0 ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        *out = nullptr;
+        return DGNN_ERR_OOM;
+    }
+    return DGNN_OK;
+}
+void dgnn_host_free(void* p) {
+    if (p) cudaFreeHost(p);
+}
+
 // (dgnn_stream.cu) second context on the same device with the same options: the other arena of the streamed build
 dgnn_ctx* dgnn_internal_twin(dgnn_ctx* ctx) {
     if (!ctx) return nullptr;

@@ -38,6 +38,23 @@ struct SoABatch {
     SoABatch() : atom_offsets{0} {}
 };
 
+// The same layout in page-locked host memory (dgnn_host_alloc): inputs that cross PCIe asynchronously, written in
+// place by io::load_vasp_batch_pinned.  Move-only; frees its buffers on destruction.
+struct PinnedSoABatch {
+    int64_t n_structs = 0, n_atoms = 0;
+    int64_t* atom_offsets = nullptr;  // [S+1]
+    double *x = nullptr, *y = nullptr, *z = nullptr;  // [N]
+    double* lattice = nullptr;        // [9 S]
+    int* element = nullptr;           // [N]
+    PinnedSoABatch() = default;
+    PinnedSoABatch(int64_t n_structs, int64_t n_atoms);  // throws std::runtime_error if pinned memory is unavailable
+    ~PinnedSoABatch();
+    PinnedSoABatch(PinnedSoABatch&& o) noexcept;
+    PinnedSoABatch& operator=(PinnedSoABatch&& o) noexcept;
+    PinnedSoABatch(const PinnedSoABatch&) = delete;
+    PinnedSoABatch& operator=(const PinnedSoABatch&) = delete;
+};
+
 // Device-resident result of one batched build.  Pointers are DEVICE pointers owned by the builder; they stay valid
 // until the next build() on the same builder or its destruction.
 struct BatchedGraphs {
@@ -82,6 +99,7 @@ public:
 
     // Throws std::runtime_error with the C-ABI error text on failure; there is no CPU fallback.
     BatchedGraphs build(const SoABatch& batch, const BatchParams& params);
+    BatchedGraphs build(const PinnedSoABatch& batch, const BatchParams& params);  // asynchronous chunked upload
     BatchedGraphs build(const std::vector<const crystal::Structure*>& structures, const BatchParams& params);
 
     // Node features gathered on the device: x[i] = atom_embeddings.at(node_keys[i]); throws std::out_of_range where

@@ -21,4 +21,9 @@ void append_vasp_text(const char* text, size_t len, graph::SoABatch& batch);
 // Files parsed in parallel (n_threads = 0: hardware concurrency), appended in the order of `paths`.
 graph::SoABatch load_vasp_batch(const std::vector<std::string>& paths, unsigned n_threads = 0);
 
+// The same ingest into PAGE-LOCKED SoA buffers (graph::PinnedSoABatch): headers first (atom counts -> offsets), then the
+// coordinate lines are parsed straight into their final place in pinned memory, which BatchBuilder::build hands to
+// dgnn_build's chunked upload queue as is.  Needs the CUDA driver (pinned allocation): throws without a device.
+graph::PinnedSoABatch load_vasp_batch_pinned(const std::vector<std::string>& paths, unsigned n_threads = 0);
+
 }  // namespace defect_gnn::io

@@ -4,6 +4,7 @@
 #include "context.hpp"
 
 #include <limits>
+#include <utility>
 #include <stdexcept>
 
 namespace defect_gnn::graph {
@@ -35,14 +36,16 @@ BatchBuilder::~BatchBuilder() {
     if (impl_ && impl_->ctx) dgnn_destroy(impl_->ctx);
 }
 
-BatchedGraphs BatchBuilder::build(const SoABatch& batch, const BatchParams& p) {
+namespace {
+BatchedGraphs build_raw(dgnn_ctx* ctx, int64_t n_structs, const int64_t* atom_offsets, const double* x, const double* y,
+                        const double* z, const double* lattice, const BatchParams& p) {
     dgnn_batch b{};
-    b.n_structs = batch.n_structs();
-    b.atom_offsets = batch.atom_offsets.data();
-    b.x = batch.x.data();
-    b.y = batch.y.data();
-    b.z = batch.z.data();
-    b.lattice = batch.lattice.data();
+    b.n_structs = n_structs;
+    b.atom_offsets = atom_offsets;
+    b.x = x;
+    b.y = y;
+    b.z = z;
+    b.lattice = lattice;
     b.r_cutoff = p.r_cutoff;
     b.max_neighbors = p.max_neighbors >= std::numeric_limits<uint64_t>::max() ? DGNN_UNCAPPED
                                                                              : static_cast<uint64_t>(p.max_neighbors);
@@ -51,8 +54,8 @@ BatchedGraphs BatchBuilder::build(const SoABatch& batch, const BatchParams& p) {
     b.dr = p.dr;
     b.flags = p.dr > 0.0 ? 0u : DGNN_SKIP_RBF;
     dgnn_graphs g{};
-    int rc = dgnn_build(impl_->ctx, &b, &g);
-    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::build");
+    int rc = dgnn_build(ctx, &b, &g);
+    if (rc != DGNN_OK) detail::throw_status(ctx, rc, "BatchBuilder::build");
     BatchedGraphs out;
     out.n_structs = g.n_structs;
     out.n_atoms = g.n_atoms;
@@ -68,10 +71,63 @@ BatchedGraphs BatchBuilder::build(const SoABatch& batch, const BatchParams& p) {
     out.n_near_cutoff = g.n_near_cutoff;
     out.n_tie_rows = g.n_tie_rows;
     out.host_struct_edge_offsets.resize(static_cast<size_t>(g.n_structs) + 1);
-    rc = dgnn_copy_to_host(impl_->ctx, &g, nullptr, nullptr, nullptr, nullptr, nullptr,
-                           out.host_struct_edge_offsets.data());
-    if (rc != DGNN_OK) detail::throw_status(impl_->ctx, rc, "BatchBuilder::build");
+    rc = dgnn_copy_to_host(ctx, &g, nullptr, nullptr, nullptr, nullptr, nullptr, out.host_struct_edge_offsets.data());
+    if (rc != DGNN_OK) detail::throw_status(ctx, rc, "BatchBuilder::build");
     return out;
+}
+}  // namespace
+
+BatchedGraphs BatchBuilder::build(const SoABatch& batch, const BatchParams& p) {
+    return build_raw(impl_->ctx, batch.n_structs(), batch.atom_offsets.data(), batch.x.data(), batch.y.data(),
+                     batch.z.data(), batch.lattice.data(), p);
+}
+
+BatchedGraphs BatchBuilder::build(const PinnedSoABatch& batch, const BatchParams& p) {
+    return build_raw(impl_->ctx, batch.n_structs, batch.atom_offsets, batch.x, batch.y, batch.z, batch.lattice, p);
+}
+
+// ---- page-locked SoA buffers ------------------------------------------------------------------------------------------
+namespace {
+template <class T>
+T* pinned(int64_t n) {
+    void* p = nullptr;
+    if (dgnn_host_alloc(static_cast<size_t>(n > 0 ? n : 1) * sizeof(T), &p) != DGNN_OK || !p)
+        throw std::runtime_error("PinnedSoABatch: page-locked allocation failed (a CUDA device is required)");
+    return static_cast<T*>(p);
+}
+}  // namespace
+
+PinnedSoABatch::PinnedSoABatch(int64_t ns, int64_t na) : n_structs(ns), n_atoms(na) {
+    try {
+        atom_offsets = pinned<int64_t>(ns + 1);
+        x = pinned<double>(na);
+        y = pinned<double>(na);
+        z = pinned<double>(na);
+        lattice = pinned<double>(9 * ns);
+        element = pinned<int>(na);
+    } catch (...) {
+        this->~PinnedSoABatch();
+        throw;
+    }
+    atom_offsets[0] = 0;
+}
+PinnedSoABatch::~PinnedSoABatch() {
+    for (void* p : {(void*)atom_offsets, (void*)x, (void*)y, (void*)z, (void*)lattice, (void*)element})
+        if (p) dgnn_host_free(p);
+    atom_offsets = nullptr;
+    x = y = z = lattice = nullptr;
+    element = nullptr;
+}
+PinnedSoABatch::PinnedSoABatch(PinnedSoABatch&& o) noexcept { *this = std::move(o); }
+PinnedSoABatch& PinnedSoABatch::operator=(PinnedSoABatch&& o) noexcept {
+    if (this != &o) {
+        this->~PinnedSoABatch();
+        n_structs = o.n_structs; n_atoms = o.n_atoms;
+        atom_offsets = o.atom_offsets; x = o.x; y = o.y; z = o.z; lattice = o.lattice; element = o.element;
+        o.atom_offsets = nullptr; o.x = o.y = o.z = o.lattice = nullptr; o.element = nullptr;
+        o.n_structs = o.n_atoms = 0;
+    }
+    return *this;
 }
 
 BatchedGraphs BatchBuilder::build(const std::vector<const crystal::Structure*>& structures, const BatchParams& p) {

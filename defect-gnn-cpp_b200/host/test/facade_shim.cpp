@@ -262,6 +262,41 @@ int facade_load_batch(const char* paths_nl, unsigned n_threads, int64_t atom_cap
     });
 }
 
+// Pinned bulk ingest + build from the pinned buffers: returns positions / offsets and the edge total of the build.
+int facade_load_batch_pinned_build(const char* paths_nl, unsigned n_threads, int64_t atom_cap, int64_t struct_cap,
+                                   int64_t* atom_offsets, double* x, double* y, double* z, double* lattices, int* element,
+                                   int64_t* n_structs, double r_cutoff, uint64_t max_neighbors, int64_t* n_edges) {
+    return guarded([&] {
+        std::vector<std::string> paths;
+        std::string cur;
+        for (const char* q = paths_nl; *q; ++q) {
+            if (*q == '\n') {
+                if (!cur.empty()) paths.push_back(cur);
+                cur.clear();
+            } else {
+                cur.push_back(*q);
+            }
+        }
+        if (!cur.empty()) paths.push_back(cur);
+        graph::PinnedSoABatch b = io::load_vasp_batch_pinned(paths, n_threads);
+        if (b.n_structs > struct_cap || b.n_atoms > atom_cap) throw std::runtime_error("caps too small");
+        *n_structs = b.n_structs;
+        std::memcpy(atom_offsets, b.atom_offsets, sizeof(int64_t) * (b.n_structs + 1));
+        std::memcpy(x, b.x, sizeof(double) * b.n_atoms);
+        std::memcpy(y, b.y, sizeof(double) * b.n_atoms);
+        std::memcpy(z, b.z, sizeof(double) * b.n_atoms);
+        std::memcpy(lattices, b.lattice, sizeof(double) * 9 * b.n_structs);
+        std::memcpy(element, b.element, sizeof(int) * b.n_atoms);
+        graph::BatchBuilder builder(0);
+        graph::BatchParams p;
+        p.r_cutoff = r_cutoff;
+        p.max_neighbors = max_neighbors == UINT64_MAX ? SIZE_MAX : static_cast<size_t>(max_neighbors);
+        p.dr = 0.0;
+        const graph::BatchedGraphs g = builder.build(b, p);
+        *n_edges = g.n_edges;
+    });
+}
+
 // host logic of the sharded builder (no GPU): contiguous structure ranges balanced by predicted edges
 int facade_partition(int64_t n_structs, const int64_t* atom_offsets, const double* lattices, double r_cutoff,
                      int n_shards, int64_t* bounds, double* weights) {

@@ -247,6 +247,11 @@ typedef struct {
 int dgnn_build_stream(dgnn_ctx* ctx, dgnn_stream_source source, void* source_user, dgnn_stream_sink sink,
                       void* sink_user, dgnn_stream_info* info);
 
+/* Page-locked host memory for input staging (the chunked upload of dgnn_build only overlaps with the count pass when
+ * the host buffers are pinned).  Used by the facade's bulk POSCAR ingest, which parses straight into such buffers. */
+int dgnn_host_alloc(size_t bytes, void** out);
+void dgnn_host_free(void* p);
+
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
 void* dgnn_stream(dgnn_ctx* ctx);
 

@@ -223,6 +223,53 @@ def test_parsers_keep_the_reference_semantics(tmp_path, facade, c1_structures):
         assert np.array_equal(np.stack([X, Y, Z], axis=1).view(np.int64), pos_ref.view(np.int64)), path
 
 
+@pytest.mark.gpu
+def test_pinned_bulk_ingest_feeds_the_build(tmp_path, facade, oracle, c1_structures):
+    """io::load_vasp_batch_pinned (SURVEY 8f f3): coordinates parsed straight into page-locked SoA buffers, which
+    BatchBuilder::build uploads as they are -- same arrays as the pageable ingest, same graphs as the oracle."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    i32p, i64p, dp = C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_double)
+    facade.facade_load_batch.argtypes = [C.c_char_p, C.c_uint, C.c_int64, C.c_int64, i64p, dp, dp, dp, dp, i32p, i64p]
+    facade.facade_load_batch_pinned_build.argtypes = [C.c_char_p, C.c_uint, C.c_int64, C.c_int64, i64p, dp, dp, dp, dp,
+                                                      i32p, i64p, C.c_double, C.c_uint64, i64p]
+    items = list(c1_structures.items())
+    paths = []
+    for nm, (x, y, z, L, species, frac) in items:
+        counts = np.bincount(species)
+        path = tmp_path / f"{nm}.vasp"
+        with open(path, "w") as f:
+            f.write(f"fixture {nm}\n1.0\n")
+            for r in L:
+                f.write("  ".join(repr(float(v)) for v in r) + "\n")
+            f.write(" ".join(f"E{i}" for i in range(len(counts))) + "\n" + "  ".join(str(int(c)) for c in counts) + "\nDirect\n")
+            for p_ in frac:
+                f.write(" ".join(repr(float(v)) for v in p_) + "\n")
+        paths.append(str(path))
+    n_atoms = sum(len(it[1][0]) for it in items)
+
+    def bufs():
+        return (np.zeros(len(items) + 1, np.int64), np.zeros(n_atoms), np.zeros(n_atoms), np.zeros(n_atoms),
+                np.zeros((len(items), 9)), np.zeros(n_atoms, np.int32), C.c_int64())
+    o1, X1, Y1, Z1, L1, e1, n1 = bufs()
+    assert facade.facade_load_batch("\n".join(paths).encode(), 3, n_atoms, len(items), _p(o1, C.c_int64), _p(X1, C.c_double),
+                                    _p(Y1, C.c_double), _p(Z1, C.c_double), _p(L1, C.c_double), _p(e1, C.c_int32),
+                                    C.byref(n1)) == 0
+    for threads in (1, 5):
+        o2, X2, Y2, Z2, L2, e2, n2 = bufs()
+        ne = C.c_int64()
+        rc_ = facade.facade_load_batch_pinned_build("\n".join(paths).encode(), threads, n_atoms, len(items),
+                                                    _p(o2, C.c_int64), _p(X2, C.c_double), _p(Y2, C.c_double),
+                                                    _p(Z2, C.c_double), _p(L2, C.c_double), _p(e2, C.c_int32), C.byref(n2),
+                                                    8.0, C.c_uint64(2**64 - 1), C.byref(ne))
+        assert rc_ == 0, facade.facade_last_error()
+        for a, b in ((o1, o2), (X1, X2), (Y1, Y2), (Z1, Z2), (L1, L2), (e1, e2)):
+            assert np.array_equal(a, b)
+        want = int(oracle.batch_edge_counts(o1, X1, Y1, Z1, L1, 8.0).sum())
+        assert ne.value == want
+
+
 # ---- GPU: reference-shaped API against the oracle -------------------------------------------------------------------
 @pytest.mark.gpu
 def test_neighbor_list_facade_vs_oracle(facade, oracle, c1_structures):
