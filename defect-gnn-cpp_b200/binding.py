@@ -27,6 +27,7 @@ EXPORTS = [
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
     "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host", "dgnn_host_alloc", "dgnn_host_free",
+    "dgnn_collated_dlpack", "dgnn_live_exports", "dgnn_dlpack_release",
 ]
 
 
@@ -103,6 +104,52 @@ STREAM_SOURCE = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnBatch)
 STREAM_SINK = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.POINTER(DgnnGraphs), C.c_void_p)
 
 
+# ---- DLPack capsules around DLManagedTensor* produced by dgnn_collated_dlpack -----------------------------------------
+_CAPSULE_NAME = b"dltensor"
+_capsule_destructor_t = C.CFUNCTYPE(None, C.c_void_p)
+
+
+def _make_capsule_destructor():
+    api = C.pythonapi
+    api.PyCapsule_IsValid.argtypes = [C.c_void_p, C.c_char_p]
+    api.PyCapsule_IsValid.restype = C.c_int
+    api.PyCapsule_GetPointer.argtypes = [C.c_void_p, C.c_char_p]
+    api.PyCapsule_GetPointer.restype = C.c_void_p
+
+    def _destroy(capsule):
+        # a consumer renames the capsule to "used_dltensor" and takes over the deleter; an unconsumed one is ours
+        if api.PyCapsule_IsValid(capsule, _CAPSULE_NAME):
+            load_library().dgnn_dlpack_release(api.PyCapsule_GetPointer(capsule, _CAPSULE_NAME))
+    return _capsule_destructor_t(_destroy)
+
+
+_capsule_destructor = None
+
+
+class DLPackArray:
+    """One array of a collated batch as a DLPack producer (`__dlpack__` / `__dlpack_device__`): zero-copy into
+    torch.from_dlpack, cupy.from_dlpack ...  Each `__dlpack__` call exports a tensor that borrows the builder's arena;
+    until the consumer drops it, build() / collate() on that builder raise DGNN_ERR_BUSY instead of overwriting it."""
+
+    def __init__(self, builder, collated, which: int):
+        self._gb, self._c, self._which = builder, collated, which
+
+    def __dlpack_device__(self):
+        return (2, int(self._gb.device))  # kDLCUDA
+
+    def __dlpack__(self, stream=None, **_kw):
+        global _capsule_destructor
+        gb = self._gb
+        mt = C.c_void_p()
+        gb._check(gb.lib.dgnn_collated_dlpack(gb.h, C.byref(self._c), self._which, C.byref(mt)))
+        if _capsule_destructor is None:
+            _capsule_destructor = _make_capsule_destructor()
+        new = C.pythonapi.PyCapsule_New
+        new.argtypes = [C.c_void_p, C.c_char_p, _capsule_destructor_t]
+        new.restype = C.py_object
+        return new(mt, _CAPSULE_NAME, _capsule_destructor)
+
+
 class DgnnError(RuntimeError):
     def __init__(self, code: int, msg: str):
         super().__init__(f"dgnn error {code}: {msg}")
@@ -169,6 +216,12 @@ def load_library():
         L.dgnn_distance_tables.restype = C.c_int
         L.dgnn_copy_distance_tables_to_host.argtypes = [C.c_void_p, C.POINTER(DgnnDistanceTables), C.c_void_p, C.c_void_p]
         L.dgnn_copy_distance_tables_to_host.restype = C.c_int
+        L.dgnn_collated_dlpack.argtypes = [C.c_void_p, C.POINTER(DgnnCollated), C.c_int32, C.POINTER(C.c_void_p)]
+        L.dgnn_collated_dlpack.restype = C.c_int
+        L.dgnn_live_exports.argtypes = [C.c_void_p]
+        L.dgnn_live_exports.restype = C.c_int
+        L.dgnn_dlpack_release.argtypes = [C.c_void_p]
+        L.dgnn_dlpack_release.restype = None
         _lib = L
     return _lib
 
@@ -381,6 +434,18 @@ class GraphBuilder:
         self._check(self.lib.dgnn_collate(self.h, C.byref(g), _ptr(node_keys), _ptr(emb_keys), _ptr(emb_table),
                                           int(n_keys), int(F), INPUT_DEVICE if device_keys else 0, C.byref(out)))
         return out
+
+    def collated_dlpack(self, c: DgnnCollated) -> dict:
+        """DLPack producers for the collated batch: {"x", "edge_index", "batch", "edge_attr"} (absent arrays left out)."""
+        out = {"edge_index": DLPackArray(self, c, 1), "batch": DLPackArray(self, c, 2)}
+        if c.x:
+            out["x"] = DLPackArray(self, c, 0)
+        if c.edge_attr and c.K > 0:
+            out["edge_attr"] = DLPackArray(self, c, 3)
+        return out
+
+    def live_exports(self) -> int:
+        return int(self.lib.dgnn_live_exports(self.h))
 
     def collated_to_host(self, c: DgnnCollated):
         x = np.empty((c.n_nodes, c.F), dtype=np.float32) if c.x else None

@@ -2,6 +2,7 @@
 // No CPU fallback: every entry point needs a CUDA device; failures are reported as status codes + message.
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -29,6 +30,8 @@ struct BuildEvents {
 
 struct dgnn_ctx {
     int device = 0;
+    std::atomic<int> live_exports{0};  // DLPack tensors that borrow the arena (dgnn_collated_dlpack)
+    std::atomic<bool> zombie{false};   // dgnn_destroy was called while exports were alive: the last deleter frees
     std::vector<std::pair<std::string, double>> opt_log;  // options applied so far (replayed on the streaming twin)
     dgnn_ctx* twin = nullptr;                              // second arena of dgnn_build_stream (created on first use)
     cudaStream_t stream = nullptr;
@@ -227,6 +230,7 @@ const char* dgnn_strerror(int code) {
         case DGNN_ERR_DEGREE: return "row degree exceeds the supported maximum";
         case DGNN_ERR_TOO_LARGE: return "batch too large: split it";
         case DGNN_ERR_UNSUPPORTED: return "unsupported";
+        case DGNN_ERR_BUSY: return "DLPack exports of this context are still alive";
         default: return "unknown error";
     }
 }
@@ -277,6 +281,7 @@ int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out) {
 
 void dgnn_destroy(dgnn_ctx* ctx) {
     if (!ctx) return;
+    if (ctx->live_exports.load() > 0 && !ctx->zombie.exchange(true)) return;  // the last DLPack deleter comes back here
     if (ctx->twin) {
         dgnn_destroy(ctx->twin);
         ctx->twin = nullptr;
@@ -427,6 +432,8 @@ int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out) {
 int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     if (!ctx) return DGNN_ERR_INVALID_ARG;
     if (!b || !out) return fail(ctx, DGNN_ERR_INVALID_ARG, "null batch / output");
+    if (ctx->live_exports.load() > 0)
+        return fail(ctx, DGNN_ERR_BUSY, "dgnn_build: %d DLPack export(s) still borrow this context's buffers", ctx->live_exports.load());
     memset(out, 0, sizeof(*out));
     ctx->err.clear();
     ctx->last.valid = false;
@@ -1210,6 +1217,8 @@ int dgnn_collate(dgnn_ctx* ctx, const dgnn_graphs* g, const int32_t* node_keys, 
                  const double* emb_table, int32_t n_keys, int32_t F, uint32_t flags, dgnn_collated* out) {
     if (!ctx) return DGNN_ERR_INVALID_ARG;
     if (!out) return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collate: null output");
+    if (ctx->live_exports.load() > 0)
+        return fail(ctx, DGNN_ERR_BUSY, "dgnn_collate: %d DLPack export(s) still borrow this context's buffers", ctx->live_exports.load());
     memset(out, 0, sizeof(*out));
     {
         int r = consumer_begin(ctx, g, "dgnn_collate");
@@ -1422,4 +1431,74 @@ int dgnn_copy_distance_tables_to_host(dgnn_ctx* ctx, const dgnn_distance_tables_
     if (table_ptr) CU(cudaMemcpyAsync(table_ptr, t->table_ptr, (size_t)(t->n_atoms + 1) * 8, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     return DGNN_OK;
+}
+
+// ---- DLPack export of the collated batch (dlpack.h, the legacy "dltensor" capsule ABI) --------------------------------
+namespace {
+struct DgDLDevice { int32_t device_type, device_id; };
+struct DgDLDataType { uint8_t code, bits; uint16_t lanes; };
+struct DgDLTensor {
+    void* data;
+    DgDLDevice device;
+    int32_t ndim;
+    DgDLDataType dtype;
+    int64_t* shape;
+    int64_t* strides;
+    uint64_t byte_offset;
+};
+struct DgDLManagedTensor {
+    DgDLTensor dl_tensor;
+    void* manager_ctx;
+    void (*deleter)(DgDLManagedTensor*);
+};
+struct DgExport {
+    DgDLManagedTensor mt;
+    int64_t shape[2];
+    dgnn_ctx* owner;
+};
+void dg_export_deleter(DgDLManagedTensor* t) {
+    if (!t) return;
+    DgExport* e = static_cast<DgExport*>(t->manager_ctx);
+    dgnn_ctx* owner = e->owner;
+    delete e;
+    if (owner->live_exports.fetch_sub(1) == 1 && owner->zombie.load()) dgnn_destroy(owner);
+}
+}  // namespace
+
+int dgnn_live_exports(const dgnn_ctx* ctx) { return ctx ? ctx->live_exports.load() : 0; }
+
+int dgnn_collated_dlpack(dgnn_ctx* ctx, const dgnn_collated* c, int32_t which, void** managed_tensor) {
+    if (!ctx || !c || !managed_tensor) return DGNN_ERR_INVALID_ARG;
+    *managed_tensor = nullptr;
+    if (c->edge_index != (const int64_t*)ctx->col_ei.p)
+        return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collated_dlpack: not the result of the last dgnn_collate on this context");
+    DgExport* e = new (std::nothrow) DgExport();
+    if (!e) return DGNN_ERR_OOM;
+    DgDLTensor& t = e->mt.dl_tensor;
+    t.device = DgDLDevice{2 /* kDLCUDA */, ctx->device};
+    t.strides = nullptr;
+    t.byte_offset = 0;
+    t.shape = e->shape;
+    switch (which) {
+        case 0: t.data = (void*)c->x; t.ndim = 2; e->shape[0] = c->n_nodes; e->shape[1] = c->F; t.dtype = DgDLDataType{2, 32, 1}; break;
+        case 1: t.data = (void*)c->edge_index; t.ndim = 2; e->shape[0] = 2; e->shape[1] = c->n_edges; t.dtype = DgDLDataType{0, 64, 1}; break;
+        case 2: t.data = (void*)c->batch; t.ndim = 1; e->shape[0] = c->n_nodes; e->shape[1] = 1; t.dtype = DgDLDataType{0, 64, 1}; break;
+        case 3: t.data = (void*)c->edge_attr; t.ndim = 2; e->shape[0] = c->n_edges; e->shape[1] = c->K; t.dtype = DgDLDataType{2, 32, 1}; break;
+        default: delete e; return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collated_dlpack: which must be 0..3");
+    }
+    if (!t.data && !(e->shape[0] == 0 || (t.ndim == 2 && e->shape[1] == 0))) {
+        delete e;
+        return fail(ctx, DGNN_ERR_INVALID_ARG, "dgnn_collated_dlpack: this array was not produced by the collate call");
+    }
+    e->owner = ctx;
+    e->mt.manager_ctx = e;
+    e->mt.deleter = dg_export_deleter;
+    ctx->live_exports.fetch_add(1);
+    *managed_tensor = &e->mt;
+    return DGNN_OK;
+}
+
+void dgnn_dlpack_release(void* managed_tensor) {
+    DgDLManagedTensor* t = static_cast<DgDLManagedTensor*>(managed_tensor);
+    if (t && t->deleter) t->deleter(t);
 }

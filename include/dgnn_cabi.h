@@ -46,7 +46,8 @@ enum {
     DGNN_ERR_UNWRAPPED = -7,     /* atoms lie absurdly far outside the unit cell (halo grid too large) */
     DGNN_ERR_DEGREE = -8,        /* a row has more neighbours than the sorter supports (see DGNN_MAX_DEGREE) */
     DGNN_ERR_TOO_LARGE = -9,     /* batch exceeds 2^31-1 atoms / image-cloud points / cells: split it */
-    DGNN_ERR_UNSUPPORTED = -10
+    DGNN_ERR_UNSUPPORTED = -10,
+    DGNN_ERR_BUSY = -11          /* DLPack exports of this ctx's buffers are still alive (see dgnn_collated_dlpack) */
 };
 
 #define DGNN_MAX_DEGREE 4096
@@ -155,6 +156,17 @@ typedef struct {
 int dgnn_collate(dgnn_ctx* ctx, const dgnn_graphs* g, const int32_t* node_keys, const int32_t* emb_keys,
                  const double* emb_table, int32_t n_keys, int32_t F, uint32_t flags, dgnn_collated* out);
 int dgnn_copy_collated_to_host(dgnn_ctx* ctx, const dgnn_collated* c, float* x, int64_t* edge_index, int64_t* batch);
+
+/* f1, zero-copy hand-over: one array of the collated batch as a DLPack tensor (DLManagedTensor*, dlpack.h ABI of the
+ * "dltensor" capsule that torch.from_dlpack / cupy.from_dlpack / jax consume; kDLCUDA, row-major, no strides).
+ * which: 0 = x [n_nodes, F] f32, 1 = edge_index [2, n_edges] i64, 2 = batch [n_nodes] i64, 3 = edge_attr [n_edges, K] f32.
+ * The tensor BORROWS the ctx arena: while any export is alive (its deleter has not run) dgnn_build / dgnn_collate on
+ * this ctx fail with DGNN_ERR_BUSY instead of overwriting memory a consumer still reads, and dgnn_destroy defers the
+ * release of the context to the last deleter.  dgnn_live_exports tells how many are outstanding. */
+int dgnn_collated_dlpack(dgnn_ctx* ctx, const dgnn_collated* c, int32_t which, void** managed_tensor);
+int dgnn_live_exports(const dgnn_ctx* ctx);
+/* runs the tensor's deleter (for producers whose capsule was never consumed) */
+void dgnn_dlpack_release(void* managed_tensor);
 
 /* f4: the viewer's flat getters (wasm_bindings.cpp:206-294) in one kernel + one D2H per array: sources / targets
  * [E] int32 (atom indices local to the structure), distances [E] float32, displacements [3E] float32

@@ -163,6 +163,61 @@ def test_gpu_edge_views_and_clouds_match_restatement(gpu_builder, gpu_builder_ce
 
 
 @pytest.mark.gpu
+def test_gpu_collated_batch_dlpack_zero_copy(pkg, oracle, syn):
+    """f1: the collated batch goes to torch through DLPack without a copy (same device pointers), with the dtypes of the
+    Python consumer (utilities.py:69-71); live exports pin the arena: build / collate refuse to overwrite it."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    gb = pkg.GraphBuilder(0)
+    b = _mixed_batch(syn)
+    g = gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=8.0, max_neighbors=oracle.UNCAPPED, rbf_r_cutoff=8.0, dr=0.2)
+    h = gb.to_host(g)
+    keys = (np.arange(b.n_atoms) % 5).astype(np.int32)
+    emb = _emb(keys=range(0, 5))
+    ek = np.array(sorted(emb), dtype=np.int32)
+    et = np.stack([emb[int(k)] for k in ek])
+    c = gb.collate(keys, ek, et)
+    X, ei, batch = gb.collated_to_host(c)
+    prod = gb.collated_dlpack(c)
+    t = {k: torch.from_dlpack(v) for k, v in prod.items()}
+    assert gb.live_exports() == 4
+    assert t["x"].dtype == torch.float32 and t["edge_attr"].dtype == torch.float32
+    assert t["edge_index"].dtype == torch.int64 and t["batch"].dtype == torch.int64
+    assert tuple(t["x"].shape) == (b.n_atoms, 92) and tuple(t["edge_index"].shape) == (2, h.n_edges)
+    assert tuple(t["edge_attr"].shape) == (h.n_edges, 40) and tuple(t["batch"].shape) == (b.n_atoms,)
+    assert t["x"].data_ptr() == c.x and t["edge_index"].data_ptr() == c.edge_index          # zero copy
+    assert t["edge_attr"].data_ptr() == g.rbf and t["batch"].data_ptr() == c.batch
+    assert all(v.device.type == "cuda" and v.device.index == 0 for v in t.values())
+    assert np.array_equal(t["x"].cpu().numpy(), X) and np.array_equal(t["edge_index"].cpu().numpy(), ei)
+    assert np.array_equal(t["batch"].cpu().numpy(), batch) and np.array_equal(t["edge_attr"].cpu().numpy(), h.rbf)
+    # the arena is pinned while consumers hold the tensors
+    with pytest.raises(pkg.binding.DgnnError) as e1:
+        gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=5.0, max_neighbors=12, skip_rbf=True)
+    assert "still borrow" in str(e1.value)
+    with pytest.raises(pkg.binding.DgnnError):
+        gb.collate()
+    del t
+    import gc
+    gc.collect()
+    assert gb.live_exports() == 0
+    # an exported-but-never-consumed capsule releases its pin when it dies
+    cap = prod["x"].__dlpack__()
+    assert gb.live_exports() == 1
+    del cap
+    gc.collect()
+    assert gb.live_exports() == 0
+    gb.build(b.atom_offsets, b.x, b.y, b.z, b.lattices, r_cutoff=5.0, max_neighbors=12, skip_rbf=True)   # free again
+    # destroying the builder under a live export defers the release to the tensor's deleter
+    c = gb.collate()
+    keep = torch.from_dlpack(gb.collated_dlpack(c)["batch"])
+    gb.close()
+    assert int(keep.sum().item()) == int(batch.sum())
+    del keep
+    gc.collect()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("which", ["direct", "cell"])
 def test_gpu_distance_tables_match_restatement(gpu_builder, gpu_builder_cell, oracle, syn, which):
     """f2: the Betti caller's (deg+1)^2 pairwise-distance tables (ripser_wrapper.cpp:60-66), bit-exact in fp64 against
