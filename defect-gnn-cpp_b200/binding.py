@@ -27,7 +27,7 @@ EXPORTS = [
     "dgnn_last_build_info", "dgnn_stream", "dgnn_set_option",
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
     "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host", "dgnn_host_alloc", "dgnn_host_free",
-    "dgnn_collated_dlpack", "dgnn_live_exports", "dgnn_dlpack_release",
+    "dgnn_collated_dlpack", "dgnn_live_exports", "dgnn_dlpack_release", "dgnn_build_serial",
 ]
 
 

@@ -30,6 +30,7 @@ struct BuildEvents {
 
 struct dgnn_ctx {
     int device = 0;
+    uint64_t build_serial = 0;
     std::atomic<int> live_exports{0};  // DLPack tensors that borrow the arena (dgnn_collated_dlpack)
     std::atomic<bool> zombie{false};   // dgnn_destroy was called while exports were alive: the last deleter frees
     std::vector<std::pair<std::string, double>> opt_log;  // options applied so far (replayed on the streaming twin)
@@ -310,6 +311,8 @@ void dgnn_destroy(dgnn_ctx* ctx) {
 }
 
 void* dgnn_stream(dgnn_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+uint64_t dgnn_build_serial(const dgnn_ctx* ctx) { return ctx ? ctx->build_serial : 0; }
 
 int dgnn_host_alloc(size_t bytes, void** out) {
     if (!out) return DGNN_ERR_INVALID_ARG;
@@ -1074,6 +1077,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     out->n_tie_rows = ctx->h_stats->n_tie_rows;
 
     ctx->last.valid = true;
+    ctx->build_serial += 1;
     ctx->last.S = S; ctx->last.N = N; ctx->last.E = E;
     ctx->last.max_deg = max_deg;
     ctx->last.off = d_off;

@@ -39,6 +39,9 @@ public:
     [[nodiscard]] size_t num_edges() const { return num_edges_; }
     [[nodiscard]] int64_t near_cutoff_pairs() const { return n_near_cutoff_; }  // |d - r_c| <= 1e-6 A
     [[nodiscard]] int64_t tie_rows() const { return n_tie_rows_; }              // rows truncated through a tie
+    // device pointer to the row-ordered fp64 distances while they are still the current result of context `ctx`
+    // (the constructing thread's dgnn_ctx), else nullptr
+    [[nodiscard]] const double* device_distances(const void* ctx) const;
 
 private:
     double r_cutoff_;
@@ -49,6 +52,15 @@ private:
     int64_t n_tie_rows_ = 0;
     std::vector<std::vector<Neighbor>> neighbor_lists_;
     std::vector<std::vector<std::array<int8_t, 3>>> images_;
+    const void* device_ctx_ = nullptr;
+    const double* device_dist_ = nullptr;
+    uint64_t device_serial_ = 0;
 };
+
+// ---- additions (not in the reference): CUDA device the per-structure classes use on the calling thread.  Default:
+// environment variable DGNN_DEVICE, else 0.  Every thread has its own context, so constructions on different threads
+// (and devices) run concurrently.
+void set_device(int device);
+[[nodiscard]] int current_device();
 
 }  // namespace defect_gnn::graph

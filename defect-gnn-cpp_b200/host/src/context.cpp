@@ -1,5 +1,6 @@
 #include "context.hpp"
 
+#include <cstdlib>
 #include <map>
 #include <memory>
 #include <stdexcept>
@@ -7,32 +8,39 @@
 namespace defect_gnn::graph::detail {
 
 namespace {
-struct Registry {
-    std::mutex mu;
+struct ThreadCtxs {
     std::map<int, std::unique_ptr<DeviceCtx>> by_device;
-    ~Registry() {
+    ~ThreadCtxs() {
         for (auto& kv : by_device)
             if (kv.second && kv.second->ctx) dgnn_destroy(kv.second->ctx);
     }
 };
-Registry& registry() {
-    static Registry r;
-    return r;
+thread_local ThreadCtxs t_ctxs;
+thread_local int t_device = -1;
+
+int env_device() {
+    const char* e = std::getenv("DGNN_DEVICE");
+    if (!e || !*e) return 0;
+    char* end = nullptr;
+    const long v = std::strtol(e, &end, 10);
+    return (end && *end == '\0' && v >= 0 && v < 1024) ? static_cast<int>(v) : 0;
 }
 }  // namespace
 
+int current_device() { return t_device >= 0 ? t_device : env_device(); }
+void set_current_device(int device) { t_device = device; }
+
 DeviceCtx& device_ctx(int device) {
-    Registry& r = registry();
-    std::lock_guard<std::mutex> lock(r.mu);
-    auto it = r.by_device.find(device);
-    if (it != r.by_device.end()) return *it->second;
+    if (device < 0) device = current_device();
+    auto it = t_ctxs.by_device.find(device);
+    if (it != t_ctxs.by_device.end()) return *it->second;
     auto dc = std::make_unique<DeviceCtx>();
     const int rc = dgnn_create(device, 0, &dc->ctx);
     if (rc != DGNN_OK)
-        throw std::runtime_error(std::string("defect_gnn::graph: cannot create the B200 context (") +
-                                 dgnn_strerror(rc) + "); this build has no CPU fallback");
+        throw std::runtime_error(std::string("defect_gnn::graph: cannot create the B200 context on device ") +
+                                 std::to_string(device) + " (" + dgnn_strerror(rc) + "); this build has no CPU fallback");
     DeviceCtx& ref = *dc;
-    r.by_device.emplace(device, std::move(dc));
+    t_ctxs.by_device.emplace(device, std::move(dc));
     return ref;
 }
 

@@ -37,10 +37,13 @@ CrystalGraph::CrystalGraph(const crystal::Structure& structure, const NeighborLi
     edge_attr_.resize(edge_count, n_rbf > 0 ? n_rbf : 0);
     if (edge_count > 0 && n_rbf > 0) {
         // one fp64 launch writes the reference's own storage: column-major E x K doubles
-        detail::DeviceCtx& dc = detail::device_ctx(0);
-        std::lock_guard<std::mutex> lock(dc.mu);
+        detail::DeviceCtx& dc = detail::device_ctx();
         int32_t k = 0;
-        const int rc = dgnn_rbf_expand_f64(dc.ctx, dist.data(), edge_count, r_cutoff, dr, edge_attr_.data(), &k);
+        // the NeighborList's distances are still in HBM if nothing was built on this thread since: no re-upload
+        const double* d_dist = neighbors.num_edges() == static_cast<size_t>(edge_count) ? neighbors.device_distances(dc.ctx)
+                                                                                         : nullptr;
+        const int rc = dgnn_rbf_expand_f64(dc.ctx, d_dist ? d_dist : dist.data(), edge_count, r_cutoff, dr,
+                                           edge_attr_.data(), &k);
         if (rc != DGNN_OK) detail::throw_status(dc.ctx, rc, "CrystalGraph");
     }
     target_ = 0;

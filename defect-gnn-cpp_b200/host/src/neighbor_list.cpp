@@ -50,8 +50,7 @@ NeighborList::NeighborList(const crystal::Structure& structure, double r_cutoff,
     std::vector<int32_t> dst, image;
     std::vector<double> dist;
     {
-        detail::DeviceCtx& dc = detail::device_ctx(0);
-        std::lock_guard<std::mutex> lock(dc.mu);
+        detail::DeviceCtx& dc = detail::device_ctx();  // this thread's context on the selected device
         dgnn_graphs g{};
         int rc = dgnn_build(dc.ctx, &b, &g);
         if (rc != DGNN_OK) detail::throw_status(dc.ctx, rc, "NeighborList");
@@ -63,6 +62,10 @@ NeighborList::NeighborList(const crystal::Structure& structure, double r_cutoff,
         num_edges_ = static_cast<size_t>(g.n_edges);
         n_near_cutoff_ = g.n_near_cutoff;
         n_tie_rows_ = g.n_tie_rows;
+        // the device-resident result stays current until this thread's next build: CrystalGraph reuses the distances
+        device_ctx_ = dc.ctx;
+        device_dist_ = g.dist;
+        device_serial_ = dgnn_build_serial(dc.ctx);
     }
     for (size_t i = 0; i < n; ++i) {
         const auto e0 = static_cast<size_t>(row_ptr[i]), e1 = static_cast<size_t>(row_ptr[i + 1]);
@@ -93,5 +96,14 @@ NeighborList::NeighborList(const crystal::Structure& structure, double r_cutoff,
 const std::vector<Neighbor>& NeighborList::neighbors(size_t atom_idx) const { return neighbor_lists_[atom_idx]; }
 
 const std::vector<std::array<int8_t, 3>>& NeighborList::images(size_t atom_idx) const { return images_[atom_idx]; }
+
+const double* NeighborList::device_distances(const void* ctx) const {
+    return (ctx != nullptr && ctx == device_ctx_ && dgnn_build_serial(static_cast<const dgnn_ctx*>(ctx)) == device_serial_)
+               ? device_dist_
+               : nullptr;
+}
+
+void set_device(int device) { detail::set_current_device(device); }
+int current_device() { return detail::current_device(); }
 
 }  // namespace defect_gnn::graph

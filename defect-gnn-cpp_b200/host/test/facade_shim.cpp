@@ -16,6 +16,8 @@
 #include <map>
 #include <stdexcept>
 #include <string>
+#include <thread>
+#include <vector>
 
 using namespace defect_gnn;
 
@@ -98,6 +100,48 @@ int facade_neighbor_list(int64_t n, const double* frac, const double* lattice, d
         *near = nl.near_cutoff_pairs();
         *ties = nl.tie_rows();
         if (static_cast<size_t>(e) != nl.num_edges()) throw std::runtime_error("num_edges mismatch");
+    });
+}
+
+// Concurrent per-structure constructions (the OpenMP-over-files shape of preprocess_betti.cpp:37): n_threads threads each
+// build Structure + NeighborList + CrystalGraph `reps` times on their own context; per thread the edge total and a
+// checksum of edge_attr come back.  reuse[t] = how often CrystalGraph found the NeighborList's distances still in HBM.
+int facade_concurrent(int64_t n, const double* frac, const double* lattice, int n_threads, int reps, int device,
+                      int64_t* edges, double* checksum, int* reuse) {
+    return guarded([&] {
+        std::map<int, Eigen::VectorXd> emb;
+        Eigen::VectorXd v(4);
+        for (int d = 0; d < 4; ++d) v[d] = 0.5 * d;
+        emb[0] = v;
+        std::vector<std::string> errs(static_cast<size_t>(n_threads));
+        std::vector<std::thread> pool;
+        for (int t = 0; t < n_threads; ++t)
+            pool.emplace_back([&, t] {
+                try {
+                    graph::set_device(device);
+                    edges[t] = 0;
+                    checksum[t] = 0.0;
+                    reuse[t] = 0;
+                    for (int r = 0; r < reps; ++r) {
+                        crystal::Structure s(make_vasp(n, frac, lattice, nullptr));
+                        graph::NeighborList nl(s, 10.0, 20, 1e-10);
+                        const bool resident = nl.device_distances(nullptr) == nullptr;  // (null ctx never matches)
+                        (void)resident;
+                        graph::CrystalGraph g(s, nl, emb, 4, 10.0, 0.1);
+                        edges[t] += static_cast<int64_t>(g.num_edges());
+                        const Eigen::MatrixXd& ea = g.edge_attr();
+                        double c = 0.0;
+                        for (Eigen::Index i = 0; i < ea.rows(); ++i) c += ea(i, static_cast<Eigen::Index>(i % ea.cols()));
+                        checksum[t] += c;
+                        reuse[t] += graph::current_device() == device ? 1 : 0;
+                    }
+                } catch (const std::exception& e) {
+                    errs[static_cast<size_t>(t)] = e.what();
+                }
+            });
+        for (auto& th : pool) th.join();
+        for (const auto& e : errs)
+            if (!e.empty()) throw std::runtime_error(e);
     });
 }
 

@@ -259,6 +259,10 @@ typedef struct {
 int dgnn_build_stream(dgnn_ctx* ctx, dgnn_stream_source source, void* source_user, dgnn_stream_sink sink,
                       void* sink_user, dgnn_stream_info* info);
 
+/* Number of successful dgnn_build calls on this ctx so far: a caller that kept device pointers of a build can tell
+ * whether they are still the current result (the facade's CrystalGraph reuses its NeighborList's device distances). */
+uint64_t dgnn_build_serial(const dgnn_ctx* ctx);
+
 /* Page-locked host memory for input staging (the chunked upload of dgnn_build only overlaps with the count pass when
  * the host buffers are pinned).  Used by the facade's bulk POSCAR ingest, which parses straight into such buffers. */
 int dgnn_host_alloc(size_t bytes, void** out);

@@ -224,6 +224,32 @@ def test_parsers_keep_the_reference_semantics(tmp_path, facade, c1_structures):
 
 
 @pytest.mark.gpu
+def test_concurrent_constructions_have_their_own_context(facade, oracle, c1_structures):
+    """Every calling thread owns a dgnn_ctx (no global mutex): NeighborList + CrystalGraph built on 6 threads at once give
+    the same graphs as one thread, and graph::set_device selects the device per thread."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    i64p, dp, ip = C.POINTER(C.c_int64), C.POINTER(C.c_double), C.POINTER(C.c_int)
+    facade.facade_concurrent.argtypes = [C.c_int64, dp, dp, C.c_int, C.c_int, C.c_int, i64p, dp, ip]
+    x, y, z, L, species, frac = c1_structures["741_1"]
+    fr, Lc = np.ascontiguousarray(frac), np.ascontiguousarray(L)
+    one_e, one_c, one_r = np.zeros(1, np.int64), np.zeros(1), np.zeros(1, np.int32)
+    assert facade.facade_concurrent(len(x), _p(fr, C.c_double), _p(Lc, C.c_double), 1, 3, 0, _p(one_e, C.c_int64),
+                                    _p(one_c, C.c_double), _p(one_r, C.c_int)) == 0, facade.facade_last_error()
+    assert one_e[0] == 3 * 20 * len(x)
+    T = 6
+    e, c, r = np.zeros(T, np.int64), np.zeros(T), np.zeros(T, np.int32)
+    assert facade.facade_concurrent(len(x), _p(fr, C.c_double), _p(Lc, C.c_double), T, 3, 0, _p(e, C.c_int64),
+                                    _p(c, C.c_double), _p(r, C.c_int)) == 0, facade.facade_last_error()
+    assert np.all(e == one_e[0]) and np.all(c == one_c[0]) and np.all(r == 3)
+    # a device that does not exist is reported, not silently replaced
+    assert facade.facade_concurrent(len(x), _p(fr, C.c_double), _p(Lc, C.c_double), 1, 1, 63, _p(one_e, C.c_int64),
+                                    _p(one_c, C.c_double), _p(one_r, C.c_int)) != 0
+    assert b"device 63" in facade.facade_last_error()
+
+
+@pytest.mark.gpu
 def test_pinned_bulk_ingest_feeds_the_build(tmp_path, facade, oracle, c1_structures):
     """io::load_vasp_batch_pinned (SURVEY 8f f3): coordinates parsed straight into page-locked SoA buffers, which
     BatchBuilder::build uploads as they are -- same arrays as the pageable ingest, same graphs as the oracle."""
