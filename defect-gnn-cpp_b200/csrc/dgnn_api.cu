@@ -131,8 +131,21 @@ void dgnn_internal_set_error(dgnn_ctx* ctx, const char* msg) {
     if (ctx) ctx->err = msg ? msg : "";
 }
 
+// Public options (include/dgnn_cabi.h): cell_frac, direct_max_atoms, hit_cap, onepass, fuse_rbf, upload_chunks, cell32,
+// sym_count.  Everything else is a tuning / testing knob and has to be asked for as "tune.<name>".
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     if (!ctx || !name) return DGNN_ERR_INVALID_ARG;
+    const char* full_name = name;
+    const bool tune = !strncmp(name, "tune.", 5);
+    if (tune) {
+        name += 5;
+    } else {
+        static const char* const kPublic[] = {"cell_frac", "direct_max_atoms", "hit_cap", "onepass",
+                                              "fuse_rbf",  "upload_chunks",    "cell32",  "sym_count"};
+        bool ok = false;
+        for (const char* q : kPublic) ok = ok || !strcmp(name, q);
+        if (!ok) return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s' (tuning knobs are spelled tune.<name>)", name);
+    }
     if (!strcmp(name, "cell_frac")) {
         if (!(value >= 0.05 && value <= 4.0)) return fail(ctx, DGNN_ERR_INVALID_ARG, "cell_frac out of range");
         ctx->cell_frac = value;
@@ -148,9 +161,6 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else if (!strcmp(name, "traverse_grid_mult")) {
         if (!(value >= 1 && value <= 64)) return fail(ctx, DGNN_ERR_INVALID_ARG, "traverse_grid_mult out of range");
         ctx->traverse_grid_mult = (int)value;
-    } else if (!strcmp(name, "direct_min_blocks")) {
-        if (!(value >= 2 && value <= 3)) return fail(ctx, DGNN_ERR_INVALID_ARG, "direct_min_blocks must be 2 or 3");
-        ctx->direct_min_blocks = (int)value;  // register budget of the direct kernels: 128 (2) or 80 (3) per thread
     } else if (!strcmp(name, "sort_buckets")) {
         const int v = (int)value;
         if (!(v == 0 || (v >= 32 && v <= 2048 && (v & (v - 1)) == 0)))
@@ -202,8 +212,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
     } else {
         return fail(ctx, DGNN_ERR_INVALID_ARG, "unknown option '%s'", name);
     }
-    ctx->opt_log.emplace_back(name, value);
-    if (ctx->twin) dgnn_set_option(ctx->twin, name, value);
+    ctx->opt_log.emplace_back(full_name, value);
+    if (ctx->twin) dgnn_set_option(ctx->twin, full_name, value);
     return DGNN_OK;
 }
 

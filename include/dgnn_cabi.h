@@ -271,11 +271,19 @@ void dgnn_host_free(void* p);
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
 void* dgnn_stream(dgnn_ctx* ctx);
 
-/* Tuning knobs (optional).  cell_frac: target grid-cell width as a fraction of r_cutoff (default 0.5);
- * direct_max_atoms: structures with more atoms use the cell-list path instead of the direct path (default 2048);
- * hit_cap: per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off);
- * onepass: single-pass build (no count pass) of batches without cell-list structures: -1 auto (small batches),
- * 0 off (count + fill), 1 wherever legal. */
+/* Options (all optional; defaults are the measured best):
+ *   cell_frac         target grid-cell width of the cell-list path as a fraction of r_cutoff (default 0.5)
+ *   direct_max_atoms  structures with more atoms use the cell-list path instead of the direct path (default 2048)
+ *   hit_cap           per-row hit-list slots recorded by the count pass (-1 auto from the density, 0 off)
+ *   onepass           single-pass build (no count pass) of batches without cell-list structures: -1 auto (small
+ *                     batches), 0 off (count + fill), 1 wherever legal
+ *   fuse_rbf          1 (default): features written by the fill pass's epilogue; 0: separate RBF launch
+ *   upload_chunks     host inputs cross PCIe in this many structure-aligned chunks behind the count pass (default 4)
+ *   cell32            1 (default): cell-list structures use fp32 tiles staged in shared memory with the fp64 decision in
+ *                     a guard band; 0: the fp64 traversal (A/B reference)
+ *   sym_count         1 (default): the count pass sweeps j >= i and decides both directions of a pair
+ * Tuning and testing knobs (tile sizes, sort buckets, look-back spin limit ...) are spelled "tune.<name>"; they are
+ * listed next to dgnn_set_option in csrc/dgnn_api.cu and are not part of the interface. */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus

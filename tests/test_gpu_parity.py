@@ -189,11 +189,11 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
     o = oracle.neighbor_list(x, y, z, L, 8.0, oracle.UNCAPPED, 1e-10, oracle.ALGO_CELLLIST)
     # default = fp32 tiles staged in shared memory (dgnn_cell32.cu); cell32 = 0 = the fp64 traversal (staged with
     # tile_limit > 0, else straight from the L2-resident cloud), with and without hit lists
-    for opts in ({}, {"tile_target": 512, "src_target": 48}, {"tile_target": 4096, "src_target": 1024}, {"cell_frac": 0.3},
-                 {"cell_frac": 1.0}, {"cell_frac": 0.3, "tile_target": 256, "src_target": 16},
-                 {"cell32": 0}, {"cell32": 0, "tile_limit": 4096}, {"cell32": 0, "tile_limit": 4096, "tile_target": 512, "src_target": 48},
-                 {"cell32": 0, "tile_limit": 4096, "hit_cap": 0}, {"cell32": 0, "hit_cap": 0}, {"cell32": 0, "hit_cap": 160},
-                 {"cell32": 0, "tile_limit": 4096, "hit_cap": 160}, {"cell32": 0, "cell_frac": 0.3},
+    for opts in ({}, {"tune.tile_target": 512, "tune.src_target": 48}, {"tune.tile_target": 4096, "tune.src_target": 1024}, {"cell_frac": 0.3},
+                 {"cell_frac": 1.0}, {"cell_frac": 0.3, "tune.tile_target": 256, "tune.src_target": 16},
+                 {"cell32": 0}, {"cell32": 0, "tune.tile_limit": 4096}, {"cell32": 0, "tune.tile_limit": 4096, "tune.tile_target": 512, "tune.src_target": 48},
+                 {"cell32": 0, "tune.tile_limit": 4096, "hit_cap": 0}, {"cell32": 0, "hit_cap": 0}, {"cell32": 0, "hit_cap": 160},
+                 {"cell32": 0, "tune.tile_limit": 4096, "hit_cap": 160}, {"cell32": 0, "cell_frac": 0.3},
                  {"cell32": 0, "cell_frac": 1.0}, {"direct_max_atoms": 4096}):
         gb = pkg.GraphBuilder(0)
         if "direct_max_atoms" not in opts:
@@ -205,11 +205,11 @@ def test_block_decomposition_and_unstaged_paths(pkg, oracle, syn):
         assert_graph_equal(h, 0, 0, len(x), o, what=str(opts))
         info = gb.info()
         if "direct_max_atoms" not in opts:
-            if opts.get("cell32", 1) == 0 and opts.get("tile_limit", 0) == 0:
+            if opts.get("cell32", 1) == 0 and opts.get("tune.tile_limit", 0) == 0:
                 assert info.staged_tile_cap == 0
             else:
                 assert info.staged_tile_cap > 0
-        if opts.get("tile_target", 4096) <= 512:
+        if opts.get("tune.tile_target", 4096) <= 512:
             assert info.n_items > 20
         assert info.n_cell_structs == (0 if "direct_max_atoms" in opts else 1)
         gb.close()
@@ -300,9 +300,9 @@ def test_hit_list_and_traversal_fill_paths_agree(pkg, oracle, syn, hit_cap):
     ({"onepass": 0, "hit_cap": 0}, 0),                       # count + traversal fill
     ({"onepass": 0}, 0),                                      # count (+ hit lists where they pay) + fill
     ({"onepass": 1}, 1),                                      # single pass, row buffer / arena from the density estimate
-    ({"onepass": 1, "onepass_row_cap": 64}, 1),               # most rows outgrow the row buffer -> completed by a fill pass
-    ({"onepass": 1, "onepass_arena_scale": 0.25}, 2),         # arena estimate too small -> every row rewritten
-    ({"onepass": 1, "lb_spin_limit": 1}, 3),                  # look-back gives up at once -> rebuilt with count + fill
+    ({"onepass": 1, "tune.onepass_row_cap": 64}, 1),               # most rows outgrow the row buffer -> completed by a fill pass
+    ({"onepass": 1, "tune.onepass_arena_scale": 0.25}, 2),         # arena estimate too small -> every row rewritten
+    ({"onepass": 1, "tune.lb_spin_limit": 1}, 3),                  # look-back gives up at once -> rebuilt with count + fill
 ])
 def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
     """The single-pass build (k_direct<ONE>: look-back row offsets, no count pass) and its two recovery routes must
@@ -322,7 +322,7 @@ def test_single_pass_build_matches_two_pass(pkg, oracle, syn, opts, expect):
     # (a look-back only times out if it has to wait at all: with the spin limit at 1 that is near certain on the many
     # chunks of the larger batch below, not guaranteed on this small one)
     assert info.onepass == expect or (expect == 3 and info.onepass == 1)
-    if opts.get("onepass_row_cap"):
+    if opts.get("tune.onepass_row_cap"):
         assert info.onepass_fallback_rows > 0
     check_batch(gb, oracle, b, 10.0, 20, dr=0.1)           # capped rows, K = 100
     check_batch(gb, oracle, b, 8.0, None, dr=0.3)           # K = 26: separate RBF launch (no float4 epilogue)
@@ -350,7 +350,7 @@ def test_chunked_upload_overlaps_count_pass(pkg, oracle, syn, opts):
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     gb = pkg.GraphBuilder(0)
-    gb.set_option("upload_min_atoms", 0)
+    gb.set_option("tune.upload_min_atoms", 0)
     for k, v in opts.items():
         gb.set_option(k, v)
     none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
@@ -380,7 +380,7 @@ def test_offset_sinks_receive_row_ptr_during_the_build(pkg, oracle, syn, onepass
         pytest.skip("no CUDA device")
     gb = pkg.GraphBuilder(0)
     gb.set_option("onepass", onepass)
-    gb.set_option("upload_min_atoms", 0)
+    gb.set_option("tune.upload_min_atoms", 0)
     none = (np.zeros(0), np.zeros(0), np.zeros(0), np.diag([5.0, 5.0, 5.0]))
     parts = [syn.perovskite_supercell(4, 4, 2, seed=61)[:4], none, syn.triclinic_cell(62)[:4],
              syn.perovskite_supercell(3, 3, 3, seed=63)[:4], syn.perovskite_supercell(2, 2, 2, seed=64)[:4]]
