@@ -295,6 +295,11 @@ def run_c5(gb, pkg, torch, dist, dev, world, rank, b, h_in, total_structs=1_000_
         torch.cuda.synchronize()
 
     stream = torch.cuda.ExternalStream(gb.stream, device=dev)
+    # warm-up: two chunks through the stream, untimed (creates the second arena: ~45 GB of cudaMalloc)
+    warm_plan, plan_full = plan[:2], plan
+    plan = warm_plan
+    gb.build_stream(source, None, r_cutoff=R_CUTOFF, max_neighbors=UNCAPPED, epsilon=1e-10, rbf_r_cutoff=R_CUTOFF, dr=DR)
+    plan = plan_full
     barrier()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
@@ -326,7 +331,8 @@ def run_c5(gb, pkg, torch, dist, dev, world, rank, b, h_in, total_structs=1_000_
             "h2d_bytes_per_chunk": sum(int(t.numel() * t.element_size()) for t in h_in),
             "note": "time = CUDA events on the ctx stream around dgnn_build_stream, max over ranks; every chunk's inputs "
                     "cross PCIe from pinned host memory and its per-structure offsets come back; graphs are dropped when "
-                    "the arena is rebuilt two chunks later; inputs cycle through a pool of %d distinct structures" % S}
+                    "the arena is rebuilt two chunks later; inputs cycle through a pool of %d distinct structures; an untimed "
+                    "two-chunk stream runs first (it creates the second arena)" % S}
 
 
 def main():
