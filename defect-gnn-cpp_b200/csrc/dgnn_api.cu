@@ -194,6 +194,11 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
+    } else if (!strcmp(name, "tie_probe")) {
+        // 1: sample rows decide the tie ranking of the uncapped fill pass (dgnn_tie_probe.cu), 0: always the compact
+        // ranking, 2: always the warp-cooperative one
+        if (!(value >= 0 && value <= 2)) return fail(ctx, DGNN_ERR_INVALID_ARG, "tie_probe must be 0, 1 or 2");
+        ctx->tie_probe = (int)value;
     } else if (!strcmp(name, "onepass")) {
         if (!(value >= -1 && value <= 1)) return fail(ctx, DGNN_ERR_INVALID_ARG, "onepass must be -1, 0 or 1");
         ctx->onepass_opt = (int)value;  // single-pass build (look-back row offsets) instead of count + fill
@@ -542,6 +547,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             }
             D.row_begin = D.row_end = 0;
             dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+            // rows that may go through the uncapped fill kernel: sample their sort keys for ties (result arrives with
+            // the statistics of sync 1)
+            if (ctx->tie_probe == 1 && max_nb >= 32) CU(dg_launch_tie_probe(st, D));
         }
     } else if (!onepass) {
         // the cell-list kernels still need the uploaded coordinates, and empty batches a valid (all zero) row_ptr
@@ -748,6 +756,10 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.row_cap = row_cap;
     D.n_buckets = n_buckets;
     D.n_warps = 8;
+    // mean number of entries sharing a truncated sort key over the probed rows: 1.0 for thermal / relaxed structures,
+    // 10-30 on the coordination shells of an ideal lattice, where the compact ranking is quadratic
+    const double tie_run_mean = ctx->h_stats->tie_n > 0 ? (double)ctx->h_stats->tie_sum / (double)ctx->h_stats->tie_n : 0.0;
+    D.full_tie_sort = ctx->tie_probe == 2 || (ctx->tie_probe == 1 && tie_run_mean >= 3.0);
     // fused RBF epilogue: rows stream their K features right after the sort (needs K % 4 == 0 for the float4 stores)
     const int keep_max = max_deg < max_nb ? max_deg : max_nb;
     const bool fuse_rbf = onepass ? (onepass_fused_rbf && E > 0)
@@ -899,6 +911,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.hit_cap = use_hits ? hit_cap : 0;
     I.onepass = onepass ? (onepass_redo_all ? 2 : 1) : 0;
     I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
+    I.tie_run_mean = (float)tie_run_mean;
+    I.full_tie_sort = (!onepass && max_nb >= row_cap && D.full_tie_sort) ? 1 : 0;
     return DGNN_OK;
 }
 

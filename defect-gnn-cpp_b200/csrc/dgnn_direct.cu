@@ -238,7 +238,7 @@ cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, 
     const size_t smem = dg_direct_smem_bytes(a, fill);
     const int threads = a.n_warps * 32;
     dg_direct_launch_bump(1);
-    if (fill && a.max_neighbors >= a.row_cap)  // no row is truncated: the lean sort
+    if (fill && a.max_neighbors >= a.row_cap && !a.full_tie_sort)  // no row is truncated, keys distinct: the lean sort
         return launch_direct_e<true, false, true>(st, a, sm_count, smem, threads);
     if (fill) return launch_direct_e<true, false, false>(st, a, sm_count, smem, threads);
     if (a.hit_cap > 0 && a.hits) return launch_direct_e<false, true, false>(st, a, sm_count, smem, threads);

@@ -29,6 +29,8 @@ struct DgStats {
     unsigned long long est_edges;  // density estimate of the edge total, sum over structures of N_s * est_deg_s
     unsigned long long unit_ctr[8];  // row-unit counters of dynamically scheduled launches (one per launch)
     int est_sparse;              // 1000000 - smallest per-structure degree estimate (0: no non-empty structure)
+    unsigned long long tie_sum;  // dgnn_tie_probe.cu: sum over probed entries of the entries sharing their sort key ...
+    unsigned long long tie_n;    // ... and the number of probed entries (ratio = mean run length; 1.0: no ties)
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -168,6 +170,7 @@ struct DgDirectArgs {
     int dyn_unit;                   // > 0: rows are handed out to warps in units of this many rows from *unit_ctr (zeroed)
     unsigned long long* unit_ctr;
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
+    int full_tie_sort;              // uncapped fill pass: 1 = warp-cooperative tie ranking (batches the probe found tie-heavy)
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -182,6 +185,7 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
 void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count);
+cudaError_t dg_launch_tie_probe(cudaStream_t st, const DgDirectArgs& a);  // dgnn_tie_probe.cu
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
 cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);

@@ -229,6 +229,9 @@ typedef struct {
                               * arena was too small and the fill pass rewrote every row, 3: its look-back timed out (SMs
                               * held by other work) and the batch was rebuilt with count + fill, 0: count + fill */
     int32_t onepass_fallback_rows; /* rows that outgrew the single-pass row buffer and were completed by a fill pass */
+    float tie_run_mean;      /* sampled rows: mean number of entries sharing a truncated sort key (1.0: none; 0: the
+                              * build did not probe).  Ideal lattices put whole coordination shells on one key */
+    int32_t full_tie_sort;   /* 1: the uncapped fill pass ran with the warp-cooperative tie ranking (tie_run_mean >= 3) */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 

@@ -470,3 +470,33 @@ def test_symmetric_count_pass_is_exact(pkg, oracle, syn, sym):
     gb.close()
 
 
+
+
+def test_tie_probe_selects_the_tie_ranking(pkg, oracle, syn):
+    """The uncapped sweep-fill kernel has two tie rankings (compact per entry / warp-cooperative); sampled rows decide
+    which one a batch gets (dgnn_tie_probe.cu).  Thermal structures: no ties, the compact one; ideal lattices (whole
+    coordination shells on one sort key): the cooperative one.  Rows, tie order and the tie statistic equal the oracle
+    either way and with the choice forced."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    ideal = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=s, jitter=0.0)[:4] for s in range(6)])
+    thermal = syn.c2_batch(6, seed0=77)
+    for probe in (1, 0, 2):
+        gb = pkg.GraphBuilder(0)
+        for k, v in (("onepass", 0), ("hit_cap", 0), ("tune.tie_probe", probe)):
+            gb.set_option(k, v)
+        check_batch(gb, oracle, thermal, 8.0, None, dr=0.2)
+        it = gb.info()
+        check_batch(gb, oracle, ideal, 8.0, None, dr=0.2, algo=oracle.ALGO_BRUTE)
+        ii = gb.info()
+        if probe == 1:
+            assert 0.99 <= it.tie_run_mean < 1.5 and it.full_tie_sort == 0
+            assert ii.tie_run_mean >= 3.0 and ii.full_tie_sort == 1
+        else:
+            assert it.tie_run_mean == 0.0 and ii.tie_run_mean == 0.0          # not probed
+            assert it.full_tie_sort == ii.full_tie_sort == (1 if probe == 2 else 0)
+        # capped rows never take the lean kernel: the flag stays 0
+        check_batch(gb, oracle, ideal, 8.0, 20, dr=0.2, algo=oracle.ALGO_BRUTE)
+        assert gb.info().full_tie_sort == 0
+        gb.close()

@@ -29,4 +29,5 @@ for jitter in (0.02, 0.0):
         t = min(ms)
         print(json.dumps({"jitter": jitter, "r_c": rc, "cap": None if cap == UNCAPPED else cap, "edges": int(g.n_edges),
                           "total_ms": round(t[0], 3), "count_ms": round(t[1], 3), "fill_ms": round(t[2], 3),
-                          "launches": int(i.kernel_launches)}))
+                          "launches": int(i.kernel_launches), "tie_run_mean": round(float(i.tie_run_mean), 2),
+                          "full_tie_sort": int(i.full_tie_sort)}))
