@@ -194,6 +194,9 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
+    } else if (!strcmp(name, "fill_hits_warps")) {
+        if (!(value >= 0 && value <= 8)) return fail(ctx, DGNN_ERR_INVALID_ARG, "fill_hits_warps must be 0 ... 8");
+        ctx->fill_hits_warps = (int)value;
     } else if (!strcmp(name, "tie_probe")) {
         // 1: sample rows decide the tie ranking of the uncapped fill pass (dgnn_tie_probe.cu), 0: always the compact
         // ranking, 2: always the warp-cooperative one
@@ -776,6 +779,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // rows with a stored hit list are filled from it; the traversal fill pass takes whatever is left
     DgDirectArgs H = D;
     H.fill_hits_bulk = ctx->fill_hits_bulk;
+    H.fill_hits_warps = ctx->fill_hits_warps;
     if (n_cell_structs > 0 && !cell32) {
         H.cloud_j = (const int*)ctx->cj.p;
         H.cloud_n = (const uint32_t*)ctx->cn.p;

@@ -76,6 +76,7 @@ struct dgnn_ctx {
                                           // guard band (dgnn_cell32.cu); 0: the fp64 traversal with hit lists (A/B reference)
     int cell32_fill_warps = 16;
     int dyn_rows = 1;                     // small batches: dynamic per-warp row schedule in the direct kernels
+    int fill_hits_warps = 0;              // (tuning) warps per CTA of k_fill_hits, 0: most resident warps per SM
     int tie_probe = 1;                    // 1: sampled rows choose the tie ranking of the uncapped fill pass, 0 / 2: fixed
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)

@@ -140,8 +140,37 @@ size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a) {
     return (size_t)a.n_warps * dg_fill_hits_warp_bytes(W);
 }
 
-cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
-    if (a.n_atoms <= 0) return cudaSuccess;
+// Warps per CTA: the kernel is bound by latency at the occupancy its shared memory allows (10 KB per warp at 192-entry
+// rows: 2 CTAs of 8 warps), so the CTA size is the one that puts the most warps on an SM -- 3 CTAs of 7 warps there.
+static int pick_fill_hits_warps(const DgDirectArgs& a, int max_warps) {
+    static size_t cached_bytes = 0;
+    static int cached_max = 0, cached_pick = 0;
+    const int W = a.hit_cap < a.row_cap ? a.hit_cap : a.row_cap;
+    const size_t per_warp = dg_fill_hits_warp_bytes(W);
+    if (per_warp == cached_bytes && max_warps == cached_max) return cached_pick;
+    int best = max_warps, best_warps = 0;
+    for (int n = max_warps; n >= 4 && n >= max_warps - 4; --n) {
+        const size_t smem = (size_t)n * per_warp;
+        if (cudaFuncSetAttribute(k_fill_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) continue;
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill_hits, n * 32, smem) != cudaSuccess) continue;
+        if (occ * n > best_warps) {
+            best_warps = occ * n;
+            best = n;
+        }
+    }
+    (void)cudaGetLastError();
+    cached_bytes = per_warp;
+    cached_max = max_warps;
+    cached_pick = best;
+    return best;
+}
+
+cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a_in, int sm_count) {
+    if (a_in.n_atoms <= 0) return cudaSuccess;
+    DgDirectArgs a = a_in;
+    if (a.fill_hits_warps > 0) a.n_warps = a.fill_hits_warps < a.n_warps ? a.fill_hits_warps : a.n_warps;
+    else a.n_warps = pick_fill_hits_warps(a, a.n_warps);
     const size_t smem = dg_fill_hits_smem_bytes(a);
     const int threads = a.n_warps * 32;
     cudaError_t e = cudaFuncSetAttribute(k_fill_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -157,4 +186,3 @@ cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_c
     k_fill_hits<<<(unsigned)grid, threads, smem, st>>>(a);
     return cudaGetLastError();
 }
-

@@ -170,6 +170,7 @@ struct DgDirectArgs {
     int dyn_unit;                   // > 0: rows are handed out to warps in units of this many rows from *unit_ctr (zeroed)
     unsigned long long* unit_ctr;
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
+    int fill_hits_warps;            // k_fill_hits: warps per CTA (0: the count that puts the most warps on an SM)
     int full_tie_sort;              // uncapped fill pass: 1 = warp-cooperative tie ranking (batches the probe found tie-heavy)
 };
 #define DG_EPS_FAST 1.0e-3

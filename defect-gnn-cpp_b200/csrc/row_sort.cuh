@@ -598,7 +598,8 @@ __device__ __forceinline__ int dg_row_prefilter_t(double* __restrict__ rd, const
         f[r] = e < m ? (float)rd[e] : 3.0e38f;
     }
     const int need = keep + 1;
-    const int good = need + 48 > 2 * need ? need + 48 : 2 * need;  // stop when need <= count <= good
+    // stop when need <= count <= good; small caps (the reference's default 20) aim at the 64-entry network
+    const int good = need <= 32 ? 56 : (need + 48 > 2 * need ? need + 48 : 2 * need);
     const float x = (float)(need + 8) / (float)m;
     float T = r2 * cbrtf(x * x) * 1.1f;  // count ~ d^3
     float lo = 0.0f, hi = 0.0f;          // lo: count < need, hi: count >= need (0: not bracketed yet)
@@ -624,25 +625,28 @@ __device__ __forceinline__ int dg_row_prefilter_t(double* __restrict__ rd, const
     const float Tk = hi * (1.0f + 1.9073486328125e-6f);
     const unsigned lt_mask = (1u << lane) - 1u;
     int base = 0;
-    for (int c0 = 0; c0 < m; c0 += 32) {
-        const int e = c0 + lane;
-        double d2 = 0.0;
-        uint2 item = make_uint2(0u, 0u);
-        bool pred = false;
-        if (e < m) {
-            d2 = rd[e];
-            pred = (float)d2 < Tk;
-            if (pred) item = P.load_item(e);
+    // (the decision is made on the fp32 copies already in registers -- the same values the search counted)
+#pragma unroll
+    for (int r = 0; r < EPL; ++r) {
+        if (r * 32 < m) {  // warp-uniform
+            const int e = r * 32 + lane;
+            const bool pred = f[r] < Tk;  // (padding is 3e38: never)
+            double d2 = 0.0;
+            uint2 item = make_uint2(0u, 0u);
+            if (pred) {
+                d2 = rd[e];
+                item = P.load_item(e);
+            }
+            const unsigned mask = __ballot_sync(FULL_MASK, pred);
+            __syncwarp();
+            if (pred) {
+                const int pos = base + __popc(mask & lt_mask);  // pos <= e: never ahead of an unread entry
+                rd[pos] = d2;
+                P.store_item(pos, item);
+            }
+            base += __popc(mask);
+            __syncwarp();
         }
-        const unsigned mask = __ballot_sync(FULL_MASK, pred);
-        __syncwarp();
-        if (pred) {
-            const int pos = base + __popc(mask & lt_mask);  // pos <= e: never ahead of an unread entry
-            rd[pos] = d2;
-            P.store_item(pos, item);
-        }
-        base += __popc(mask);
-        __syncwarp();
     }
     return base;
 }
@@ -663,7 +667,12 @@ __device__ __forceinline__ long long dg_row_sort_bitonic_any_op(double* rd, uint
                                                                 const Payload& P, int m, int keep, double key_scale,
                                                                 OP& op, int* dst, uint32_t* image, double* dist,
                                                                 DgStats* stats, int lane) {
-    if (!LEAN) m = dg_row_prefilter<Payload, MAXEPL>(rd, P, m, keep, key_scale, lane);
+    if (!LEAN) {
+        const int m0 = m;
+        m = dg_row_prefilter<Payload, MAXEPL>(rd, P, m, keep, key_scale, lane);
+        if (m < m0 && m <= 64)  // what the prefilter of a small cap leaves
+            return dg_row_sort_bitonic<2, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
+    }
     if (m <= 128)
         return dg_row_sort_bitonic<4, Payload, OP, LEAN>(rd, sk, fd, tie, P, m, keep, key_scale, op, dst, image, dist, stats, lane);
     if (MAXEPL <= 8 || m <= 256)
