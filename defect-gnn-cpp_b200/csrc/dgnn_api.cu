@@ -80,7 +80,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
-                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->hits_n, &ctx->hit_thr, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats, &ctx->col_x, &ctx->col_ei, &ctx->col_batch, &ctx->col_keys,
                       &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b, &ctx->tab_cnt, &ctx->tab_ptr,
                       &ctx->tab_val};
@@ -194,6 +194,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
+    } else if (!strcmp(name, "hit_threshold")) {
+        ctx->hit_threshold = value != 0.0;
     } else if (!strcmp(name, "fill_hits_warps")) {
         if (!(value >= 0 && value <= 8)) return fail(ctx, DGNN_ERR_INVALID_ARG, "fill_hits_warps must be 0 ... 8");
         ctx->fill_hits_warps = (int)value;
@@ -371,6 +373,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     // traversal.  Slots per row come from the density estimate of the degree (rows that outgrow them, and structures
     // whose image range does not fit the 5-bit fields, are filled by the traversal pass instead).
     int hit_cap = ctx->hit_cap_opt > 0 ? round_up(ctx->hit_cap_opt, 32) : 0;  // rows stay 16-byte aligned
+    double hit_target = 0.0;  // > 0: lists of truncated rows hold ~this many pairs (per-structure d2 threshold)
     bool have_est = false;
     if ((ctx->hit_cap_opt < 0 || ctx->onepass_opt != 0) && N > 0) {
         int r = fetch_stats(ctx);  // sync: density estimate, classification, input errors
@@ -392,12 +395,31 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         // (the fp32-tile traversal of cell-list structures needs no lists; only the fp64 one, option cell32 = 0, does)
         if (est > 0 && ((ctx->h_stats->n_cell_structs > 0 && !ctx->cell32) || (bytes_per_pair < 64.0 && !onepass_likely)))
             hit_cap = round_up((int)(est + est / 4 + 16 < DGNN_MAX_DEGREE ? est + est / 4 + 16 : DGNN_MAX_DEGREE), 32);
+        // Truncated rows (the reference's default max_neighbors = 20 of ~160-330 accepted pairs): the lists only need
+        // the pairs that can reach the first max_neighbors + 1 ranks.  The count pass stores the pairs below a
+        // per-structure d2 threshold set for ~target of them (mean + 4 sigma of a Poisson count, plus the margin the
+        // exactness argument needs) and the slots shrink to match; rows the threshold fails go to the traversal fill.
+        if (hit_cap > 0 && ctx->hit_threshold && (ctx->h_stats->n_cell_structs == 0 || ctx->cell32)) {
+            const double need = (double)max_nb_for_est(b->max_neighbors) + 1.0;
+            const double target = need + 4.0 * sqrt(need) + 8.0;
+            const int slots = round_up((int)(target + 6.0 * sqrt(target) + 16.0), 32);
+            if (slots < hit_cap && target < 0.4 * (double)est) {
+                hit_target = target;
+                hit_cap = slots;
+            }
+        }
     }
     if (hit_cap > 512) hit_cap = 512;  // the hit-list fill pass sorts in registers: rows of up to 512 entries
     if (hit_cap > 0 && (double)N * (double)hit_cap * 12.0 > ctx->hits_max_bytes) hit_cap = 0;
+    if (hit_cap == 0) hit_target = 0.0;
     if (hit_cap > 0) {
         ENSURE(ctx->hits, (size_t)N * (size_t)hit_cap * 4 + 16);
         ENSURE(ctx->hits_d2, (size_t)N * (size_t)hit_cap * 8 + 16);
+    }
+    if (hit_target > 0.0) {
+        ENSURE(ctx->hits_n, (size_t)(N + 1) * 4);
+        ENSURE(ctx->hit_thr, (size_t)(S + 1) * 8);
+        dg_launch_hit_thresholds(st, S, small, hit_target, b->r_cutoff * b->r_cutoff, (double*)ctx->hit_thr.p);
     }
     CU(cudaEventRecord(ctx->ev.e[2], st));
 
@@ -440,6 +462,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     D.hits = hit_cap > 0 ? (uint32_t*)ctx->hits.p : nullptr;
     D.hits_d2 = hit_cap > 0 ? (double*)ctx->hits_d2.p : nullptr;
     D.hit_cap = hit_cap;
+    D.hit_d2_max = hit_target > 0.0 ? (const double*)ctx->hit_thr.p : nullptr;
+    D.hits_n = hit_target > 0.0 ? (int*)ctx->hits_n.p : nullptr;
     D.stats = d_stats;
     // small batches (fewer than two rounds of 64-row chunks over a full grid): rows go to warps a few at a time from a
     // device counter -- uneven rows (tiny triclinic cells: 2-8 atoms, 343-729 images per pair) otherwise leave most of
@@ -801,6 +825,11 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         if ((int)dg_fill_hits_smem_bytes(H) > ctx->smem_optin) use_hits = false;
     }
     if (!use_hits) D.hit_cap = 0;
+    if (use_hits && hit_target > 0.0) {
+        // thresholded lists: the stored count (INT_MAX: not served by the list) decides who fills a row
+        H.deg_raw = (int*)ctx->hits_n.p;
+        D.deg_raw = (int*)ctx->hits_n.p;
+    }
     if (E > 0 && use_hits && (any_direct || (n_cell_structs > 0 && !cell32))) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
     if (E > 0 && !onepass && any_direct && (!use_hits || n_fallback_rows > 0)) {
         dyn_arm(D);

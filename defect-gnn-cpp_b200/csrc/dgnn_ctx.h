@@ -45,7 +45,7 @@ struct dgnn_ctx {
     DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
     DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
     // results
-    DevBuf deg, deg_raw, hits, hits_d2, row_ptr, seo, dst, image, dist, rbf;
+    DevBuf deg, deg_raw, hits, hits_d2, hits_n, hit_thr, row_ptr, seo, dst, image, dist, rbf;
     // stand-alone rbf staging
     DevBuf tmp_in, tmp_out;
     DevBuf stats;
@@ -76,6 +76,7 @@ struct dgnn_ctx {
                                           // guard band (dgnn_cell32.cu); 0: the fp64 traversal with hit lists (A/B reference)
     int cell32_fill_warps = 16;
     int dyn_rows = 1;                     // small batches: dynamic per-warp row schedule in the direct kernels
+    int hit_threshold = 1;                // truncated rows: hit lists hold only pairs below a per-structure d2 threshold
     int fill_hits_warps = 0;              // (tuning) warps per CTA of k_fill_hits, 0: most resident warps per SM
     int tie_probe = 1;                    // 1: sampled rows choose the tie ranking of the uncapped fill pass, 0 / 2: fixed
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair

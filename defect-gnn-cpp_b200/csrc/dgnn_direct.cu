@@ -147,15 +147,33 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
             const bool store_hits = HITS && nimg <= DG_HIT_NMAX;                                                         \
             uint32_t* __restrict__ hrow = HITS ? A.hits + (size_t)a * (size_t)A.hit_cap : nullptr;                       \
             double* __restrict__ hd2 = HITS ? A.hits_d2 + (size_t)a * (size_t)A.hit_cap : nullptr;                       \
-            int m = traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);             \
+            HitTally ht;                                                                                                 \
+            if (HITS) {                                                                                                  \
+                ht.tot = ht.lo = 0;                                                                                      \
+                ht.d2_max = A.hit_d2_max ? A.hit_d2_max[A.astruct[a]] : DG_INF;                                          \
+                ht.d2_lo = ht.d2_max * (1.0 - 3.814697265625e-6);                                                        \
+            }                                                                                                            \
+            int m = HITS ? traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht)   \
+                         : traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);      \
             if (!FILL && !HITS) m = __reduce_add_sync(FULL_MASK, m);                                                     \
+            int mh = 0, mlo = 0; /* HITS: stored pairs, pairs safely below the storing threshold */                      \
+            if (HITS) {                                                                                                  \
+                mh = m;                                                                                                  \
+                m = __reduce_add_sync(FULL_MASK, ht.tot);                                                                \
+                mlo = __reduce_add_sync(FULL_MASK, ht.lo);                                                               \
+            }                                                                                                            \
             maxdeg = m > maxdeg ? m : maxdeg;                                                                            \
             const int keep = m < A.max_neighbors ? m : A.max_neighbors;                                                  \
             if (!FILL) {                                                                                                 \
                 if (lane == 0) {                                                                                         \
                     A.deg_capped[a] = keep;                                                                              \
                     A.deg_raw[a] = m;                                                                                    \
-                    if (HITS && (m > A.hit_cap || !store_hits)) atomicAdd(&A.stats->n_fallback_rows, 1);                 \
+                    if (HITS) {                                                                                          \
+                        /* the list serves the fill pass if it is complete, or holds the first max_neighbors + 1 ranks */  \
+                        const bool ok = store_hits && mh <= A.hit_cap && (mh == m || mlo > A.max_neighbors);             \
+                        if (A.hits_n) A.hits_n[a] = ok ? mh : 0x7fffffff;                                                \
+                        if (!ok) atomicAdd(&A.stats->n_fallback_rows, 1);                                                \
+                    }                                                                                                    \
                 }                                                                                                        \
             } else if (m > A.row_cap) { /* cannot happen: row_cap >= max degree of the count pass */                     \
                 if (lane == 0) atomicExch(&A.stats->overflow, 1);                                                        \

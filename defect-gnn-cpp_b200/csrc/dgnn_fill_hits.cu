@@ -140,6 +140,32 @@ size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a) {
     return (size_t)a.n_warps * dg_fill_hits_warp_bytes(W);
 }
 
+// Storing threshold of the count pass's hit lists for truncated rows: the d2 below which a structure of N atoms in volume
+// V is expected to hold `target` neighbours, r^3 = target V / (N 4/3 pi).  Rows whose neighbourhood is sparser than the
+// structure's mean (next to a vacancy cluster, a surface) may fall short; the count pass notices and leaves them to the
+// traversal fill (direct_sweep.cuh, HitTally).
+__global__ void __launch_bounds__(128) k_hit_thresholds(long long S, const DgSmall* __restrict__ small, double target,
+                                                        double r2, double* __restrict__ out) {
+    const long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= S) return;
+    const DgSmall* G = small + s;
+    double thr = DG_INF;
+    if (G->status == DG_ST_OK && G->natoms > 0 && G->mode != DG_MODE_CELL) {
+        const double* L = G->L;
+        const double det = fabs(L[0] * (L[4] * L[8] - L[5] * L[7]) + L[1] * (L[5] * L[6] - L[3] * L[8]) +
+                                L[2] * (L[3] * L[7] - L[4] * L[6]));
+        const double r3 = target * det / ((double)G->natoms * 4.18879020478639);
+        const double t = cbrt(r3 * r3);
+        if (t < 0.8 * r2) thr = t;  // (otherwise nearly everything would be stored anyway)
+    }
+    out[s] = thr;
+}
+void dg_launch_hit_thresholds(cudaStream_t st, long long S, const DgSmall* small, double target, double r2, double* out) {
+    if (S <= 0) return;
+    k_hit_thresholds<<<(unsigned)((S + 127) / 128), 128, 0, st>>>(S, small, target, r2, out);
+    dg_direct_launch_bump(1);
+}
+
 // Warps per CTA: the kernel is bound by latency at the occupancy its shared memory allows (10 KB per warp at 192-entry
 // rows: 2 CTAs of 8 warps), so the CTA size is the one that puts the most warps on an SM -- 3 CTAs of 7 warps there.
 static int pick_fill_hits_warps(const DgDirectArgs& a, int max_warps) {

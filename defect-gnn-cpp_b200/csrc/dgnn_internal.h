@@ -170,6 +170,11 @@ struct DgDirectArgs {
     int dyn_unit;                   // > 0: rows are handed out to warps in units of this many rows from *unit_ctr (zeroed)
     unsigned long long* unit_ctr;
     double sym_band;                // symmetric count pass: |d2 - r_c^2| <= sym_band recomputes the mirror edge exactly
+    // truncated rows: the count pass stores only accepted pairs with d2 below the structure's threshold (direct_sweep.cuh,
+    // HitTally) and writes the stored count -- or INT_MAX for rows the list cannot serve -- to hits_n; the fill passes
+    // are then given hits_n as their deg_raw.  Null: everything is stored and deg_raw decides.
+    const double* hit_d2_max;       // [S]
+    int* hits_n;                    // [N]
     int fill_hits_warps;            // k_fill_hits: warps per CTA (0: the count that puts the most warps on an SM)
     int full_tie_sort;              // uncapped fill pass: 1 = warp-cooperative tie ranking (batches the probe found tie-heavy)
 };
@@ -193,6 +198,8 @@ cudaError_t dg_launch_direct_onepass(cudaStream_t st, const DgDirectArgs& a, int
 // fill pass from the count pass's hit lists (rows with degree <= hit_cap and image range <= DG_HIT_NMAX)
 size_t dg_fill_hits_smem_bytes(const DgDirectArgs& a);
 cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a, int sm_count);
+// per-structure d2 below which about `target` neighbours are expected (+inf where that is most of the cutoff sphere)
+void dg_launch_hit_thresholds(cudaStream_t st, long long S, const DgSmall* small, double target, double r2, double* out);
 int dg_direct_launch_count_reset();
 
 // ---- dgnn_rbf.cu ----

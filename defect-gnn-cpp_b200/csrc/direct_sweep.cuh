@@ -44,6 +44,18 @@ struct Src {
     int iloc;
 };
 
+// Count pass with hit lists of truncated rows (HITS): only accepted pairs below a per-structure d2 threshold are stored
+// (a little more than max_neighbors + 1 of them, from the density) -- the fill pass reads and sorts ~50 instead of all
+// ~160-330.  tot / lo are per-lane tallies of all accepted pairs and of those safely below the threshold
+// (d2 < d2_max (1 - 2^-18)): a row whose lo reaches max_neighbors + 1 has every entry of its first max_neighbors + 1
+// canonical ranks, and every entry that ties with one of them, in the list (ties differ by < 2^-50 in d2); the others
+// are left to the traversal fill.  d2_max = +inf: everything is stored.
+#define DG_INF __longlong_as_double(0x7ff0000000000000LL)
+struct HitTally {
+    int tot, lo;
+    double d2_max, d2_lo;
+};
+
 // One candidate image point (px,py,pz) of atom jloc per lane; compacts hits into the row buffer.
 // EPS selects the self-exclusion rule `orig == i && sqrt(d2) < epsilon` (neighbor_list.cpp:47-49):
 //   0: epsilon <= 0, nothing is excluded;  1: 0 < epsilon <= DG_EPS_FAST: only the atom's own n = (0,0,0) image can
@@ -59,7 +71,7 @@ template <bool FILL, int EPS, bool HITS, bool ONE>
 __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, const RowBuf& rb,
                                            uint32_t* __restrict__ hrow, double* __restrict__ hd2, bool active,
                                            bool self, int jloc, double px, double py, double pz, int na, int nb, int nc,
-                                           unsigned lt_mask, int& m, unsigned& near) {
+                                           unsigned lt_mask, int& m, unsigned& near, HitTally& ht) {
     const double dx = DG_SUB(S.x, px);
     const double dy = DG_SUB(S.y, py);
     const double dz = DG_SUB(S.z, pz);
@@ -78,6 +90,9 @@ __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, 
     if (!FILL) {
         // count pass: per-lane tallies, reduced once per row (no ballot per candidate)
         if (HITS) {
+            ht.tot += hit ? 1 : 0;
+            ht.lo += (hit && d2 < ht.d2_lo) ? 1 : 0;
+            hit = hit && d2 < ht.d2_max;
             const unsigned mask = __ballot_sync(FULL_MASK, hit);
             if (hit) {
                 const int pos = m + __popc(mask & lt_mask);
@@ -105,11 +120,12 @@ __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, 
 }
 
 // Candidate sweep of one source atom a of structure G (mode: DG_MODE_ATOMPAR / DG_MODE_IMGPAR); returns the number of
-// accepted pairs (per lane when !FILL && !HITS, warp-uniform otherwise).  All 32 lanes must call.
+// accepted pairs (per lane when !FILL && !HITS, warp-uniform otherwise; HITS: the STORED pairs, the tallies are in ht).
+// All 32 lanes must call.
 template <bool FILL, int EPS, bool HITS, bool ONE>
 __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall* __restrict__ G, long long a, int mode,
                                             const RowBuf& rb, uint32_t* __restrict__ hrow, double* __restrict__ hd2,
-                                            int lane, unsigned lt_mask, unsigned& near) {
+                                            int lane, unsigned lt_mask, unsigned& near, HitTally& ht) {
     const long long base = G->atom_base;
     const int N = G->natoms, nimg = G->nimg;
     Src S;
@@ -164,7 +180,7 @@ __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall
                         const double py = DG_ADD(yj, DG_ADD(ob1, DG_MUL(ncd, L21)));
                         const double pz = DG_ADD(zj, DG_ADD(ob2, DG_MUL(ncd, L22)));
                         test_point<FILL, EPS, HITS, ONE>(A, S, rb, hrow, hd2, act_ab && sc < c2, self, jj, px, py, pz,
-                                                    lo0 + sa, lo1 + sb, lo2 + sc, lt_mask, m, near);
+                                                    lo0 + sa, lo1 + sb, lo2 + sc, lt_mask, m, near, ht);
                     }
                 }
             }
@@ -189,10 +205,18 @@ __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall
                 const double py = DG_ADD(yj, dg_image_offset(G->L, 1, na, nb, nc));
                 const double pz = DG_ADD(zj, dg_image_offset(G->L, 2, na, nb, nc));
                 test_point<FILL, EPS, HITS, ONE>(A, S, rb, hrow, hd2, active, j == S.iloc, j, px, py, pz, na, nb, nc,
-                                            lt_mask, m, near);
+                                            lt_mask, m, near, ht);
             }
         }
     }
     return m;
 }
-
+template <bool FILL, int EPS, bool HITS, bool ONE>
+__device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall* __restrict__ G, long long a, int mode,
+                                            const RowBuf& rb, uint32_t* __restrict__ hrow, double* __restrict__ hd2,
+                                            int lane, unsigned lt_mask, unsigned& near) {
+    HitTally ht;  // (dead without HITS)
+    ht.tot = ht.lo = 0;
+    ht.d2_max = ht.d2_lo = 0.0;
+    return traverse_row<FILL, EPS, HITS, ONE>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht);
+}

@@ -500,3 +500,40 @@ def test_tie_probe_selects_the_tie_ranking(pkg, oracle, syn):
         check_batch(gb, oracle, ideal, 8.0, 20, dr=0.2, algo=oracle.ALGO_BRUTE)
         assert gb.info().full_tie_sort == 0
         gb.close()
+
+
+def test_thresholded_hit_lists_of_truncated_rows(pkg, oracle, syn):
+    """Truncated rows (max_neighbors << degree): the count pass stores only accepted pairs below a per-structure d2
+    threshold sized from the density for a little more than max_neighbors + 1 of them, and the fill pass sorts those.
+    Rows the threshold cannot serve -- sparser than the structure's mean (atoms above a slab, next to a void), or
+    denser than the slots -- must be completed by the traversal fill; whole shells of equal distances at the threshold
+    (ideal lattices) must not lose a tie partner.  Every case equals the exhaustive oracle."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    x, y, z, L = syn.perovskite_supercell(4, 4, 2, seed=5)[:4]
+    half = z < 0.5 * L[2, 2]
+    lone = np.zeros_like(half)
+    lone[np.flatnonzero(~half)[:3]] = True                      # three atoms above a slab: sparse rows
+    keep = half | lone
+    slab = (x[keep], y[keep], z[keep], L)
+    tall = L.copy()
+    tall[2] *= 3.0                                              # mostly vacuum: local density 3x the mean
+    vac = (x, y, z, tall)
+    thermal = syn.c2_batch(5, seed0=11)
+    ideal = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=s, jitter=0.0)[:4] for s in range(3)])
+    mixed = syn.concat([slab, vac, syn.perovskite_supercell(3, 3, 2, seed=2)[:4], syn.triclinic_cell(5)[:4]])
+    for thr in (1, 0):
+        gb = pkg.GraphBuilder(0)
+        gb.set_option("onepass", 0)
+        gb.set_option("tune.hit_threshold", thr)
+        caps_seen = []
+        for b, algo in ((thermal, None), (ideal, oracle.ALGO_BRUTE), (mixed, oracle.ALGO_BRUTE)):
+            for rc, cap in ((8.0, 20), (10.0, 20), (8.0, 1), (8.0, 12), (10.0, 40)):
+                check_batch(gb, oracle, b, rc, cap, dr=0.2, algo=algo)
+                caps_seen.append(gb.info().hit_cap)
+        if thr:
+            assert min(caps_seen) > 0 and max(caps_seen) <= 160      # slots follow the cap, not the degree
+        else:
+            assert max(caps_seen) >= 192
+        gb.close()
