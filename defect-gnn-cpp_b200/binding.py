@@ -28,6 +28,7 @@ EXPORTS = [
     "dgnn_collate", "dgnn_copy_collated_to_host", "dgnn_edge_views", "dgnn_neighborhood_clouds",
     "dgnn_last_consumer_info", "dgnn_set_offset_sinks", "dgnn_build_stream", "dgnn_distance_tables", "dgnn_copy_distance_tables_to_host", "dgnn_host_alloc", "dgnn_host_free",
     "dgnn_collated_dlpack", "dgnn_live_exports", "dgnn_dlpack_release", "dgnn_build_serial",
+    "dgnn_row_offsets_noalloc",
 ]
 
 
@@ -223,8 +224,26 @@ def load_library():
         L.dgnn_live_exports.restype = C.c_int
         L.dgnn_dlpack_release.argtypes = [C.c_void_p]
         L.dgnn_dlpack_release.restype = None
+        L.dgnn_row_offsets_noalloc.argtypes = [C.c_int, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_char_p,
+                                               C.c_size_t]
+        L.dgnn_row_offsets_noalloc.restype = C.c_int
         _lib = L
     return _lib
+
+
+NOALLOC_MAX_ROWS = 1 << 24  # DGNN_NOALLOC_MAX_ROWS (include/dgnn_cabi.h)
+
+
+def row_offsets_noalloc(device: int, degrees_ptr: int, n_rows: int, row_ptr_ptr: int, stream: int | None = None) -> None:
+    """dgnn_row_offsets_noalloc over raw DEVICE pointers (int32 degrees[n_rows] -> int64 row_ptr[n_rows + 1]) on
+    `stream` (cudaStream_t as int, None = default stream); does not synchronise and allocates nothing.  No counterpart
+    in the reference (see include/dgnn_cabi.h)."""
+    lib = load_library()
+    err = C.create_string_buffer(256)
+    rc = lib.dgnn_row_offsets_noalloc(int(device), C.c_void_p(degrees_ptr), int(n_rows), C.c_void_p(row_ptr_ptr),
+                                      C.c_void_p(stream), err, len(err))
+    if rc != 0:
+        raise DgnnError(rc, err.value.decode() or lib.dgnn_strerror(rc).decode())
 
 
 @dataclass

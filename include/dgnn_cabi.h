@@ -271,6 +271,24 @@ uint64_t dgnn_build_serial(const dgnn_ctx* ctx);
 int dgnn_host_alloc(size_t bytes, void** out);
 void dgnn_host_free(void* p);
 
+/* ---- allocation-free row offsets ------------------------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  A variant of the degree scan that
+ * dgnn_build runs between its count and fill passes: row_ptr[i] = degrees[0] + ... + degrees[i - 1] for i = 0 ... n_rows
+ * (row_ptr has n_rows + 1 entries; row_ptr[n_rows] = number of edges).  `degrees` and `row_ptr` are DEVICE pointers on
+ * `device`; the kernels are issued on `cuda_stream` (a cudaStream_t, NULL = default stream) and the call returns
+ * without synchronising.  It needs no dgnn_ctx and calls no cudaMalloc / cudaFree / allocating routine: the scan's
+ * per-tile sums live in a fixed __device__ array of 65 544 bytes inside the library (every GPU that loads the library
+ * holds it until the process exits).
+ *   Limit: n_rows <= DGNN_NOALLOC_MAX_ROWS (2^24); more is rejected with DGNN_ERR_TOO_LARGE.
+ *   All calls on one device share that array: calls that overlap on the GPU (different streams, concurrent host
+ *   threads) race -- issue them on one stream or order them with events.  Nothing in it needs clearing between calls.
+ *   err / err_len: optional buffer for the message of a failing call (may be NULL / 0).
+ * Makes `device` the calling thread's current device, like every other entry point here. */
+#define DGNN_NOALLOC_MAX_ROWS (1LL << 24)
+int dgnn_row_offsets_noalloc(int device, const int32_t* degrees, int64_t n_rows, int64_t* row_ptr, void* cuda_stream,
+                             char* err, size_t err_len);
+
 /* The CUDA stream (cudaStream_t) all work of this ctx is issued on, for event timing by callers. */
 void* dgnn_stream(dgnn_ctx* ctx);
 
