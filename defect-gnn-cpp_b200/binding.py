@@ -75,7 +75,7 @@ class DgnnBuildInfo(C.Structure):
         ("staged_tile_cap", C.c_int32), ("row_cap", C.c_int32),
         ("n_cell_structs", C.c_int32), ("direct_warps", C.c_int32), ("rbf_fused", C.c_int32), ("hit_cap", C.c_int32),
         ("onepass", C.c_int32), ("onepass_fallback_rows", C.c_int32),
-        ("tie_run_mean", C.c_float), ("full_tie_sort", C.c_int32),
+        ("tie_run_mean", C.c_float), ("full_tie_sort", C.c_int32), ("split_big_rows", C.c_int32),
     ]
 
 

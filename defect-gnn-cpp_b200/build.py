@@ -19,7 +19,7 @@ def build_library(force: bool = False) -> str:
     csrc = os.path.join(HERE, "csrc")
     if force:
         _run(["make", "-C", csrc, "clean"])
-    _run(["make", "-C", csrc, "all"])
+    _run(["make", "-C", csrc, f"-j{max(1, min(8, os.cpu_count() or 1))}", "all"])
     out = os.path.join(HERE, "libdgnn_b200.so")
     if not os.path.exists(out):
         raise RuntimeError("libdgnn_b200.so was not produced")

@@ -48,11 +48,15 @@ int dgnn_create(int device, size_t arena_bytes, dgnn_ctx** out) {
     if (prop.major < 10) return bail(DGNN_ERR_UNSUPPORTED);  // sm_100a cubin only
     ctx->sm_count = prop.multiProcessorCount;
     ctx->smem_optin = (int)prop.sharedMemPerBlockOptin;
+    ctx->smem_per_sm = (int)prop.sharedMemPerMultiprocessor;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     for (auto& e : ctx->copy_ev)
         if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     if (cudaEventCreateWithFlags(&ctx->copy_meta_ev, cudaEventDisableTiming) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (cudaStreamCreateWithFlags(&ctx->aux_stream, cudaStreamNonBlocking) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (cudaEventCreateWithFlags(&ctx->aux_fork, cudaEventDisableTiming) != cudaSuccess) return bail(DGNN_ERR_CUDA);
+    if (cudaEventCreateWithFlags(&ctx->aux_join, cudaEventDisableTiming) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     for (auto& e : ctx->ev.e)
         if (cudaEventCreate(&e) != cudaSuccess) return bail(DGNN_ERR_CUDA);
     if (cudaMallocHost(&ctx->h_stats, sizeof(DgStats)) != cudaSuccess) return bail(DGNN_ERR_CUDA);
@@ -93,6 +97,9 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     for (auto& e : ctx->copy_ev)
         if (e) cudaEventDestroy(e);
     if (ctx->copy_meta_ev) cudaEventDestroy(ctx->copy_meta_ev);
+    if (ctx->aux_fork) cudaEventDestroy(ctx->aux_fork);
+    if (ctx->aux_join) cudaEventDestroy(ctx->aux_join);
+    if (ctx->aux_stream) cudaStreamDestroy(ctx->aux_stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -194,6 +201,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
+    } else if (!strcmp(name, "split_rows")) {
+        ctx->split_rows = value != 0.0;
     } else if (!strcmp(name, "hit_threshold")) {
         ctx->hit_threshold = value != 0.0;
     } else if (!strcmp(name, "fill_hits_warps")) {
@@ -546,6 +555,25 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             onepass = true;
         }
     }
+    // Skewed degrees: the fill pass sizes every warp's row buffer for the largest row, and a few dense rows (config 3:
+    // mean degree 180, max 841) take it from 16 warps per SM to 4.  split_cap is the largest buffer that still gives
+    // 2 CTAs x 8 warps; the count pass tallies the rows beyond it, and when they are few they get a launch of their own.
+    int split_cap = 0, split_main_smem = 0;
+    if (ctx->split_rows) {
+        DgDirectArgs T = D;
+        T.n_warps = 8;
+        // (two main CTAs per SM, and one main CTA next to the large-row CTA of >= 4 warps of up to ~30 KB each)
+        const int budget = (ctx->smem_per_sm - 3 * 1024) * 7 / 16;
+        for (int rc = 512; rc >= 128; rc -= 32) {
+            T.row_cap = rc;
+            T.n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (rc <= 256 ? 256 : 512);
+            if ((int)dg_direct_smem_bytes(T, true) <= budget) {
+                split_cap = rc;
+                split_main_smem = (int)dg_direct_smem_bytes(T, true) + 2 * 1024;
+                break;
+            }
+        }
+    }
     // (a batch of cell-list structures only -- config 4 -- has no rows for the direct kernels: they are not launched)
     const bool any_direct = !have_est || ctx->h_stats->n_direct_structs > 0;
     if (!onepass && any_direct) {
@@ -574,6 +602,9 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             }
             D.row_begin = D.row_end = 0;
             dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
+            if (split_cap > 0 && D.hit_cap == 0)
+                dg_launch_count_big_rows(st, N, (const int*)ctx->astruct.p, small, (const int*)ctx->deg_raw.p, split_cap,
+                                         d_stats, ctx->sm_count);
             // rows that may go through the uncapped fill kernel: sample their sort keys for ties (result arrives with
             // the statistics of sync 1)
             if (ctx->tie_probe == 1 && max_nb >= 32) CU(dg_launch_tie_probe(st, D));
@@ -774,8 +805,17 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     ENSURE(ctx->dst, (size_t)(E + 1) * 4);
     ENSURE(ctx->image, (size_t)(E + 1) * 4);
     ENSURE(ctx->dist, (size_t)(E + 1) * 8);
-    const int row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
-    const int n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 256 ? 256 : (row_cap <= 1024 ? 512 : 1024));
+    int row_cap = round_up(max_deg > 32 ? max_deg : 32, 32);
+    int n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 256 ? 256 : (row_cap <= 1024 ? 512 : 1024));
+    // rows beyond split_cap are few: the bulk of the rows runs with the small row buffer (full occupancy), the rest
+    // in a second launch with the large one
+    const int row_cap_big = row_cap, n_buckets_big = n_buckets;
+    const bool split_fill = !onepass && split_cap > 0 && hit_cap == 0 && row_cap > split_cap && any_direct &&
+                            (long long)ctx->h_stats->n_big_rows * 8 <= N;
+    if (split_fill) {
+        row_cap = split_cap;
+        n_buckets = ctx->sort_buckets > 0 ? ctx->sort_buckets : (row_cap <= 256 ? 256 : 512);
+    }
     D.row_ptr = (const long long*)ctx->row_ptr.p;
     D.dst = (int*)ctx->dst.p;
     D.image = (uint32_t*)ctx->image.p;
@@ -832,8 +872,30 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     }
     if (E > 0 && use_hits && (any_direct || (n_cell_structs > 0 && !cell32))) CU(dg_launch_fill_hits(st, H, ctx->sm_count));
     if (E > 0 && !onepass && any_direct && (!use_hits || n_fallback_rows > 0)) {
+        // split fill: the few rows beyond split_cap go first, on the auxiliary stream, with a buffer for the largest row
+        // (one CTA of few warps per SM); the main launch's CTAs fit beside it (split_cap leaves room), so the large
+        // rows do not cost a low-occupancy tail of their own
+        const bool aux = split_fill && ctx->h_stats->n_big_rows > 0;
+        if (aux) {
+            DgDirectArgs B2 = D;
+            B2.row_cap = row_cap_big;
+            B2.n_buckets = n_buckets_big;
+            B2.skip_deg_le = split_cap;  // (rows up to split_cap entries are written by the main launch)
+            B2.n_warps = 8;
+            while (B2.n_warps > 1 && (int)dg_direct_smem_bytes(B2, true) > ctx->smem_optin - split_main_smem) B2.n_warps -= 1;
+            if ((int)dg_direct_smem_bytes(B2, true) > ctx->smem_optin)
+                return fail(ctx, DGNN_ERR_DEGREE, "row buffer for degree %d does not fit in shared memory", max_deg);
+            dyn_arm(B2);
+            CU(cudaEventRecord(ctx->aux_fork, st));
+            CU(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
+            CU(dg_launch_direct(ctx->aux_stream, B2, true, ctx->sm_count, ctx->direct_min_blocks));
+            CU(cudaEventRecord(ctx->aux_join, ctx->aux_stream));
+        }
         dyn_arm(D);
+        D.defer_big = split_fill ? 1 : 0;
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
+        D.defer_big = 0;
+        if (aux) CU(cudaStreamWaitEvent(st, ctx->aux_join, 0));
     }
     bool cell32_rest = false;  // rows the fp32-tile fill left to the fp64 traversal (degree beyond the register sort)
     if (cell32 && E > 0) {
@@ -841,7 +903,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         A.dst = (int*)ctx->dst.p;
         A.image = (uint32_t*)ctx->image.p;
         A.dist = (double*)ctx->dist.p;
-        A.row_cap = row_cap < 512 ? row_cap : 512;
+        A.row_cap = row_cap_big < 512 ? row_cap_big : 512;
         A.n_warps = ctx->cell32_fill_warps;  // the tile is staged in fp32 and in fp64: one CTA per SM shares it
         if (A.row_cap > 256 && A.n_warps > 16) A.n_warps = 16;  // (the 512-entry sort network needs 128 registers)
         A.rbf = D.rbf;
@@ -870,8 +932,8 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         A.dst = (int*)ctx->dst.p;
         A.image = (uint32_t*)ctx->image.p;
         A.dist = (double*)ctx->dist.p;
-        A.row_cap = row_cap;
-        A.n_buckets = n_buckets;
+        A.row_cap = row_cap_big;
+        A.n_buckets = n_buckets_big;
         A.n_warps = 8;
         A.rbf = D.rbf;
         while (A.n_warps > 1 && (int)dg_traverse_smem_bytes(A, true) > ctx->smem_optin) A.n_warps >>= 1;
@@ -946,6 +1008,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
     I.onepass_fallback_rows = onepass ? n_fallback_rows : 0;
     I.tie_run_mean = (float)tie_run_mean;
     I.full_tie_sort = (!onepass && max_nb >= row_cap && D.full_tie_sort) ? 1 : 0;
+    I.split_big_rows = split_fill ? ctx->h_stats->n_big_rows : 0;
     return DGNN_OK;
 }
 

@@ -37,6 +37,7 @@ struct dgnn_ctx {
     cudaStream_t stream = nullptr;
     int sm_count = 148;
     int smem_optin = 0;
+    int smem_per_sm = 0;
     std::string err;
     // inputs staged from host
     DevBuf in_off, in_x, in_y, in_z, in_lat;
@@ -68,6 +69,8 @@ struct dgnn_ctx {
     cudaEvent_t copy_ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // stream ...
     long long upload_min_atoms = 1 << 18; // smaller batches go up in one piece
     cudaEvent_t copy_meta_ev = nullptr;
+    cudaStream_t aux_stream = nullptr;    // split fill pass: the launch of the few large rows runs beside the main one
+    cudaEvent_t aux_fork = nullptr, aux_join = nullptr;
     int64_t* sink_row_ptr = nullptr;      // dgnn_set_offset_sinks
     int64_t* sink_seo = nullptr;
     int upload_chunks = 4;                // ... while the per-atom prep + count pass of earlier chunks already run
@@ -79,6 +82,7 @@ struct dgnn_ctx {
     int hit_threshold = 1;                // truncated rows: hit lists hold only pairs below a per-structure d2 threshold
     int fill_hits_warps = 0;              // (tuning) warps per CTA of k_fill_hits, 0: most resident warps per SM
     int tie_probe = 1;                    // 1: sampled rows choose the tie ranking of the uncapped fill pass, 0 / 2: fixed
+    int split_rows = 1;                   // fill pass: rows beyond the full-occupancy row buffer get a launch of their own when few
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)
     bool onepass_skip = false;            // (set while a build whose look-back timed out is being redone in two passes)

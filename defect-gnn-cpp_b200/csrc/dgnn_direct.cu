@@ -175,8 +175,9 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                         if (!ok) atomicAdd(&A.stats->n_fallback_rows, 1);                                                \
                     }                                                                                                    \
                 }                                                                                                        \
-            } else if (m > A.row_cap) { /* cannot happen: row_cap >= max degree of the count pass */                     \
-                if (lane == 0) atomicExch(&A.stats->overflow, 1);                                                        \
+            } else if (m > A.row_cap) { /* defer_big: a later launch with a larger row buffer owns the row; otherwise */ \
+                /* it cannot happen (row_cap >= max degree of the count pass) */                                        \
+                if (lane == 0 && !A.defer_big) atomicExch(&A.stats->overflow, 1);                                        \
             } else {                                                                                                     \
                 dg_row_sort_emit<LEAN>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image,    \
                                        A.dist, A.stats, lane, A.rbf);                                                    \
@@ -210,6 +211,29 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
             if (maxdeg) atomicMax(&A.stats->max_deg, maxdeg);
         }
     }
+}
+
+// Rows whose degree exceeds `cap` (direct-path structures only): a handful of dense rows would otherwise size every
+// warp's row buffer and take the whole fill pass down to a quarter of its occupancy (config 3: mean degree 180, max 841).
+__global__ void __launch_bounds__(256) k_count_big_rows(long long N, const int* __restrict__ astruct,
+                                                        const DgSmall* __restrict__ small,
+                                                        const int* __restrict__ deg_raw, int cap,
+                                                        DgStats* __restrict__ stats) {
+    int n = 0;
+    for (long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x; a < N; a += (long long)gridDim.x * blockDim.x) {
+        const DgSmall* __restrict__ G = small + astruct[a];
+        n += (G->mode != DG_MODE_CELL && G->status == DG_ST_OK && deg_raw[a] > cap) ? 1 : 0;
+    }
+    n = __reduce_add_sync(FULL_MASK, n);
+    if ((threadIdx.x & 31) == 0 && n) atomicAdd(&stats->n_big_rows, n);
+}
+void dg_launch_count_big_rows(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
+                              int cap, DgStats* stats, int sm_count) {
+    if (N <= 0) return;
+    long long g = (N + 255) / 256;
+    if (g > (long long)sm_count * 8) g = (long long)sm_count * 8;
+    k_count_big_rows<<<(unsigned)g, 256, 0, st>>>(N, astruct, small, deg_raw, cap, stats);
+    dg_direct_launch_bump(1);
 }
 
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {

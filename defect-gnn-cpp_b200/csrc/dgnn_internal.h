@@ -31,6 +31,8 @@ struct DgStats {
     int est_sparse;              // 1000000 - smallest per-structure degree estimate (0: no non-empty structure)
     unsigned long long tie_sum;  // dgnn_tie_probe.cu: sum over probed entries of the entries sharing their sort key ...
     unsigned long long tie_n;    // ... and the number of probed entries (ratio = mean run length; 1.0: no ties)
+    int n_big_rows;              // direct-path rows whose degree exceeds the row buffer that still gives the fill pass
+                                 // its full occupancy (k_count_big_rows): they get a fill launch of their own
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -177,6 +179,7 @@ struct DgDirectArgs {
     int* hits_n;                    // [N]
     int fill_hits_warps;            // k_fill_hits: warps per CTA (0: the count that puts the most warps on an SM)
     int full_tie_sort;              // uncapped fill pass: 1 = warp-cooperative tie ranking (batches the probe found tie-heavy)
+    int defer_big;                  // fill pass: rows with more than row_cap pairs are left to a later launch (no overflow flag)
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -191,6 +194,9 @@ void dg_launch_direct_prep(cudaStream_t st, long long a_begin, long long a_end, 
 size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill);
 cudaError_t dg_launch_direct(cudaStream_t st, const DgDirectArgs& a, bool fill, int sm_count, int min_blocks);
 void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count);
+// stats->n_big_rows += direct-path rows with deg_raw > cap
+void dg_launch_count_big_rows(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
+                              int cap, DgStats* stats, int sm_count);
 cudaError_t dg_launch_tie_probe(cudaStream_t st, const DgDirectArgs& a);  // dgnn_tie_probe.cu
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);

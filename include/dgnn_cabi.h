@@ -232,6 +232,8 @@ typedef struct {
     float tie_run_mean;      /* sampled rows: mean number of entries sharing a truncated sort key (1.0: none; 0: the
                               * build did not probe).  Ideal lattices put whole coordination shells on one key */
     int32_t full_tie_sort;   /* 1: the uncapped fill pass ran with the warp-cooperative tie ranking (tie_run_mean >= 3) */
+    int32_t split_big_rows;  /* > 0: skewed degrees -- this many rows beyond the full-occupancy row buffer (row_cap) were
+                              * filled by a second launch with a buffer for the largest row; 0: one fill launch */
 } dgnn_build_info;
 int dgnn_last_build_info(const dgnn_ctx* ctx, dgnn_build_info* out);
 

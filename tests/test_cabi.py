@@ -30,7 +30,7 @@ def test_struct_layouts_match_header(pkg):
     b = pkg.binding
     assert C.sizeof(b.DgnnBatch) == 8 * 6 + 8 * 5 + 8   # 6 ptr/int64, r_cutoff/max_nbr/eps/rbf_rc/dr, flags(+pad)
     assert C.sizeof(b.DgnnGraphs) == 8 * 3 + 4 * 2 + 8 * 6 + 8 * 2
-    assert C.sizeof(b.DgnnBuildInfo) == 4 * 6 + 4 * 2 + 8 + 4 * 8 + 4 * 2
+    assert C.sizeof(b.DgnnBuildInfo) == 4 * 6 + 4 * 2 + 8 + 4 * 8 + 4 * 2 + 4 + 4   # (+ split_big_rows, + tail padding)
 
 
 def test_no_cpu_fallback(pkg):

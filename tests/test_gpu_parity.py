@@ -121,6 +121,32 @@ def test_c3_triclinic_short_vectors(gpu_builder, gpu_builder_cell, oracle, syn):
     assert np.any(local_src == h.dst)
 
 
+def test_skewed_degrees_split_the_fill_pass(pkg, oracle, syn):
+    """A few dense rows must not size every warp's row buffer: rows beyond the full-occupancy buffer are filled by a
+    second launch (dgnn_build_info.split_big_rows), the rest by the first; both equal the oracle, and the single-launch
+    plan (tune.split_rows = 0) gives the same graphs."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    c3 = syn.c3_batch(400, seed0=4242)
+    mixed = syn.concat([syn.c2_batch(3, seed0=5).structure(s) for s in range(3)] +
+                       [syn.triclinic_cell(9000 + s)[:4] for s in range(12)])
+    for split in (1, 0):
+        gb = pkg.GraphBuilder(0)
+        gb.set_option("onepass", 0)
+        gb.set_option("tune.split_rows", split)
+        seen = []
+        for b, rc, cap in ((c3, 8.0, None), (mixed, 8.0, None), (c3, 8.0, 400), (c3, 6.0, None)):
+            h = check_batch(gb, oracle, b, rc, cap, dr=0.2)
+            seen.append((gb.info().split_big_rows, gb.info().row_cap, int(np.diff(h.row_ptr).max())))
+        if split:
+            assert seen[0][0] > 0 and seen[0][1] < seen[0][2]      # C3: max degree ~800, buffer of the first launch ~350
+            assert all(n * 8 <= c3.n_atoms for n, _, _ in seen)
+        else:
+            assert all(n == 0 for n, _, _ in seen)
+        gb.close()
+
+
 def test_adversarial_cells_reference_image_range(gpu_builder, gpu_builder_cell, oracle, syn):
     b = syn.adversarial_cells()
     for gb in (gpu_builder, gpu_builder_cell):
