@@ -586,10 +586,20 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
         }
         {
+            bool probe_forked = false;
             for (int c = 0; c < n_up; ++c) {
                 if (!dev_in) CU(cudaStreamWaitEvent(st, ctx->copy_ev[c], 0));
                 dg_launch_direct_prep(st, up_a[c], up_a[c + 1], S, d_off, d_x, d_y, d_z, small, (int*)ctx->astruct.p,
                                       (double*)ctx->fa.p, (double*)ctx->fb.p, (double*)ctx->fc.p, d_stats);
+                // rows that may go through the uncapped fill kernel: sample their sort keys for ties -- beside the
+                // last chunk's count pass, on the auxiliary stream (the result arrives with the statistics of sync 1)
+                if (c == n_up - 1 && ctx->tie_probe == 1 && max_nb >= 32) {
+                    CU(cudaEventRecord(ctx->aux_fork, st));
+                    CU(cudaStreamWaitEvent(ctx->aux_stream, ctx->aux_fork, 0));
+                    CU(dg_launch_tie_probe(ctx->aux_stream, D));
+                    CU(cudaEventRecord(ctx->aux_join, ctx->aux_stream));
+                    probe_forked = true;
+                }
                 if (up_a[c + 1] > up_a[c]) {
                     D.row_begin = up_a[c];
                     D.row_end = up_a[c + 1];
@@ -605,9 +615,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             if (split_cap > 0 && D.hit_cap == 0)
                 dg_launch_count_big_rows(st, N, (const int*)ctx->astruct.p, small, (const int*)ctx->deg_raw.p, split_cap,
                                          d_stats, ctx->sm_count);
-            // rows that may go through the uncapped fill kernel: sample their sort keys for ties (result arrives with
-            // the statistics of sync 1)
-            if (ctx->tie_probe == 1 && max_nb >= 32) CU(dg_launch_tie_probe(st, D));
+            if (probe_forked) CU(cudaStreamWaitEvent(st, ctx->aux_join, 0));
         }
     } else if (!onepass) {
         // the cell-list kernels still need the uploaded coordinates, and empty batches a valid (all zero) row_ptr
