@@ -84,7 +84,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
-                      &ctx->deg, &ctx->deg_raw, &ctx->hits, &ctx->hits_d2, &ctx->hits_n, &ctx->hit_thr, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->deg, &ctx->deg_raw, &ctx->row_perm, &ctx->hits, &ctx->hits_d2, &ctx->hits_n, &ctx->hit_thr, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats, &ctx->col_x, &ctx->col_ei, &ctx->col_batch, &ctx->col_keys,
                       &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b, &ctx->tab_cnt, &ctx->tab_ptr,
                       &ctx->tab_val};
@@ -901,8 +901,20 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         dyn_arm(D);
         D.defer_big = split_fill ? 1 : 0;
+        if (split_fill && D.dyn_unit > 0) {
+            // rows of very different lengths run different sort networks; in class order the warps of an SM execute
+            // the same code at the same time (instruction-cache misses were the top stall of the config-3 fill pass)
+            const long long n_perm = (long long)ctx->h_stats->cls_n[0] + ctx->h_stats->cls_n[1] + ctx->h_stats->cls_n[2] +
+                                     ctx->h_stats->cls_n[3];
+            ENSURE(ctx->row_perm, (size_t)(N + 32) * 4);
+            dg_launch_class_scatter(st, N, (const int*)ctx->astruct.p, small, (const int*)ctx->deg_raw.p, split_cap,
+                                    d_stats, (int*)ctx->row_perm.p, ctx->sm_count);
+            D.row_perm = (const int*)ctx->row_perm.p;
+            D.n_perm = n_perm;
+        }
         CU(dg_launch_direct(st, D, true, ctx->sm_count, ctx->direct_min_blocks));
         D.defer_big = 0;
+        D.row_perm = nullptr;
         if (aux) CU(cudaStreamWaitEvent(st, ctx->aux_join, 0));
     }
     bool cell32_rest = false;  // rows the fp32-tile fill left to the fp64 traversal (degree beyond the register sort)

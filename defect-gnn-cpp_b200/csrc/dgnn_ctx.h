@@ -46,7 +46,7 @@ struct dgnn_ctx {
     DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
     DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
     // results
-    DevBuf deg, deg_raw, hits, hits_d2, hits_n, hit_thr, row_ptr, seo, dst, image, dist, rbf;
+    DevBuf deg, deg_raw, row_perm, hits, hits_d2, hits_n, hit_thr, row_ptr, seo, dst, image, dist, rbf;
     // stand-alone rbf staging
     DevBuf tmp_in, tmp_out;
     DevBuf stats;

@@ -183,14 +183,17 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                                        A.dist, A.stats, lane, A.rbf);                                                    \
             }
     if (DYN) {
+        const int* __restrict__ perm = A.row_perm;
+        const long long n_rows = perm ? A.n_perm : r1 - r0;
         for (;;) {
             unsigned long long u = 0;
             if (lane == 0) u = atomicAdd(A.unit_ctr, 1ULL);
             u = __shfl_sync(FULL_MASK, u, 0);
-            const long long a_first = r0 + (long long)u * A.dyn_unit;
-            if (a_first >= r1) break;
-            const long long a_end = a_first + A.dyn_unit < r1 ? a_first + A.dyn_unit : r1;
-            for (long long a = a_first; a < a_end; ++a) {
+            const long long i_first = (long long)u * A.dyn_unit;
+            if (i_first >= n_rows) break;
+            const long long i_end = i_first + A.dyn_unit < n_rows ? i_first + A.dyn_unit : n_rows;
+            for (long long i = i_first; i < i_end; ++i) {
+                const long long a = perm ? (long long)perm[i] : r0 + i;
                 DG_DIRECT_ROW_BODY
             }
         }
@@ -215,17 +218,35 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
 
 // Rows whose degree exceeds `cap` (direct-path structures only): a handful of dense rows would otherwise size every
 // warp's row buffer and take the whole fill pass down to a quarter of its occupancy (config 3: mean degree 180, max 841).
+__device__ __forceinline__ int dg_row_class(int m) { return m <= 64 ? 0 : (m <= 128 ? 1 : (m <= 256 ? 2 : 3)); }
 __global__ void __launch_bounds__(256) k_count_big_rows(long long N, const int* __restrict__ astruct,
                                                         const DgSmall* __restrict__ small,
                                                         const int* __restrict__ deg_raw, int cap,
                                                         DgStats* __restrict__ stats) {
-    int n = 0;
+    int n = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
     for (long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x; a < N; a += (long long)gridDim.x * blockDim.x) {
         const DgSmall* __restrict__ G = small + astruct[a];
-        n += (G->mode != DG_MODE_CELL && G->status == DG_ST_OK && deg_raw[a] > cap) ? 1 : 0;
+        if (G->mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;
+        const int m = deg_raw[a];
+        if (m > cap) {
+            ++n;
+        } else {
+            const int c = dg_row_class(m);
+            c0 += c == 0; c1 += c == 1; c2 += c == 2; c3 += c == 3;
+        }
     }
     n = __reduce_add_sync(FULL_MASK, n);
-    if ((threadIdx.x & 31) == 0 && n) atomicAdd(&stats->n_big_rows, n);
+    c0 = __reduce_add_sync(FULL_MASK, c0);
+    c1 = __reduce_add_sync(FULL_MASK, c1);
+    c2 = __reduce_add_sync(FULL_MASK, c2);
+    c3 = __reduce_add_sync(FULL_MASK, c3);
+    if ((threadIdx.x & 31) == 0) {
+        if (n) atomicAdd(&stats->n_big_rows, n);
+        if (c0) atomicAdd(&stats->cls_n[0], c0);
+        if (c1) atomicAdd(&stats->cls_n[1], c1);
+        if (c2) atomicAdd(&stats->cls_n[2], c2);
+        if (c3) atomicAdd(&stats->cls_n[3], c3);
+    }
 }
 void dg_launch_count_big_rows(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
                               int cap, DgStats* stats, int sm_count) {
@@ -233,6 +254,44 @@ void dg_launch_count_big_rows(cudaStream_t st, long long N, const int* astruct, 
     long long g = (N + 255) / 256;
     if (g > (long long)sm_count * 8) g = (long long)sm_count * 8;
     k_count_big_rows<<<(unsigned)g, 256, 0, st>>>(N, astruct, small, deg_raw, cap, stats);
+    dg_direct_launch_bump(1);
+}
+// Rows grouped by class, runs of consecutive rows of a class kept together (a warp places its 32 rows class by class
+// with one atomic per class): the atoms of a structure mostly stay adjacent, so its lines stay in L1.
+__global__ void __launch_bounds__(256) k_class_scatter(long long N, const int* __restrict__ astruct,
+                                                       const DgSmall* __restrict__ small,
+                                                       const int* __restrict__ deg_raw, int cap,
+                                                       DgStats* __restrict__ stats, int* __restrict__ perm) {
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int b1 = stats->cls_n[0], b2 = b1 + stats->cls_n[1], b3 = b2 + stats->cls_n[2];
+    const long long n32 = (N + 31) & ~31LL;
+    for (long long a = (long long)blockIdx.x * blockDim.x + threadIdx.x; a < n32; a += (long long)gridDim.x * blockDim.x) {
+        int c = -1;
+        if (a < N) {
+            const DgSmall* __restrict__ G = small + astruct[a];
+            if (G->mode != DG_MODE_CELL && G->status == DG_ST_OK) {
+                const int m = deg_raw[a];
+                if (m <= cap) c = dg_row_class(m);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const unsigned mask = __ballot_sync(FULL_MASK, c == k);
+            if (mask == 0u) continue;
+            int base = 0;
+            if (lane == __ffs(mask) - 1) base = atomicAdd(&stats->cls_fill[k], __popc(mask));
+            base = __shfl_sync(FULL_MASK, base, __ffs(mask) - 1);
+            if (c == k) perm[(k == 0 ? 0 : (k == 1 ? b1 : (k == 2 ? b2 : b3))) + base + __popc(mask & lt_mask)] = (int)a;
+        }
+    }
+}
+void dg_launch_class_scatter(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
+                             int cap, DgStats* stats, int* perm, int sm_count) {
+    if (N <= 0) return;
+    long long g = (N + 255) / 256;
+    if (g > (long long)sm_count * 8) g = (long long)sm_count * 8;
+    k_class_scatter<<<(unsigned)g, 256, 0, st>>>(N, astruct, small, deg_raw, cap, stats, perm);
     dg_direct_launch_bump(1);
 }
 
@@ -249,7 +308,7 @@ static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int s
     if (e != cudaSuccess) return e;
     if (occ < 1) occ = 1;
     // persistent grid: every SM full; static schedule = chunks of DG_ROW_CHUNK consecutive rows round-robin over CTAs
-    const long long rows = (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
+    const long long rows = (DYN && a.row_perm) ? a.n_perm : (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
     const long long want = DYN ? (rows + (long long)a.dyn_unit * (threads / 32) - 1) / ((long long)a.dyn_unit * (threads / 32))
                                : (rows + DG_ROW_CHUNK - 1) / DG_ROW_CHUNK;
     long long grid = (long long)sm_count * occ;

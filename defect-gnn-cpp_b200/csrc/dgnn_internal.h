@@ -33,6 +33,8 @@ struct DgStats {
     unsigned long long tie_n;    // ... and the number of probed entries (ratio = mean run length; 1.0: no ties)
     int n_big_rows;              // direct-path rows whose degree exceeds the row buffer that still gives the fill pass
                                  // its full occupancy (k_count_big_rows): they get a fill launch of their own
+    int cls_n[4];                // ... and the other direct-path rows by sort-network class (<= 64, 128, 256, more entries)
+    int cls_fill[4];             // k_class_scatter: slots handed out per class
 };
 
 // Fused RBF epilogue of the fill passes (row_sort.cuh).  K4 = 0: no features in this launch.
@@ -180,6 +182,10 @@ struct DgDirectArgs {
     int fill_hits_warps;            // k_fill_hits: warps per CTA (0: the count that puts the most warps on an SM)
     int full_tie_sort;              // uncapped fill pass: 1 = warp-cooperative tie ranking (batches the probe found tie-heavy)
     int defer_big;                  // fill pass: rows with more than row_cap pairs are left to a later launch (no overflow flag)
+    // dynamically scheduled fill pass: rows in the order of row_perm[0, n_perm) (grouped by sort-network class, so that
+    // the warps of an SM run the same code at the same time: the kernel is ~190 KB of SASS); null = rows in order
+    const int* row_perm;
+    long long n_perm;
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27
@@ -197,6 +203,9 @@ void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count)
 // stats->n_big_rows += direct-path rows with deg_raw > cap
 void dg_launch_count_big_rows(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
                               int cap, DgStats* stats, int sm_count);
+// perm[0, sum of stats->cls_n) = the direct-path rows with deg_raw <= cap grouped by class (after dg_launch_count_big_rows)
+void dg_launch_class_scatter(cudaStream_t st, long long N, const int* astruct, const DgSmall* small, const int* deg_raw,
+                             int cap, DgStats* stats, int* perm, int sm_count);
 cudaError_t dg_launch_tie_probe(cudaStream_t st, const DgDirectArgs& a);  // dgnn_tie_probe.cu
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks);
 size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a);
