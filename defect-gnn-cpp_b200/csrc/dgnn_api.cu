@@ -901,7 +901,17 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         dyn_arm(D);
         D.defer_big = split_fill ? 1 : 0;
-        if (split_fill && D.dyn_unit > 0) {
+        bool class_order = false;
+        if (D.dyn_unit > 0 && hit_cap == 0 && split_cap > 0 && (split_fill || ctx->h_stats->n_big_rows == 0)) {
+            // (worth it when at least 5 % of the rows are outside the dominant class)
+            long long tot = 0, mx = 0;
+            for (int k = 0; k < 4; ++k) {
+                tot += ctx->h_stats->cls_n[k];
+                if (ctx->h_stats->cls_n[k] > mx) mx = ctx->h_stats->cls_n[k];
+            }
+            class_order = (tot - mx) * 20 >= tot && tot > 0;
+        }
+        if (class_order) {
             // rows of very different lengths run different sort networks; in class order the warps of an SM execute
             // the same code at the same time (instruction-cache misses were the top stall of the config-3 fill pass)
             const long long n_perm = (long long)ctx->h_stats->cls_n[0] + ctx->h_stats->cls_n[1] + ctx->h_stats->cls_n[2] +

@@ -153,8 +153,8 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                 ht.d2_max = A.hit_d2_max ? A.hit_d2_max[A.astruct[a]] : DG_INF;                                          \
                 ht.d2_lo = ht.d2_max * (1.0 - 3.814697265625e-6);                                                        \
             }                                                                                                            \
-            int m = HITS ? traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht)   \
-                         : traverse_row<FILL, EPS, HITS, false>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);      \
+            int m = HITS ? traverse_row<FILL, EPS, HITS, false, DYN>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht) \
+                         : traverse_row<FILL, EPS, HITS, false, DYN>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near);  \
             if (!FILL && !HITS) m = __reduce_add_sync(FULL_MASK, m);                                                     \
             int mh = 0, mlo = 0; /* HITS: stored pairs, pairs safely below the storing threshold */                      \
             if (HITS) {                                                                                                  \

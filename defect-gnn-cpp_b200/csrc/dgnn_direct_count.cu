@@ -114,7 +114,7 @@ __device__ __noinline__ void count_row_imgpar(const DgDirectArgs& A, const DgSma
                                               int lane, unsigned* near_io) {
     const RowBuf rb = RowBuf{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     unsigned near = 0;
-    int m = traverse_row<false, EPS, false, false>(A, G, a, mode, rb, nullptr, nullptr, lane, (1u << lane) - 1u, near);
+    int m = traverse_row<false, EPS, false, false, true>(A, G, a, mode, rb, nullptr, nullptr, lane, (1u << lane) - 1u, near);
     m = __reduce_add_sync(FULL_MASK, m);
     if (lane == 0 && m) atomicAdd(A.deg_raw + a, m);
     *near_io += near;

@@ -122,7 +122,10 @@ __device__ __forceinline__ void test_point(const DgDirectArgs& A, const Src& S, 
 // Candidate sweep of one source atom a of structure G (mode: DG_MODE_ATOMPAR / DG_MODE_IMGPAR); returns the number of
 // accepted pairs (per lane when !FILL && !HITS, warp-uniform otherwise; HITS: the STORED pairs, the tallies are in ht).
 // All 32 lanes must call.
-template <bool FILL, int EPS, bool HITS, bool ONE>
+// IMGSTEP: the IMGPAR sweep walks a lane's (n_a, n_b, n_c) with mixed-radix additions of 32 instead of two divisions
+// and two remainders per candidate (same images, same order).  Only the dynamically scheduled instantiations use it:
+// the headline kernel's code generation is kept exactly as it was.
+template <bool FILL, int EPS, bool HITS, bool ONE, bool IMGSTEP = false>
 __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall* __restrict__ G, long long a, int mode,
                                             const RowBuf& rb, uint32_t* __restrict__ hrow, double* __restrict__ hd2,
                                             int lane, unsigned lt_mask, unsigned& near, HitTally& ht) {
@@ -195,6 +198,30 @@ __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall
             const int c1 = axis_window_fast(fi1 - A.fb[gj], w1, nimg, &lo1);
             const int c2 = axis_window_fast(fi2 - A.fc[gj], w2, nimg, &lo2);
             const int T = c0 * c1 * c2;
+            if (IMGSTEP) {
+                if (T == 0) continue;
+                // t = (ia * c1 + ib) * c2 + ic, t = lane, lane + 32, ...: + 32 = + (q / c1, q % c1, 32 % c2), q = 32 / c2
+                const int s2 = 32 % c2, q = 32 / c2, s1 = q % c1, s0 = q / c1;
+                int ic = lane % c2, tq = lane / c2;
+                int ib = tq % c1, ia = tq / c1;
+                for (int tb = 0; tb < T; tb += 32) {
+                    const bool active = tb + lane < T;
+                    const int na = active ? lo0 + ia : lo0, nb = active ? lo1 + ib : lo1, nc = active ? lo2 + ic : lo2;
+                    const double px = DG_ADD(xj, dg_image_offset(G->L, 0, na, nb, nc));
+                    const double py = DG_ADD(yj, dg_image_offset(G->L, 1, na, nb, nc));
+                    const double pz = DG_ADD(zj, dg_image_offset(G->L, 2, na, nb, nc));
+                    test_point<FILL, EPS, HITS, ONE>(A, S, rb, hrow, hd2, active, j == S.iloc, j, px, py, pz, na, nb, nc,
+                                                lt_mask, m, near, ht);
+                    ic += s2;
+                    int carry = ic >= c2 ? 1 : 0;
+                    ic -= carry ? c2 : 0;
+                    ib += s1 + carry;
+                    carry = ib >= c1 ? 1 : 0;
+                    ib -= carry ? c1 : 0;
+                    ia += s0 + carry;
+                }
+                continue;
+            }
             for (int tb = 0; tb < T; tb += 32) {
                 const int t = tb + lane;
                 const bool active = t < T;
@@ -211,12 +238,12 @@ __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall
     }
     return m;
 }
-template <bool FILL, int EPS, bool HITS, bool ONE>
+template <bool FILL, int EPS, bool HITS, bool ONE, bool IMGSTEP = false>
 __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall* __restrict__ G, long long a, int mode,
                                             const RowBuf& rb, uint32_t* __restrict__ hrow, double* __restrict__ hd2,
                                             int lane, unsigned lt_mask, unsigned& near) {
     HitTally ht;  // (dead without HITS)
     ht.tot = ht.lo = 0;
     ht.d2_max = ht.d2_lo = 0.0;
-    return traverse_row<FILL, EPS, HITS, ONE>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht);
+    return traverse_row<FILL, EPS, HITS, ONE, IMGSTEP>(A, G, a, mode, rb, hrow, hd2, lane, lt_mask, near, ht);
 }
