@@ -582,6 +582,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         // without hit lists the count pass is symmetric: one sweep decides i -> j and j -> i (dgnn_direct.cu)
         const bool sym = ctx->sym_count && D.hit_cap == 0 && eps_mode <= 1;
         if (sym) {
+            D.split_cap = split_cap;
             D.sym_band = (D.near_d2_hi - D.near_d2_lo) + 1.0e-9 * r2;
             CU(cudaMemsetAsync(ctx->deg_raw.p, 0, (size_t)(N + 1) * 4, st));
         }
@@ -612,7 +613,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
             }
             D.row_begin = D.row_end = 0;
             dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
-            if (split_cap > 0 && D.hit_cap == 0)
+            if (split_cap > 0 && D.hit_cap == 0 && !sym)  // (the symmetric count's k_cap_degrees has tallied them)
                 dg_launch_count_big_rows(st, N, (const int*)ctx->astruct.p, small, (const int*)ctx->deg_raw.p, split_cap,
                                          d_stats, ctx->sm_count);
             if (probe_forked) CU(cudaStreamWaitEvent(st, ctx->aux_join, 0));

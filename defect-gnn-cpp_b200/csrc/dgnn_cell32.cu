@@ -46,8 +46,9 @@ struct C32Shared {
 
 __host__ __device__ inline size_t c32_align16(size_t v) { return (v + 15) & ~(size_t)15; }
 // tile: float4 per point (+ one sentinel slot that pads the slot lists); FILL also stages the fp64 operands (24 B/point)
+// and the point's (atom, packed image) (8 B/point): the sorted row is emitted without gathers from the cloud arrays
 __host__ __device__ inline size_t c32_shared_part(int tile_cap, int tcs_cap, bool fill) {
-    return c32_align16((size_t)(tile_cap + 1) * 16) + (fill ? c32_align16((size_t)tile_cap * 8) * 3 : 0) +
+    return c32_align16((size_t)(tile_cap + 1) * 16) + (fill ? c32_align16((size_t)tile_cap * 8) * 4 : 0) +
            c32_align16((size_t)tcs_cap * 4) + c32_align16((size_t)(DG_ROWS_CAP + 1) * 4) +
            c32_align16((size_t)DG_STN_CAP * 2) * 2;
 }
@@ -95,6 +96,7 @@ struct C32Warp {
 struct C32Tile {
     const float4* T;
     const double *X, *Y, *Z;  // FILL: the reference's fp64 operands of the tile points
+    const uint2* JN;          // FILL: (local atom index, packed image) of the tile points
     const int* tcs;
     const signed char* stn;   // stencil row q: z-range [stn[2q], stn[2q+1]] (empty if lo > hi)
     const short* srow;        // stencil row q: tile-row offset d_a * td_b + d_b
@@ -147,6 +149,18 @@ __device__ __forceinline__ int c32_build_list(const DgGeom& G, const ItemBox& B,
     return Tp;
 }
 
+struct C32TilePayload {  // FILL: hit word = tile slot; (atom, image) from the staged table
+    uint32_t* hw;
+    const uint2* JN;
+    __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
+    __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
+    __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
+        const uint2 v = JN[hw[e]];
+        j = (int)v.x;
+        img = v.y;
+    }
+};
+
 struct C32Src {
     float x, y, z;       // tile coordinates
     double qx, qy, qz;   // reference operands
@@ -168,7 +182,7 @@ __device__ __forceinline__ int c32_drain(const DgTraverseArgs& A, const C32Share
                                : c32_exact_d2(S.qx, S.qy, S.qz, A.cx[pc], A.cy[pc], A.cz[pc]);
         bool acc = valid && d2 < A.r2;
         if (acc && d2 <= sh.eps_guard2) {  // neighbor_list.cpp:47-49
-            if (A.cj[pc] == S.iloc && __dsqrt_rn(d2) < A.epsilon) acc = false;
+            if ((FILL ? (int)tl.JN[slot].x : A.cj[pc]) == S.iloc && __dsqrt_rn(d2) < A.epsilon) acc = false;
         }
         if (!FILL) {
             if (valid && fabs(__dsqrt_rn(d2) - A.r_cutoff) <= 1e-6) near++;
@@ -179,7 +193,7 @@ __device__ __forceinline__ int c32_drain(const DgTraverseArgs& A, const C32Share
                 const int pos = m + __popc(mask & lt_mask);
                 if (pos < A.row_cap) {
                     w.rd[pos] = d2;
-                    w.hw[pos] = pc;
+                    w.hw[pos] = slot;
                 }
             }
             m += __popc(mask);
@@ -252,10 +266,12 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
     unsigned char* p = smem_raw;
     float4* T = (float4*)p; p += c32_align16((size_t)(A.tile_cap + 1) * 16);
     double *X = nullptr, *Y = nullptr, *Z = nullptr;
+    uint2* JN = nullptr;
     if (FILL) {
         X = (double*)p; p += c32_align16((size_t)A.tile_cap * 8);
         Y = (double*)p; p += c32_align16((size_t)A.tile_cap * 8);
         Z = (double*)p; p += c32_align16((size_t)A.tile_cap * 8);
+        JN = (uint2*)p; p += c32_align16((size_t)A.tile_cap * 8);
     }
     int* tcs = (int*)p; p += c32_align16((size_t)A.tcs_cap * 4);
     int* rowbase = (int*)p; p += c32_align16((size_t)(DG_ROWS_CAP + 1) * 4);
@@ -391,12 +407,14 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                 for (int k = lane; k < cnt; k += 32) {
                     const long long pc = gs + k;
                     const double px = A.cx[pc], py = A.cy[pc], pz = A.cz[pc];
-                    const uint32_t wbits = (uint32_t)pc | (A.cn[pc] != 0u ? C32_IMG_FLAG : 0u);
+                    const uint32_t pn = A.cn[pc];
+                    const uint32_t wbits = (uint32_t)pc | (pn != 0u ? C32_IMG_FLAG : 0u);
                     T[lb + k] = make_float4((float)(px - ox), (float)(py - oy), (float)(pz - oz), __uint_as_float(wbits));
                     if (FILL) {
                         X[lb + k] = px;
                         Y[lb + k] = py;
                         Z[lb + k] = pz;
+                        JN[lb + k] = make_uint2((uint32_t)A.cj[pc], pn);
                     }
                 }
                 for (int c = lane; c <= B.td[2]; c += 32) tcs[r * zs + c] = lb + (int)(A.cellstart[g0 + c] - gs);
@@ -404,7 +422,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
             if (tid == 0) T[total] = make_float4(3.0e18f, 3.0e18f, 3.0e18f, __uint_as_float(C32_IMG_FLAG));
         }
         __syncthreads();
-        const C32Tile tl{T, X, Y, Z, tcs, stn, srow, total};
+        const C32Tile tl{T, X, Y, Z, JN, tcs, stn, srow, total};
 
         const int nbc0 = B.c1[0] - B.c0[0], nbc1 = B.c1[1] - B.c0[1], nbc2 = B.c1[2] - B.c0[2];
         const int nbcells = nbc0 * nbc1 * nbc2;
@@ -418,26 +436,41 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
             tc = bc % nbc2 + G.R[2];
             const int k0 = tcs[(ta * B.td[1] + tb) * zs + tc], k1 = tcs[(ta * B.td[1] + tb) * zs + tc + 1];
             if (k0 < k1) Tn = c32_build_list(G, B, tl, w.idx, A.src_cap, ta, tb, tc, lane);
-            for (int ps = k0; ps < k1; ++ps) {
+            for (int pb = k0; pb < k1; pb += 32) {
+            // FILL: the rows' degrees and CSR offsets of up to 32 source points are fetched lane-parallel, one round trip
+            // per cell instead of two dependent ones per atom
+            int pre_deg = 0;
+            long long pre_o = 0;
+            if (FILL && pb + lane < k1) {
+                const uint32_t wl = __float_as_uint(T[pb + lane].w);
+                if (!(wl & C32_IMG_FLAG)) {
+                    const long long ig = G.atom_base + (int)JN[pb + lane].x;
+                    pre_deg = A.deg_raw[ig];
+                    pre_o = A.row_ptr[ig];
+                }
+            }
+            const int pe = pb + 32 < k1 ? pb + 32 : k1;
+            for (int ps = pb; ps < pe; ++ps) {
                 const float4 sv = T[ps];
                 const uint32_t wb = __float_as_uint(sv.w);
                 if (wb & C32_IMG_FLAG) continue;  // a periodic image that shares the cell: not a source
                 C32Src S;
                 S.x = sv.x; S.y = sv.y; S.z = sv.z;
                 S.pc = wb;
-                S.iloc = A.cj[wb];
                 if (FILL) {
+                    S.iloc = (int)JN[ps].x;
                     S.qx = X[ps]; S.qy = Y[ps]; S.qz = Z[ps];
                 } else {
+                    S.iloc = A.cj[wb];
                     S.qx = A.cx[wb]; S.qy = A.cy[wb]; S.qz = A.cz[wb];
                 }
                 const long long iglob = G.atom_base + S.iloc;
                 int deg_known = 0;
                 long long o = 0;
                 if (FILL) {
-                    deg_known = A.deg_raw[iglob];
+                    deg_known = __shfl_sync(FULL_MASK, pre_deg, ps - pb);
+                    o = __shfl_sync(FULL_MASK, pre_o, ps - pb);
                     if (deg_known > W) continue;  // (rows beyond the register sort: the fp64 traversal's fill)
-                    o = A.row_ptr[iglob];
                 }
                 int cnt = 0, qn = 0, m = 0;
                 if (Tn >= 0) {
@@ -470,7 +503,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                         continue;
                     }
                     const int keep = m < A.max_neighbors ? m : A.max_neighbors;
-                    const CloudPayload P{w.hw, A.cj, A.cn};
+                    const C32TilePayload P{w.hw, JN};
                     dg_row_sort_bitonic_upto<MAXEPL>(w.rd, w.sk, w.fd, w.tie, P, m, keep, A.key_scale, o, A.dst, A.image,
                                                      A.dist, A.stats, lane);
                     if (A.rbf.K4 > 0) {
@@ -478,6 +511,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                         __syncwarp();
                     }
                 }
+            }
             }
             __syncwarp();
             int nxt = 0;

@@ -149,15 +149,40 @@ __global__ void __launch_bounds__(256, MINB) k_direct_count_sym(const __grid_con
 __global__ void __launch_bounds__(256) k_cap_degrees(const DgDirectArgs A) {
     const long long r0 = A.row_begin, r1 = A.row_end > 0 ? A.row_end : A.n_atoms;
     int mx = 0;
+    // (split_cap > 0: rows beyond the full-occupancy row buffer and the others by sort-network class, see dgnn_direct.cu)
+    int nb = 0, c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+    const int cap = A.split_cap;
     for (long long a = r0 + (long long)blockIdx.x * blockDim.x + threadIdx.x; a < r1; a += (long long)gridDim.x * blockDim.x) {
         const DgSmall* __restrict__ G = A.small + A.astruct[a];
         if (G->mode == DG_MODE_CELL || G->status != DG_ST_OK) continue;
         const int m = A.deg_raw[a];
         A.deg_capped[a] = m < A.max_neighbors ? m : A.max_neighbors;
         mx = m > mx ? m : mx;
+        if (cap > 0) {
+            const bool small_row = m <= cap;  // (classes as dg_row_class, dgnn_direct.cu)
+            nb += !small_row;
+            c0 += small_row && m <= 64;
+            c1 += small_row && m > 64 && m <= 128;
+            c2 += small_row && m > 128 && m <= 256;
+            c3 += small_row && m > 256;
+        }
     }
     mx = __reduce_max_sync(FULL_MASK, mx);
     if ((threadIdx.x & 31) == 0 && mx) atomicMax(&A.stats->max_deg, mx);
+    if (cap > 0) {
+        nb = __reduce_add_sync(FULL_MASK, nb);
+        c0 = __reduce_add_sync(FULL_MASK, c0);
+        c1 = __reduce_add_sync(FULL_MASK, c1);
+        c2 = __reduce_add_sync(FULL_MASK, c2);
+        c3 = __reduce_add_sync(FULL_MASK, c3);
+        if ((threadIdx.x & 31) == 0) {
+            if (nb) atomicAdd(&A.stats->n_big_rows, nb);
+            if (c0) atomicAdd(&A.stats->cls_n[0], c0);
+            if (c1) atomicAdd(&A.stats->cls_n[1], c1);
+            if (c2) atomicAdd(&A.stats->cls_n[2], c2);
+            if (c3) atomicAdd(&A.stats->cls_n[3], c3);
+        }
+    }
 }
 
 template <int MINB>

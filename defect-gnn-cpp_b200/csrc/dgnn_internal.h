@@ -186,6 +186,7 @@ struct DgDirectArgs {
     // the warps of an SM run the same code at the same time: the kernel is ~190 KB of SASS); null = rows in order
     const int* row_perm;
     long long n_perm;
+    int split_cap;                  // > 0: k_cap_degrees also tallies stats->n_big_rows / cls_n (as k_count_big_rows does)
 };
 #define DG_EPS_FAST 1.0e-3
 // hit word: neighbour atom (17 bits) | n_a + 16 (5 bits) << 17 | n_b + 16 << 22 | n_c + 16 << 27

@@ -522,19 +522,35 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
             const unsigned inrun = __ballot_sync(FULL_MASK, nb_l || nb_r);
             int rank = p;
             if (inrun) {
-                const unsigned long long ke = (nb_l || nb_r) ? dg_payload_tie_key(P, e) : 0ull;
-                int cnt = 0, first = lane;
-                for (unsigned mask = inrun; mask; mask &= mask - 1) {
-                    const int r = __ffs(mask) - 1;
+                // A shell of an ideal lattice is one run of ~26 entries but only a few DISTINCT distances (equal up to
+                // the last bit or two): the lanes of a run are grouped by exact distance (match.any), a lane counts the
+                // groups of its run with a smaller distance by their sizes -- one broadcast per group, not per entry --
+                // and orders itself inside its own group by (dst, image), one broadcast per member of the largest group.
+                const bool in = nb_l || nb_r;
+                const unsigned long long ke = in ? dg_payload_tie_key(P, e) : 0ull;
+                // (lanes outside every run get keys of their own: a truncated key has its id bits clear)
+                const unsigned runmask = __match_any_sync(FULL_MASK, in ? tk : (1u | ((uint32_t)lane << 1)));
+                const unsigned eqmask = __match_any_sync(FULL_MASK, __double_as_longlong(de)) & runmask;
+                const int gsz = __popc(eqmask);
+                const unsigned leaders = __ballot_sync(FULL_MASK, in && lane == __ffs(eqmask) - 1);
+                int cnt = 0;
+                const int first = __ffs(runmask) - 1;
+                for (unsigned lm = leaders; lm; lm &= lm - 1) {
+                    const int r = __ffs(lm) - 1;
                     const uint32_t tk_r = __shfl_sync(FULL_MASK, tk, r);
                     const double de_r = __shfl_sync(FULL_MASK, de, r);
-                    const unsigned long long ke_r = __shfl_sync(FULL_MASK, ke, r);
-                    if (tk_r == tk) {
-                        first = min(first, r);
-                        cnt += (de_r < de || (de_r == de && ke_r < ke)) ? 1 : 0;
-                    }
+                    const int sz_r = __shfl_sync(FULL_MASK, gsz, r);
+                    if (tk_r == tk && de_r < de) cnt += sz_r;
                 }
-                if (nb_l || nb_r) {
+                unsigned gm = in ? (eqmask & ~(1u << lane)) : 0u;
+                const int iters = __reduce_max_sync(FULL_MASK, __popc(gm));
+                for (int t = 0; t < iters; ++t) {
+                    const int src = gm ? __ffs(gm) - 1 : lane;
+                    gm &= gm - 1u;
+                    const unsigned long long ke_s = __shfl_sync(FULL_MASK, ke, src);
+                    cnt += (src != lane && ke_s < ke) ? 1 : 0;
+                }
+                if (in) {
                     int s0 = c0 + first;
                     if (first == 0) {  // the run may begin in an earlier window
                         for (int q = c0 - 1; q >= 0; --q) {

@@ -14,13 +14,21 @@ pkg = entry.load_package()
 syn = pkg.synthetic
 UNCAPPED = 0x7fffffff
 gb = pkg.GraphBuilder(0)
+only = None  # only=<jitter>,<r_c>,<cap or 0>: one case (for profiler captures)
 for kv in sys.argv[1:]:
     k, v = kv.split("=")
+    if k == "only":
+        only = tuple(float(x) for x in v.split(","))
+        continue
     gb.set_option(k, float(v))
 for jitter in (0.02, 0.0):
     b = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=s, jitter=jitter)[:4] for s in range(2000)])
     d_in = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (b.atom_offsets, b.x, b.y, b.z, b.lattices)]
+    if only and only[0] != jitter:
+        continue
     for rc, cap in ((8.0, UNCAPPED), (10.0, 20), (10.0, UNCAPPED)):
+        if only and (only[1] != rc or (only[2] == 0) != (cap == UNCAPPED)):
+            continue
         ms = []
         for _ in range(4):
             g = gb.build(*d_in, r_cutoff=rc, max_neighbors=cap, rbf_r_cutoff=rc, dr=0.25, device_inputs=True)
