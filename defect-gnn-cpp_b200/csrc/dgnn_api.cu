@@ -84,7 +84,7 @@ void dgnn_destroy(dgnn_ctx* ctx) {
     DevBuf* bufs[] = {&ctx->in_off, &ctx->in_x, &ctx->in_y, &ctx->in_z, &ctx->in_lat, &ctx->small, &ctx->fa, &ctx->fb, &ctx->fc, &ctx->geoms, &ctx->astruct,
                       &ctx->acell, &ctx->ncells32, &ctx->nitems32, &ctx->cell_base, &ctx->item_base, &ctx->scratch,
                       &ctx->cellcount, &ctx->cellstart, &ctx->cx, &ctx->cy, &ctx->cz, &ctx->cj, &ctx->cn,
-                      &ctx->deg, &ctx->deg_raw, &ctx->row_perm, &ctx->hits, &ctx->hits_d2, &ctx->hits_n, &ctx->hit_thr, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
+                      &ctx->deg, &ctx->deg_raw, &ctx->row_perm, &ctx->cmask, &ctx->cmask_tn, &ctx->hits, &ctx->hits_d2, &ctx->hits_n, &ctx->hit_thr, &ctx->lb_status, &ctx->row_ptr, &ctx->seo, &ctx->dst, &ctx->image, &ctx->dist, &ctx->rbf,
                       &ctx->tmp_in, &ctx->tmp_out, &ctx->stats, &ctx->col_x, &ctx->col_ei, &ctx->col_batch, &ctx->col_keys,
                       &ctx->col_lut, &ctx->col_table, &ctx->col_err, &ctx->view_a, &ctx->view_b, &ctx->tab_cnt, &ctx->tab_ptr,
                       &ctx->tab_val};
@@ -201,6 +201,8 @@ int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value) {
         ctx->sym_count = value != 0.0;
     } else if (!strcmp(name, "rbf_recur")) {
         ctx->rbf_recur = value != 0.0;
+    } else if (!strcmp(name, "cell32_mask")) {
+        ctx->cell32_mask = value != 0.0;
     } else if (!strcmp(name, "split_rows")) {
         ctx->split_rows = value != 0.0;
     } else if (!strcmp(name, "hit_threshold")) {
@@ -778,6 +780,15 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
         }
         tile_cap_report = A.tile_cap;
         if (cell32) {
+            // candidate words for the fill pass: 132 B per atom of the batch (skipped beyond 2 GB)
+            A.cmask = nullptr;
+            A.cmask_tn = nullptr;
+            if (ctx->cell32_mask && (double)N * 132.0 <= 2.0e9) {
+                ENSURE(ctx->cmask, (size_t)N * 128 + 16);
+                ENSURE(ctx->cmask_tn, (size_t)N * 4 + 16);
+                A.cmask = (uint32_t*)ctx->cmask.p;
+                A.cmask_tn = (int*)ctx->cmask_tn.p;
+            }
             CU(dg_launch_cell32(st, A, false, grid));
         } else {
             if ((int)dg_traverse_smem_bytes(A, false) > ctx->smem_optin)

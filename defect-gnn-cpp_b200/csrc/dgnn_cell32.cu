@@ -209,7 +209,7 @@ __device__ __forceinline__ int c32_drain(const DgTraverseArgs& A, const C32Share
 template <bool FILL, bool LIST>
 __device__ __forceinline__ void c32_sweep(const DgTraverseArgs& A, const C32Shared& sh, const C32Tile& tl, const C32Warp& w,
                                           const C32Src& S, int s0, int T, int lane, unsigned lt_mask, int& cnt, int& qn,
-                                          int& m, unsigned& near, int qcap) {
+                                          int& m, unsigned& near, int qcap, uint32_t& cand_word) {
     const float r2m = sh.r2m, r2p = sh.r2p, lowthr = sh.lowthr;
     for (int f0 = 0; f0 < T; f0 += 32) {
         unsigned slot;
@@ -218,6 +218,10 @@ __device__ __forceinline__ void c32_sweep(const DgTraverseArgs& A, const C32Shar
         const float4 c = tl.T[slot];
         const float dx = S.x - c.x, dy = S.y - c.y, dz = S.z - c.z;
         const float d2f = fmaf(dz, dz, fmaf(dy, dy, dx * dx));
+        if (!FILL && LIST && A.cmask) {  // the fill pass's candidates of this step (lane f0 / 32 keeps the word)
+            const unsigned cm = __ballot_sync(FULL_MASK, d2f <= r2p);
+            if (lane == (f0 >> 5)) cand_word = cm;
+        }
         if (!FILL) {
             // sure hits are tallied per lane; what lies in the guard band, or close enough to the source for the
             // epsilon rule (tallied above, taken back here), waits for the fp64 decision
@@ -439,7 +443,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
             for (int pb = k0; pb < k1; pb += 32) {
             // FILL: the rows' degrees and CSR offsets of up to 32 source points are fetched lane-parallel, one round trip
             // per cell instead of two dependent ones per atom
-            int pre_deg = 0;
+            int pre_deg = 0, pre_tn = -1;
             long long pre_o = 0;
             if (FILL && pb + lane < k1) {
                 const uint32_t wl = __float_as_uint(T[pb + lane].w);
@@ -447,6 +451,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                     const long long ig = G.atom_base + (int)JN[pb + lane].x;
                     pre_deg = A.deg_raw[ig];
                     pre_o = A.row_ptr[ig];
+                    if (A.cmask) pre_tn = A.cmask_tn[ig];
                 }
             }
             const int pe = pb + 32 < k1 ? pb + 32 : k1;
@@ -465,16 +470,32 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                     S.qx = A.cx[wb]; S.qy = A.cy[wb]; S.qz = A.cz[wb];
                 }
                 const long long iglob = G.atom_base + S.iloc;
-                int deg_known = 0;
+                int deg_known = 0, pre_tn_s = -1;
                 long long o = 0;
                 if (FILL) {
                     deg_known = __shfl_sync(FULL_MASK, pre_deg, ps - pb);
                     o = __shfl_sync(FULL_MASK, pre_o, ps - pb);
+                    pre_tn_s = __shfl_sync(FULL_MASK, pre_tn, ps - pb);
                     if (deg_known > W) continue;  // (rows beyond the register sort: the fp64 traversal's fill)
                 }
                 int cnt = 0, qn = 0, m = 0;
-                if (Tn >= 0) {
-                    c32_sweep<FILL, true>(A, sh, tl, w, S, 0, Tn, lane, lt_mask, cnt, qn, m, near, qcap);
+                uint32_t cand_word = 0u;
+                if (FILL && Tn >= 0 && pre_tn_s == Tn) {
+                    // candidates from the count pass's words: no tile reads, no arithmetic
+                    const uint32_t myw = A.cmask[(size_t)iglob * 32 + lane];
+                    for (int f0 = 0; f0 < Tn; f0 += 32) {
+                        const unsigned cm = __shfl_sync(FULL_MASK, myw, f0 >> 5);
+                        if (cm == 0u) continue;
+                        if ((cm >> lane) & 1u) w.q[qn + __popc(cm & lt_mask)] = w.idx[f0 + lane];
+                        qn += __popc(cm);
+                        if (qn > qcap - 32) {
+                            __syncwarp();
+                            c32_drain<true>(A, sh, tl, w, S, qn, lane, lt_mask, m, near);
+                            qn = 0;
+                        }
+                    }
+                } else if (Tn >= 0) {
+                    c32_sweep<FILL, true>(A, sh, tl, w, S, 0, Tn, lane, lt_mask, cnt, qn, m, near, qcap, cand_word);
                 } else {
                     // the stencil does not fit the slot list (very dense cells): one contiguous range at a time
                     const int row0 = ta * B.td[1] + tb;
@@ -484,7 +505,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                         const int base = (row0 + srow[q]) * zs + tc;
                         const int s0 = tcs[base + zlo];
                         c32_sweep<FILL, false>(A, sh, tl, w, S, s0, tcs[base + zhi + 1] - s0, lane, lt_mask, cnt, qn, m,
-                                               near, qcap);
+                                               near, qcap, cand_word);
                     }
                 }
                 __syncwarp();
@@ -494,6 +515,10 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
                     if (lane == 0) {
                         A.deg_raw[iglob] = deg;
                         A.deg_capped[iglob] = deg < A.max_neighbors ? deg : A.max_neighbors;
+                    }
+                    if (A.cmask) {
+                        if (Tn >= 0) A.cmask[(size_t)iglob * 32 + lane] = cand_word;
+                        if (lane == 0) A.cmask_tn[iglob] = Tn;
                     }
                     maxdeg = deg > maxdeg ? deg : maxdeg;
                 } else {

@@ -46,7 +46,7 @@ struct dgnn_ctx {
     DevBuf geoms, astruct, acell, ncells32, nitems32, cell_base, item_base, scratch;
     DevBuf cellcount, cellstart, cx, cy, cz, cj, cn;
     // results
-    DevBuf deg, deg_raw, row_perm, hits, hits_d2, hits_n, hit_thr, row_ptr, seo, dst, image, dist, rbf;
+    DevBuf deg, deg_raw, row_perm, cmask, cmask_tn, hits, hits_d2, hits_n, hit_thr, row_ptr, seo, dst, image, dist, rbf;
     // stand-alone rbf staging
     DevBuf tmp_in, tmp_out;
     DevBuf stats;
@@ -82,6 +82,7 @@ struct dgnn_ctx {
     int hit_threshold = 1;                // truncated rows: hit lists hold only pairs below a per-structure d2 threshold
     int fill_hits_warps = 0;              // (tuning) warps per CTA of k_fill_hits, 0: most resident warps per SM
     int tie_probe = 1;                    // 1: sampled rows choose the tie ranking of the uncapped fill pass, 0 / 2: fixed
+    int cell32_mask = 1;                  // fp32-tile count pass hands its candidate masks to the fill pass
     int split_rows = 1;                   // fill pass: rows beyond the full-occupancy row buffer get a launch of their own when few
     int sym_count = 1;                    // count pass sweeps j >= i only and decides both directions of a pair
     int rbf_recur = 1;                    // fused epilogue: Gaussian recurrence across a float4 (2 ex2 instead of 4)

@@ -88,6 +88,11 @@ struct DgTraverseArgs {
     double* dist;
     DgStats* stats;
     DgRbfEpi rbf;
+    // fp32-tile traversal: the count pass records, per source atom, which slots of its flattened stencil list passed
+    // the fp32 pre-filter (bit s of word w = list position 32 w + s; lists hold up to 1024 slots) and the list length;
+    // the fill pass then compacts its candidates from the words instead of repeating the sweep.  Null: not recorded.
+    uint32_t* cmask;             // [N * 32]
+    int* cmask_tn;               // [N] padded list length the words belong to (-1: none, the fill pass sweeps)
 };
 
 #define DG_ROWS_CAP 1024  // tile rows (td_a * td_b) <= 32 * 32
