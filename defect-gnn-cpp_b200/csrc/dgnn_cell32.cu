@@ -562,7 +562,7 @@ __global__ void __launch_bounds__(NW * 32, FILL ? 1 : 3) k_cell32(const __grid_c
 
 template <bool FILL, int NW, int MAXEPL>
 static cudaError_t c32_launch_t(cudaStream_t st, const DgTraverseArgs& a, int grid, size_t smem) {
-    cudaError_t e = cudaFuncSetAttribute(k_cell32<FILL, NW, MAXEPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = dg_raise_dyn_smem<k_cell32<FILL, NW, MAXEPL>>();
     if (e != cudaSuccess) return e;
     k_cell32<FILL, NW, MAXEPL><<<grid, a.n_warps * 32, smem, st>>>(a);
     return cudaGetLastError();

@@ -381,12 +381,12 @@ cudaError_t dg_launch_distance_tables(cudaStream_t st, long long a0, long long a
     if (grid > (long long)sm_count * 16) grid = (long long)sm_count * 16;
     cudaError_t e;
     if (mode == 0) {
-        e = cudaFuncSetAttribute(k_distance_tables<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = dg_raise_dyn_smem<k_distance_tables<0>>();
         if (e != cudaSuccess) return e;
         k_distance_tables<0><<<(unsigned)grid, DG_TABLE_THREADS, smem, st>>>(a0, a1, row_ptr, astruct, small, x, y, z, dst,
                                                                               image, table_ptr, out, m_cap);
     } else {
-        e = cudaFuncSetAttribute(k_distance_tables<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = dg_raise_dyn_smem<k_distance_tables<1>>();
         if (e != cudaSuccess) return e;
         k_distance_tables<1><<<(unsigned)grid, DG_TABLE_THREADS, smem, st>>>(a0, a1, row_ptr, astruct, small, x, y, z, dst,
                                                                               image, table_ptr, out, m_cap);

@@ -300,8 +300,7 @@ size_t dg_direct_smem_bytes(const DgDirectArgs& a, bool fill) {
 }
 template <bool FILL, int EPS, bool HITS, bool LEAN, bool DYN>
 static cudaError_t launch_direct_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e = cudaFuncSetAttribute(k_direct<FILL, 2, EPS, HITS, LEAN, DYN>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = dg_raise_dyn_smem<k_direct<FILL, 2, EPS, HITS, LEAN, DYN>>();
     if (e != cudaSuccess) return e;
     int occ = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct<FILL, 2, EPS, HITS, LEAN, DYN>, threads, smem);

@@ -265,7 +265,7 @@ size_t dg_direct_onepass_smem_bytes(const DgDirectArgs& a) {
 // single-pass build: a.lb_status ([ceil(N / n_warps)] chunk status words) must be zeroed on the stream before the launch
 template <int MINB, int EPS>
 static cudaError_t launch_one_t(cudaStream_t st, const DgDirectArgs& a, int sm_count, size_t smem, int threads) {
-    cudaError_t e = cudaFuncSetAttribute(k_direct_one<MINB, EPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = dg_raise_dyn_smem<k_direct_one<MINB, EPS>>();
     if (e != cudaSuccess) return e;
     int occ = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_direct_one<MINB, EPS>, threads, smem);

@@ -169,15 +169,15 @@ void dg_launch_hit_thresholds(cudaStream_t st, long long S, const DgSmall* small
 // Warps per CTA: the kernel is bound by latency at the occupancy its shared memory allows (10 KB per warp at 192-entry
 // rows: 2 CTAs of 8 warps), so the CTA size is the one that puts the most warps on an SM -- 3 CTAs of 7 warps there.
 static int pick_fill_hits_warps(const DgDirectArgs& a, int max_warps) {
-    static size_t cached_bytes = 0;
-    static int cached_max = 0, cached_pick = 0;
+    static thread_local size_t cached_bytes = 0;  // (a context is driven by one host thread at a time)
+    static thread_local int cached_max = 0, cached_pick = 0;
     const int W = a.hit_cap < a.row_cap ? a.hit_cap : a.row_cap;
     const size_t per_warp = dg_fill_hits_warp_bytes(W);
     if (per_warp == cached_bytes && max_warps == cached_max) return cached_pick;
     int best = max_warps, best_warps = 0;
     for (int n = max_warps; n >= 4 && n >= max_warps - 4; --n) {
         const size_t smem = (size_t)n * per_warp;
-        if (cudaFuncSetAttribute(k_fill_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) continue;
+        if (dg_raise_dyn_smem<k_fill_hits>() != cudaSuccess) continue;
         int occ = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill_hits, n * 32, smem) != cudaSuccess) continue;
         if (occ * n > best_warps) {
@@ -199,7 +199,7 @@ cudaError_t dg_launch_fill_hits(cudaStream_t st, const DgDirectArgs& a_in, int s
     else a.n_warps = pick_fill_hits_warps(a, a.n_warps);
     const size_t smem = dg_fill_hits_smem_bytes(a);
     const int threads = a.n_warps * 32;
-    cudaError_t e = cudaFuncSetAttribute(k_fill_hits, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = dg_raise_dyn_smem<k_fill_hits>();
     if (e != cudaSuccess) return e;
     int occ = 1;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_fill_hits, threads, smem);

@@ -6,6 +6,27 @@
 
 #include "geom.h"
 
+// Opt-in dynamic shared memory of a kernel is always raised to the DEVICE'S maximum, never to the size of the launch at
+// hand: the attribute is per function and device, and several contexts (host threads: graph::ShardedBuilder, the
+// streamed build's twin) launch the same kernels with different sizes -- between one thread's set and its launch
+// another could lower it and the launch failed with "invalid argument".  A constant value makes the race harmless.
+template <auto Kernel>
+inline cudaError_t dg_raise_dyn_smem() {
+    static thread_local int done_dev = -1;  // (once per host thread and device: the value never changes)
+    int dev = 0, optin = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev == done_dev) return cudaSuccess;
+    e = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    if (e != cudaSuccess) return e;
+    cudaFuncAttributes fa;
+    e = cudaFuncGetAttributes(&fa, Kernel);
+    if (e != cudaSuccess) return e;
+    e = cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, optin - (int)fa.sharedSizeBytes);
+    if (e == cudaSuccess) done_dev = dev;
+    return e;
+}
+
 // Device-resident statistics block, copied to the host at the (few) sync points of a build.
 struct DgStats {
     unsigned long long n_near;   // candidate pairs with |d - r_c| <= 1e-6

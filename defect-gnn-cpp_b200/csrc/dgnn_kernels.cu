@@ -789,11 +789,11 @@ cudaError_t dg_launch_traverse(cudaStream_t st, const DgTraverseArgs& a, bool fi
     cudaError_t e;
     const int threads = a.n_warps * 32;
     if (fill) {
-        e = cudaFuncSetAttribute(k_traverse<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = dg_raise_dyn_smem<k_traverse<true>>();
         if (e != cudaSuccess) return e;
         k_traverse<true><<<grid, threads, smem, st>>>(a);
     } else {
-        e = cudaFuncSetAttribute(k_traverse<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        e = dg_raise_dyn_smem<k_traverse<false>>();
         if (e != cudaSuccess) return e;
         k_traverse<false><<<grid, threads, smem, st>>>(a);
     }

@@ -121,6 +121,46 @@ def test_c3_triclinic_short_vectors(gpu_builder, gpu_builder_cell, oracle, syn):
     assert np.any(local_src == h.dst)
 
 
+def test_concurrent_contexts_on_one_device(pkg, oracle, syn):
+    """Several contexts driven by their own host threads on ONE device (graph::ShardedBuilder's shape, the streamed
+    build's twin): batches of different shapes -- different shared-memory sizes of the same kernels -- built side by side
+    must neither fail nor differ from the same builds done alone.  (The per-function opt-in shared-memory attribute is
+    set to the device maximum: a per-launch value raced between threads and a launch could fail with "invalid
+    argument".)"""
+    import threading
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    cases = [(syn.c2_batch(6, seed0=21), 8.0, None), (syn.c3_batch(40, seed0=5), 8.0, None),
+             (syn.c2_batch(3, seed0=9), 10.0, 20), (syn.c3_batch(25, seed0=77), 6.0, 12)]
+    ref = []
+    gb0 = pkg.GraphBuilder(0)
+    for b, rc, cap in cases:
+        h = build_and_fetch(gb0, b, rc, oracle.UNCAPPED if cap is None else cap, None, 0.2, 1e-10)
+        ref.append((h.n_edges, h.dst.copy(), h.dist.copy()))
+    gb0.close()
+    errors = []
+
+    def worker(k):
+        try:
+            gb = pkg.GraphBuilder(0)
+            b, rc, cap = cases[k]
+            for _ in range(25):
+                h = build_and_fetch(gb, b, rc, oracle.UNCAPPED if cap is None else cap, None, 0.2, 1e-10)
+                assert h.n_edges == ref[k][0]
+                assert np.array_equal(h.dst, ref[k][1]) and np.array_equal(h.dist, ref[k][2])
+            gb.close()
+        except Exception as e:  # noqa: BLE001
+            errors.append((k, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=(k,)) for k in range(len(cases))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
+
+
 def test_skewed_degrees_split_the_fill_pass(pkg, oracle, syn):
     """A few dense rows must not size every warp's row buffer: rows beyond the full-occupancy buffer are filled by a
     second launch (dgnn_build_info.split_big_rows), the rest by the first; both equal the oracle, and the single-launch
