@@ -614,6 +614,7 @@ int dgnn_build(dgnn_ctx* ctx, const dgnn_batch* b, dgnn_graphs* out) {
                 }
             }
             D.row_begin = D.row_end = 0;
+            if (sym) dg_launch_cap_degrees(st, D, ctx->sm_count);  // one launch for all chunks' rows
             dg_scan_i32_i64(st, (const int*)ctx->deg.p, (long long*)ctx->row_ptr.p, N, (long long*)ctx->scratch.p);
             if (split_cap > 0 && D.hit_cap == 0 && !sym)  // (the symmetric count's k_cap_degrees has tallied them)
                 dg_launch_count_big_rows(st, N, (const int*)ctx->astruct.p, small, (const int*)ctx->deg_raw.p, split_cap,

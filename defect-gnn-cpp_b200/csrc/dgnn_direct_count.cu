@@ -201,14 +201,10 @@ static cudaError_t launch_count_sym_m(cudaStream_t st, const DgDirectArgs& a, in
     k_direct_count_sym<MINB, E><<<(unsigned)grid, 256, 0, st>>>(a);
     if (a.eps_mode == 0) { DG_LAUNCH_SYM(0) } else { DG_LAUNCH_SYM(1) }
 #undef DG_LAUNCH_SYM
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    long long g2 = (rows + 255) / 256;
-    if (g2 > (long long)sm_count * 8) g2 = (long long)sm_count * 8;
-    k_cap_degrees<<<(unsigned)g2, 256, 0, st>>>(a);
-    dg_direct_launch_bump(2);
+    dg_direct_launch_bump(1);
     return cudaGetLastError();
 }
+// (once per build, after the count pass of every upload chunk: the caller resets the row range)
 void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count) {
     const long long rows = (a.row_end > 0 ? a.row_end : a.n_atoms) - a.row_begin;
     if (rows <= 0) return;
@@ -217,7 +213,8 @@ void dg_launch_cap_degrees(cudaStream_t st, const DgDirectArgs& a, int sm_count)
     k_cap_degrees<<<(unsigned)g2, 256, 0, st>>>(a);
     dg_direct_launch_bump(1);
 }
-// symmetric count pass of rows [row_begin, row_end): deg_raw must be zero there; eps_mode 0 or 1 only
+// symmetric count pass of rows [row_begin, row_end): deg_raw must be zero there; eps_mode 0 or 1 only.  Leaves raw degrees;
+// dg_launch_cap_degrees turns them into deg_capped / max_deg (and the row-class tallies) afterwards.
 cudaError_t dg_launch_direct_count_sym(cudaStream_t st, const DgDirectArgs& a, int sm_count, int min_blocks) {
     if (a.n_atoms <= 0) return cudaSuccess;
     if (a.eps_mode > 1) return cudaErrorInvalidValue;
