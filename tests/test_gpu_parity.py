@@ -179,7 +179,13 @@ def test_skewed_degrees_split_the_fill_pass(pkg, oracle, syn):
         for b, rc, cap in ((c3, 8.0, None), (mixed, 8.0, None), (c3, 8.0, 400), (c3, 6.0, None)):
             h = check_batch(gb, oracle, b, rc, cap, dr=0.2)
             seen.append((gb.info().split_big_rows, gb.info().row_cap, int(np.diff(h.row_ptr).max())))
+        # the same skewed cells next to structures on the cell-list path (whose rows keep the buffer for the largest row)
+        gb.set_option("direct_max_atoms", 100)
+        both = syn.concat([c3.structure(s) for s in range(150)] + [syn.c2_batch(2, seed0=8).structure(s) for s in range(2)])
+        check_batch(gb, oracle, both, 8.0, None, dr=0.2)
+        assert gb.info().n_cell_structs == 2
         if split:
+            assert gb.info().split_big_rows > 0
             assert seen[0][0] > 0 and seen[0][1] < seen[0][2]      # C3: max degree ~800, buffer of the first launch ~350
             assert all(n * 8 <= c3.n_atoms for n, _, _ in seen)
         else:
