@@ -306,7 +306,7 @@ void* dgnn_stream(dgnn_ctx* ctx);
  *                     a guard band; 0: the fp64 traversal (A/B reference)
  *   sym_count         1 (default): the count pass sweeps j >= i and decides both directions of a pair
  * Tuning and testing knobs (tile sizes, sort buckets, look-back spin limit ...) are spelled "tune.<name>"; they are
- * listed next to dgnn_set_option in csrc/dgnn_api.cu and are not part of the interface. */
+ * listed next to dgnn_set_option in csrc/dgnn_options.cu and are not part of the interface. */
 int dgnn_set_option(dgnn_ctx* ctx, const char* name, double value);
 
 #ifdef __cplusplus
