@@ -150,6 +150,7 @@ __device__ __forceinline__ int c32_build_list(const DgGeom& G, const ItemBox& B,
 }
 
 struct C32TilePayload {  // FILL: hit word = tile slot; (atom, image) from the staged table
+    static constexpr bool kSweepOrder = false;
     uint32_t* hw;
     const uint2* JN;
     __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }

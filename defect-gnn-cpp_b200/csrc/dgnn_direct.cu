@@ -179,7 +179,7 @@ __global__ void __launch_bounds__(256, MINB) k_direct(const DgDirectArgs A) {
                 /* it cannot happen (row_cap >= max degree of the count pass) */                                        \
                 if (lane == 0 && !A.defer_big) atomicExch(&A.stats->overflow, 1);                                        \
             } else {                                                                                                     \
-                dg_row_sort_emit<LEAN>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image,    \
+                dg_row_sort_emit<LEAN, true>(rb, m, keep, A.n_buckets, A.inv_rc, A.key_scale, A.row_ptr[a], A.dst, A.image,    \
                                        A.dist, A.stats, lane, A.rbf);                                                    \
             }
     if (DYN) {

@@ -166,8 +166,8 @@ __device__ __forceinline__ void dg_one_finish_row(const DgDirectArgs& A, const D
         op.wait();
         if (valid && lane == 0) atomicAdd(&A.stats->n_fallback_rows, 1);
     } else {
-        dg_row_sort_emit_op(rb, P.m, P.keep, A.n_buckets, A.inv_rc, A.key_scale, op, A.dst, A.image, A.dist, A.stats,
-                            lane, A.rbf);
+        dg_row_sort_emit_op<DgOneOffset, false, true>(rb, P.m, P.keep, A.n_buckets, A.inv_rc, A.key_scale, op, A.dst, A.image,
+                                                      A.dist, A.stats, lane, A.rbf);
     }
     if (valid && lane == 0) {
         A.deg_raw[P.a] = P.m;

@@ -276,7 +276,11 @@ __device__ __forceinline__ uint32_t dg_dist_key(double d, double key_scale) {
 // Payload policies give the sort access to an entry's (dst, packed image):
 // ---------------------------------------------------------------------------------------------------------------------
 // (load_item / store_item move an entry inside the row buffer: the top-k prefilter compacts the survivors in place)
+// kSweepOrder: entries of one neighbour atom appear in the row buffer in ascending (n_a, n_b, n_c) -- true for rows the
+// direct-path sweeps compact (a lane owns an atom and walks its images in order; the top-k prefilter's compaction is
+// stable); the tie ranking then orders a group of exactly equal distances by dst alone (dg_row_sort_bitonic).
 struct RowBufPayload {  // traversal kernels: rj / rn arrays filled by the ballot compaction
+    static constexpr bool kSweepOrder = false;
     int* rj;
     uint32_t* rn;
     __device__ __forceinline__ void get(int e, int& j, uint32_t& img) const {
@@ -289,7 +293,13 @@ struct RowBufPayload {  // traversal kernels: rj / rn arrays filled by the ballo
         rn[e] = v.y;
     }
 };
+struct SweepRowPayload : RowBufPayload {  // ... of the direct-path sweeps (k_direct, k_direct_one)
+    static constexpr bool kSweepOrder = true;
+};
+template <bool SWEEP> struct DgSelectPayload { typedef RowBufPayload type; };
+template <> struct DgSelectPayload<true> { typedef SweepRowPayload type; };
 struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (dg_pack_hit in dgnn_direct.cu)
+    static constexpr bool kSweepOrder = false;
     uint32_t* hw;
     __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
     __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
@@ -300,6 +310,7 @@ struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (d
     }
 };
 struct CloudPayload {  // hit-list fill pass, cell-list structures: hit word = index into the binned image cloud
+    static constexpr bool kSweepOrder = false;
     uint32_t* hw;
     __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
     __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
@@ -542,13 +553,32 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                     const int sz_r = __shfl_sync(FULL_MASK, gsz, r);
                     if (tk_r == tk && de_r < de) cnt += sz_r;
                 }
-                unsigned gm = in ? (eqmask & ~(1u << lane)) : 0u;
-                const int iters = __reduce_max_sync(FULL_MASK, __popc(gm));
-                for (int t = 0; t < iters; ++t) {
-                    const int src = gm ? __ffs(gm) - 1 : lane;
-                    gm &= gm - 1u;
-                    const unsigned long long ke_s = __shfl_sync(FULL_MASK, ke, src);
-                    cnt += (src != lane && ke_s < ke) ? 1 : 0;
+                if (Payload::kSweepOrder) {
+                    // inside a group the order is (dst, image), and the images of one dst already sit in order (lane
+                    // order = entry order): a radix walk over the bits of dst splits the group into smaller / equal dst
+                    const int dj = in ? (int)(ke >> 32) : 0;
+                    const unsigned ord = __reduce_or_sync(FULL_MASK, (unsigned)dj);
+                    unsigned ltm = 0u, eq = in ? eqmask : 0u;
+                    for (int b = 31 - __clz(ord | 1u); b >= 0; --b) {
+                        const bool bit = ((dj >> b) & 1) != 0;
+                        const unsigned B = __ballot_sync(FULL_MASK, bit);
+                        if (bit) {
+                            ltm |= eq & ~B;
+                            eq &= B;
+                        } else {
+                            eq &= ~B;
+                        }
+                    }
+                    cnt += __popc(ltm) + __popc(eq & ((1u << lane) - 1u));
+                } else {
+                    unsigned gm = in ? (eqmask & ~(1u << lane)) : 0u;
+                    const int iters = __reduce_max_sync(FULL_MASK, __popc(gm));
+                    for (int t = 0; t < iters; ++t) {
+                        const int src = gm ? __ffs(gm) - 1 : lane;
+                        gm &= gm - 1u;
+                        const unsigned long long ke_s = __shfl_sync(FULL_MASK, ke, src);
+                        cnt += (src != lane && ke_s < ke) ? 1 : 0;
+                    }
                 }
                 if (in) {
                     int s0 = c0 + first;
@@ -714,17 +744,20 @@ __device__ __forceinline__ void dg_row_sort_bitonic_any(double* rd, uint32_t* sk
 // Sort the m collected entries of the warp's row buffer and write the first `keep` to the CSR arrays at offset o.
 // NBk (number of buckets) is a power of two, 32 <= NBk <= 2048.  All 32 lanes must call.
 // rbf.K4 > 0: fused Gaussian RBF epilogue straight from the sorted distances in shared memory.
-template <class OP, bool LEAN = false>
+// SWEEP: the row buffer was filled by a direct-path sweep (SweepRowPayload)
+template <class OP, bool LEAN = false, bool SWEEP = false>
 __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
                                                     double key_scale, OP& op, int* __restrict__ dst,
                                                     uint32_t* __restrict__ image, double* __restrict__ dist,
                                                     DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     if (m <= DG_BITONIC_MAX) {
-        const RowBufPayload P{sm.rj, sm.rn};
+        typedef typename DgSelectPayload<SWEEP>::type PL;
+        PL P;
+        P.rj = sm.rj;
+        P.rn = sm.rn;
         // padded sorted words: bs (unused by this path) and sk are adjacent, 2 * row_cap words
-        const long long o = dg_row_sort_bitonic_any_op<RowBufPayload, OP, LEAN>(sm.rd, sm.bs, sm.fd, sm.cnt, P, m, keep,
-                                                                                key_scale, op, dst, image, dist, stats,
-                                                                                lane);
+        const long long o = dg_row_sort_bitonic_any_op<PL, OP, LEAN>(sm.rd, sm.bs, sm.fd, sm.cnt, P, m, keep, key_scale, op,
+                                                                     dst, image, dist, stats, lane);
         if (o >= 0 && rbf.K4 > 0) {
             dg_rbf_row(sm.fd, keep, o, lane, rbf);
             __syncwarp();
@@ -826,11 +859,12 @@ __device__ __forceinline__ void dg_row_sort_emit_op(const RowBuf& sm, int m, int
     }
 }
 
-template <bool LEAN = false>
+template <bool LEAN = false, bool SWEEP = false>
 __device__ __forceinline__ void dg_row_sort_emit(const RowBuf& sm, int m, int keep, int NBk, float inv_rc,
                                                  double key_scale, long long o, int* __restrict__ dst,
                                                  uint32_t* __restrict__ image, double* __restrict__ dist,
                                                  DgStats* __restrict__ stats, int lane, const DgRbfEpi& rbf) {
     DgFixedOffset op{o};
-    dg_row_sort_emit_op<DgFixedOffset, LEAN>(sm, m, keep, NBk, inv_rc, key_scale, op, dst, image, dist, stats, lane, rbf);
+    dg_row_sort_emit_op<DgFixedOffset, LEAN, SWEEP>(sm, m, keep, NBk, inv_rc, key_scale, op, dst, image, dist, stats, lane,
+                                                    rbf);
 }
