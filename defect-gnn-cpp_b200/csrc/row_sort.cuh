@@ -323,6 +323,13 @@ struct CloudPayload {  // hit-list fill pass, cell-list structures: hit word = i
     }
 };
 template <class Payload>
+__device__ __forceinline__ int dg_payload_dst(const Payload& P, int e) {
+    int j;
+    uint32_t img;
+    P.get(e, j, img);
+    return j;
+}
+template <class Payload>
 __device__ __forceinline__ unsigned long long dg_payload_tie_key(const Payload& P, int e) {
     int j;
     uint32_t img;
@@ -588,7 +595,10 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                             if ((wq & ~IDMASK) != tk) break;
                             const int f = (int)(wq & IDMASK);
                             const double df = rd[f];
-                            cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                            // (sweep-ordered rows: f sits earlier in the run, i.e. has the smaller entry id -- with the
+                            // same dst it is the smaller image)
+                            if (Payload::kSweepOrder) cnt += (df < de || (df == de && dg_payload_dst(P, f) <= (int)(ke >> 32))) ? 1 : 0;
+                            else cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
                             s0 = q;
                         }
                     }
@@ -598,7 +608,8 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                         if ((wq & ~IDMASK) != tk) break;
                         const int f = (int)(wq & IDMASK);
                         const double df = rd[f];
-                        cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                        if (Payload::kSweepOrder) cnt += (df < de || (df == de && dg_payload_dst(P, f) < (int)(ke >> 32))) ? 1 : 0;
+                        else cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
                     }
                     rank = s0 + cnt;
                 }
