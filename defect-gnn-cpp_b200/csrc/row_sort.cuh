@@ -365,6 +365,44 @@ struct DgFixedOffset {
 // instantiates -- no top-k prefilter (its rows are never truncated) and the compact per-entry tie ranking instead of
 // the warp-cooperative one.  Same results; measured on the same box, the full variant costs that kernel 6 % (8.82
 // against 8.33 ms: two registers spill), and calling either piece out of line costs more (8.96 - 9.0 ms).
+// Tie runs longer than the 32-position window of the ranking below (sweep-ordered rows only, see SweepRowPayload): the
+// part of the run that sits in another window is brought into the lanes 32 entries at a time (vS: lane holds an entry of
+// the run, dS its distance, jS its dst) and every lane of the run in the CURRENT window (mine: distance de, dst dj) adds
+// the number of those entries ordered before it -- groups of a smaller distance by their sizes, its own distance's group
+// by a radix walk over the bits of dst.  inclusive: the block lies BEFORE the window (its entries have the smaller entry
+// ids: with the same dst they come first); otherwise after it.  All 32 lanes must call.
+__device__ __forceinline__ int dg_tie_block_count(bool vS, double dS, int jS, bool mine, double de, int dj, bool inclusive,
+                                                  int lane) {
+    const unsigned vmask = __ballot_sync(FULL_MASK, vS);
+    const long long pat = vS ? __double_as_longlong(dS) : (long long)(0xfff8000000000000ULL | (unsigned long long)lane);
+    const unsigned eqS = __match_any_sync(FULL_MASK, pat) & vmask;
+    const unsigned leadS = __ballot_sync(FULL_MASK, vS && lane == __ffs(eqS) - 1);
+    int cnt = 0;
+    unsigned mygrp = 0u;
+    for (unsigned lm = leadS; lm; lm &= lm - 1) {
+        const int r = __ffs(lm) - 1;
+        const double d_r = __shfl_sync(FULL_MASK, dS, r);
+        const unsigned g_r = __shfl_sync(FULL_MASK, eqS, r);
+        if (mine) {
+            if (d_r < de) cnt += __popc(g_r);
+            else if (d_r == de) mygrp = g_r;
+        }
+    }
+    const unsigned ord = __reduce_or_sync(FULL_MASK, (unsigned)(vS ? jS : 0) | (unsigned)(mine ? dj : 0));
+    unsigned ltm = 0u, eq = mygrp;
+    for (int b = 31 - __clz(ord | 1u); b >= 0; --b) {
+        const unsigned B = __ballot_sync(FULL_MASK, vS && ((jS >> b) & 1) != 0);
+        if ((dj >> b) & 1) {
+            ltm |= eq & ~B;
+            eq &= B;
+        } else {
+            eq &= ~B;
+        }
+    }
+    if (mine) cnt += __popc(ltm) + (inclusive ? __popc(eq) : 0);
+    return cnt;
+}
+
 template <int EPL, class Payload, class OP, bool LEAN = false>
 __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd, uint32_t* __restrict__ sk,
                                                          float* __restrict__ fd, int* __restrict__ tie,
@@ -587,7 +625,43 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                         cnt += (src != lane && ke_s < ke) ? 1 : 0;
                     }
                 }
-                if (in) {
+                int run_start = c0;
+                if (Payload::kSweepOrder) {
+                    // parts of a run outside this window, 32 entries at a time (dg_tie_block_count); only the run that
+                    // holds position c0 can begin earlier, only a run that fills the whole window can go on after it
+                    const int dj = in ? (int)(ke >> 32) : 0;
+                    const uint32_t tk0 = __shfl_sync(FULL_MASK, tk, 0);
+                    const bool in0 = __shfl_sync(FULL_MASK, in ? 1 : 0, 0) != 0;
+                    const bool mine0 = in && in0 && tk == tk0;
+                    bool more = in0 && c0 > 0 && (sk[DG_SKI(c0 - 1)] & ~IDMASK) == tk0;
+                    for (int qend = c0; more; qend -= 32) {
+                        const int q = qend - 32 + lane;
+                        const uint32_t wq = q >= 0 ? sk[DG_SKI(q)] : 0u;
+                        const bool vS = q >= 0 && (wq & ~IDMASK) == tk0;
+                        const int f = (int)(wq & IDMASK);
+                        cnt += dg_tie_block_count(vS, vS ? rd[f] : 0.0, vS ? dg_payload_dst(P, f) : 0, mine0, de, dj, true, lane);
+                        const unsigned vm = __ballot_sync(FULL_MASK, vS);
+                        run_start = qend - __popc(vm);
+                        more = vm == FULL_MASK && qend - 32 > 0 && (sk[DG_SKI(qend - 33)] & ~IDMASK) == tk0;
+                    }
+                    const int last = adv - 1;  // (a run that goes on after the window fills all of it: adv == 32)
+                    const uint32_t tkL = __shfl_sync(FULL_MASK, tk, last);
+                    const bool inL = __shfl_sync(FULL_MASK, in ? 1 : 0, last) != 0;
+                    const bool mineL = in && inL && tk == tkL;
+                    more = inL && c0 + adv < lim && (sk[DG_SKI(c0 + adv)] & ~IDMASK) == tkL;
+                    for (int qs = c0 + adv; more; qs += 32) {
+                        const int q = qs + lane;
+                        const uint32_t wq = q < lim ? sk[DG_SKI(q)] : 0u;
+                        const bool vS = q < lim && (wq & ~IDMASK) == tkL;
+                        const int f = (int)(wq & IDMASK);
+                        cnt += dg_tie_block_count(vS, vS ? rd[f] : 0.0, vS ? dg_payload_dst(P, f) : 0, mineL, de, dj, false, lane);
+                        const unsigned vm = __ballot_sync(FULL_MASK, vS);
+                        more = vm == FULL_MASK && qs + 32 < lim && (sk[DG_SKI(qs + 32)] & ~IDMASK) == tkL;
+                    }
+                }
+                if (in && Payload::kSweepOrder) {
+                    rank = (first == 0 ? run_start : c0 + first) + cnt;
+                } else if (in) {
                     int s0 = c0 + first;
                     if (first == 0) {  // the run may begin in an earlier window
                         for (int q = c0 - 1; q >= 0; --q) {
@@ -595,10 +669,7 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                             if ((wq & ~IDMASK) != tk) break;
                             const int f = (int)(wq & IDMASK);
                             const double df = rd[f];
-                            // (sweep-ordered rows: f sits earlier in the run, i.e. has the smaller entry id -- with the
-                            // same dst it is the smaller image)
-                            if (Payload::kSweepOrder) cnt += (df < de || (df == de && dg_payload_dst(P, f) <= (int)(ke >> 32))) ? 1 : 0;
-                            else cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                            cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
                             s0 = q;
                         }
                     }
@@ -608,8 +679,7 @@ __device__ __forceinline__ long long dg_row_sort_bitonic(double* __restrict__ rd
                         if ((wq & ~IDMASK) != tk) break;
                         const int f = (int)(wq & IDMASK);
                         const double df = rd[f];
-                        if (Payload::kSweepOrder) cnt += (df < de || (df == de && dg_payload_dst(P, f) < (int)(ke >> 32))) ? 1 : 0;
-                        else cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
+                        cnt += (df < de || (df == de && dg_payload_tie_key(P, f) < ke)) ? 1 : 0;
                     }
                     rank = s0 + cnt;
                 }

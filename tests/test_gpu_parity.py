@@ -574,6 +574,48 @@ def test_tie_probe_selects_the_tie_ranking(pkg, oracle, syn):
         gb.close()
 
 
+@pytest.mark.parametrize("onepass", [0, 1])
+def test_long_tie_runs_cross_the_ranking_window(pkg, oracle, syn, onepass):
+    """Coordination shells of more than 32 (and more than 64) exactly or nearly equal distances: the warp-cooperative
+    ranking works on 32 sorted positions at a time and counts the rest of such a run block by block
+    (dg_tie_block_count: groups of equal distance by size, the own group by a radix walk over dst).  Simple-cubic
+    supercells (shells of up to 72+ sites, every site a different dst or another image of the same one) and ideal
+    perovskite cells at r_c = 10 / 12, uncapped and truncated in the middle of a shell, against the exhaustive oracle."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+
+    def cubic(n, a):
+        g = np.arange(n) * a
+        X, Y, Z = np.meshgrid(g, g, g, indexing="ij")
+        return X.ravel().astype(np.float64), Y.ravel().astype(np.float64), Z.ravel().astype(np.float64), np.diag([n * a] * 3)
+
+    def fcc(n, a):  # the shell at r^2 = 6.5 a^2 has 72 sites (320 sites within it)
+        g = np.arange(n)
+        C = np.stack(np.meshgrid(g, g, g, indexing="ij"), axis=-1).reshape(-1, 1, 3).astype(np.float64)
+        B = np.array([[0, 0, 0], [0.5, 0.5, 0], [0.5, 0, 0.5], [0, 0.5, 0.5]], dtype=np.float64)[None]
+        P = ((C + B) * a).reshape(-1, 3)
+        return P[:, 0].copy(), P[:, 1].copy(), P[:, 2].copy(), np.diag([n * a] * 3)
+
+    sc = syn.concat([cubic(4, 2.0), cubic(3, 1.7), cubic(5, 2.5)])
+    fc = syn.concat([fcc(3, 3.0), fcc(2, 3.0)])
+    ideal = syn.concat([syn.perovskite_supercell(4, 4, 2, seed=s, jitter=0.0)[:4] for s in range(2)])
+    gb = pkg.GraphBuilder(0)
+    for k, v in (("onepass", onepass), ("hit_cap", 0), ("tune.tie_probe", 2)):
+        gb.set_option(k, v)
+    longest = 0
+    for b, rc, cap in ((sc, 6.0, None), (sc, 7.5, None), (sc, 6.0, 50), (sc, 7.5, 129), (fc, 7.8, None), (fc, 7.8, 280),
+                       (fc, 7.8, 300), (ideal, 10.0, None), (ideal, 12.0, None), (ideal, 10.0, 100)):
+        h = check_batch(gb, oracle, b, rc, cap, dr=0.25, algo=oracle.ALGO_BRUTE)
+        # longest run of equal rounded distances in any row of this build (what the ranking had to order)
+        for a in range(0, b.n_atoms, 37):
+            d = np.round(h.dist[h.row_ptr[a]:h.row_ptr[a + 1]], 9)
+            if d.size:
+                longest = max(longest, int(np.unique(d, return_counts=True)[1].max()))
+    assert longest > 64
+    gb.close()
+
+
 def test_thresholded_hit_lists_of_truncated_rows(pkg, oracle, syn):
     """Truncated rows (max_neighbors << degree): the count pass stores only accepted pairs below a per-structure d2
     threshold sized from the density for a little more than max_neighbors + 1 of them, and the fill pass sorts those.
