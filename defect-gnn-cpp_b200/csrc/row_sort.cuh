@@ -299,7 +299,7 @@ struct SweepRowPayload : RowBufPayload {  // ... of the direct-path sweeps (k_di
 template <bool SWEEP> struct DgSelectPayload { typedef RowBufPayload type; };
 template <> struct DgSelectPayload<true> { typedef SweepRowPayload type; };
 struct HitWordPayload {  // hit-list fill pass: the count pass's packed words (dg_pack_hit in dgnn_direct.cu)
-    static constexpr bool kSweepOrder = false;
+    static constexpr bool kSweepOrder = true;  // (the lists are compacted by the same sweep, the threshold only filters)
     uint32_t* hw;
     __device__ __forceinline__ uint2 load_item(int e) const { return make_uint2(hw[e], 0u); }
     __device__ __forceinline__ void store_item(int e, uint2 v) const { hw[e] = v.x; }
