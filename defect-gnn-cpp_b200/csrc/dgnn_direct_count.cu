@@ -62,6 +62,45 @@ __device__ __forceinline__ void sweep_row_sym(const DgDirectArgs& A, const DgSma
         const int mc1 = __reduce_max_sync(FULL_MASK, c0 ? c1 : 0);
         const int mc2 = __reduce_max_sync(FULL_MASK, c0 ? c2 : 0);
         int theirs = 0;
+        // (innermost body: this direction's test and the mirror's)
+#define DG_SYM_BODY                                                                                                  \
+                    const bool act = act_ab && sc < c2;                                                              \
+                    const double ox = DG_ADD(ob0, DG_MUL(ncd, L20)); /* offset(n), neighbor_list.cpp:82-84 */        \
+                    const double oy = DG_ADD(ob1, DG_MUL(ncd, L21));                                                 \
+                    const double oz = DG_ADD(ob2, DG_MUL(ncd, L22));                                                 \
+                    const double dx = DG_SUB(sx, DG_ADD(xj, ox));                                                    \
+                    const double dy = DG_SUB(sy, DG_ADD(yj, oy));                                                    \
+                    const double dz = DG_SUB(sz, DG_ADD(zj, oz));                                                    \
+                    const double d2 = DG_ADD(DG_ADD(DG_MUL(dx, dx), DG_MUL(dy, dy)), DG_MUL(dz, dz));                \
+                    bool hit = act && d2 < r2;                                                                       \
+                    if (EPS == 1) hit = hit && !(self && d2 == 0.0);                                                 \
+                    bool hit_m = hit && !self; /* the mirror of a self image is another image of this very row */    \
+                    if (act && fabs(d2 - r2) <= band) {                                                              \
+                        near += (d2 >= A.near_d2_lo && d2 <= A.near_d2_hi) ? 1u : 0u;                                \
+                        if (!self) {                                                                                 \
+                            const double ex = DG_SUB(xj, DG_SUB(sx, ox)); /* pos_i + (-offset) == pos_i - offset */  \
+                            const double ey = DG_SUB(yj, DG_SUB(sy, oy));                                            \
+                            const double ez = DG_SUB(zj, DG_SUB(sz, oz));                                            \
+                            const double e2 = DG_ADD(DG_ADD(DG_MUL(ex, ex), DG_MUL(ey, ey)), DG_MUL(ez, ez));        \
+                            hit_m = e2 < r2;                                                                         \
+                            near += (e2 >= A.near_d2_lo && e2 <= A.near_d2_hi) ? 1u : 0u;                            \
+                        }                                                                                            \
+                    }                                                                                                \
+                    own += hit ? 1 : 0;                                                                              \
+                    theirs += hit_m ? 1 : 0;
+        if (mc0 == 1 && mc1 == 1) {
+            // one image along a and b for every lane of the chunk (cells at least 2 r_c wide along those axes): only the
+            // loop over n_c remains
+            const double nad = (double)lo0, nbd = (double)lo1;
+            const double ob0 = DG_ADD(DG_MUL(nad, L00), DG_MUL(nbd, L10));
+            const double ob1 = DG_ADD(DG_MUL(nad, L01), DG_MUL(nbd, L11));
+            const double ob2 = DG_ADD(DG_MUL(nad, L02), DG_MUL(nbd, L12));
+            const bool act_ab = c0 > 0 && c1 > 0;
+            double ncd = (double)lo2;
+            for (int sc = 0; sc < mc2; ++sc, ncd += 1.0) {
+                DG_SYM_BODY
+            }
+        } else {
         double nad = (double)lo0;
         for (int sa = 0; sa < mc0; ++sa, nad += 1.0) {
             const double oa0 = DG_MUL(nad, L00), oa1 = DG_MUL(nad, L01), oa2 = DG_MUL(nad, L02);
@@ -73,33 +112,12 @@ __device__ __forceinline__ void sweep_row_sym(const DgDirectArgs& A, const DgSma
                 const bool act_ab = sa < c0 && sb < c1;
                 double ncd = (double)lo2;
                 for (int sc = 0; sc < mc2; ++sc, ncd += 1.0) {
-                    const bool act = act_ab && sc < c2;
-                    const double ox = DG_ADD(ob0, DG_MUL(ncd, L20));  // offset(n), neighbor_list.cpp:82-84
-                    const double oy = DG_ADD(ob1, DG_MUL(ncd, L21));
-                    const double oz = DG_ADD(ob2, DG_MUL(ncd, L22));
-                    const double dx = DG_SUB(sx, DG_ADD(xj, ox));
-                    const double dy = DG_SUB(sy, DG_ADD(yj, oy));
-                    const double dz = DG_SUB(sz, DG_ADD(zj, oz));
-                    const double d2 = DG_ADD(DG_ADD(DG_MUL(dx, dx), DG_MUL(dy, dy)), DG_MUL(dz, dz));
-                    bool hit = act && d2 < r2;
-                    if (EPS == 1) hit = hit && !(self && d2 == 0.0);
-                    bool hit_m = hit && !self;  // the mirror of a self image is another image of this very row
-                    if (act && fabs(d2 - r2) <= band) {
-                        near += (d2 >= A.near_d2_lo && d2 <= A.near_d2_hi) ? 1u : 0u;
-                        if (!self) {
-                            const double ex = DG_SUB(xj, DG_SUB(sx, ox));  // pos_i + (-offset) == pos_i - offset
-                            const double ey = DG_SUB(yj, DG_SUB(sy, oy));
-                            const double ez = DG_SUB(zj, DG_SUB(sz, oz));
-                            const double e2 = DG_ADD(DG_ADD(DG_MUL(ex, ex), DG_MUL(ey, ey)), DG_MUL(ez, ez));
-                            hit_m = e2 < r2;
-                            near += (e2 >= A.near_d2_lo && e2 <= A.near_d2_hi) ? 1u : 0u;
-                        }
-                    }
-                    own += hit ? 1 : 0;
-                    theirs += hit_m ? 1 : 0;
+                    DG_SYM_BODY
                 }
             }
         }
+        }
+#undef DG_SYM_BODY
         if (theirs) atomicAdd(A.deg_raw + (base + jj), theirs);
     }
     own = __reduce_add_sync(FULL_MASK, own);

@@ -167,6 +167,25 @@ __device__ __forceinline__ int traverse_row(const DgDirectArgs& A, const DgSmall
             const int mc0 = __reduce_max_sync(FULL_MASK, c0);
             const int mc1 = __reduce_max_sync(FULL_MASK, c0 ? c1 : 0);
             const int mc2 = __reduce_max_sync(FULL_MASK, c0 ? c2 : 0);
+            if (mc0 == 1 && mc1 == 1) {
+                // one image along a and b for every lane of the chunk (cells at least 2 r_c wide along those axes: the C2
+                // supercells): only the loop over n_c remains -- same images, same order as the nest below, without its
+                // loop-carried moves (headline fill 8.33 -> 8.10 ms, capped count 3.15 -> 2.88 ms, same-box A/B)
+                const double na_d = (double)lo0, nb_d = (double)lo1;
+                const double ob0 = DG_ADD(DG_MUL(na_d, L00), DG_MUL(nb_d, L10));
+                const double ob1 = DG_ADD(DG_MUL(na_d, L01), DG_MUL(nb_d, L11));
+                const double ob2 = DG_ADD(DG_MUL(na_d, L02), DG_MUL(nb_d, L12));
+                const bool act_ab = c0 > 0 && c1 > 0;
+                double ncd = (double)lo2;
+                for (int sc = 0; sc < mc2; ++sc, ncd += 1.0) {
+                    const double px = DG_ADD(xj, DG_ADD(ob0, DG_MUL(ncd, L20)));
+                    const double py = DG_ADD(yj, DG_ADD(ob1, DG_MUL(ncd, L21)));
+                    const double pz = DG_ADD(zj, DG_ADD(ob2, DG_MUL(ncd, L22)));
+                    test_point<FILL, EPS, HITS, ONE>(A, S, rb, hrow, hd2, act_ab && sc < c2, self, jj, px, py, pz, lo0, lo1,
+                                                     lo2 + sc, lt_mask, m, near, ht);
+                }
+                continue;
+            }
             double nad = (double)lo0;
             for (int sa = 0; sa < mc0; ++sa, nad += 1.0) {
                 const double oa0 = DG_MUL(nad, L00), oa1 = DG_MUL(nad, L01), oa2 = DG_MUL(nad, L02);
